@@ -1,0 +1,298 @@
+"""
+oracle.py -- TEST INFRASTRUCTURE ONLY (see the header of mc_oracle.c).
+
+ctypes front-end of ``oracle/libmc_oracle.so`` (the plain-C restatement of the reference's native
+functions) plus a numpy/scipy restatement of the Python glue between the native calls on the
+per-pile k-NN path.  Every function cites the reference file:line it follows (paths relative to
+the tanaylab/metacells v0.9.5 tree).  Nothing under ``metacells_b200/`` may import this module.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Optional, Tuple
+
+import numpy as np
+import scipy.sparse as sp
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libmc_oracle.so")
+_lib: Optional[ctypes.CDLL] = None
+
+
+def build(force: bool = False) -> str:
+    """Compile mc_oracle.c with gcc (seconds).  Building the checker is not using it."""
+    src = os.path.join(_HERE, "mc_oracle.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
+        subprocess.check_call([cc, "-O2", "-fPIC", "-shared", "-o", _LIB_PATH, src, "-lm"])
+    return _LIB_PATH
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        _lib = ctypes.CDLL(build())
+    return _lib
+
+
+def _p(array: np.ndarray, dtype: str) -> ctypes.c_void_p:
+    assert array.dtype == np.dtype(dtype), (array.dtype, dtype)
+    assert array.flags.c_contiguous
+    return ctypes.c_void_p(array.ctypes.data)
+
+
+_i64 = ctypes.c_int64
+_u64 = ctypes.c_uint64
+_i32 = ctypes.c_int32
+
+
+def _check(code: int) -> None:
+    if code != 0:
+        raise MemoryError("mc_oracle: allocation failed")
+
+
+# ---------------------------------------------------------------------------------------------
+# native restatements
+# ---------------------------------------------------------------------------------------------
+
+
+def downsample_compressed(data: np.ndarray, indptr: np.ndarray, samples: np.ndarray, seed: int) -> np.ndarray:
+    """downsample.cpp:171-192; returns the downsampled ``data`` (same sparsity structure)."""
+    out = np.zeros_like(data)
+    _check(lib().mco_downsample_compressed_f32_i32_f32(
+        _p(data, "float32"), _p(indptr, "int32"), _p(out, "float32"), _p(samples, "int32"), _i64(len(indptr) - 1), _u64(seed)))
+    return out
+
+
+def downsample_dense(matrix: np.ndarray, samples: np.ndarray, seed: int) -> np.ndarray:
+    """downsample.cpp:131-151."""
+    out = np.zeros_like(matrix)
+    _check(lib().mco_downsample_dense_f32_f32(
+        _p(matrix, "float32"), _p(out, "float32"), _p(samples, "int32"), _i64(matrix.shape[0]), _i64(matrix.shape[1]), _u64(seed)))
+    return out
+
+
+def downsample_array(vector: np.ndarray, samples: int, seed: int) -> np.ndarray:
+    """downsample.cpp:116-128."""
+    out = np.zeros_like(vector)
+    _check(lib().mco_downsample_array_f32_f32(_p(vector, "float32"), _p(out, "float32"), _i64(len(vector)), _i32(samples), _u64(seed)))
+    return out
+
+
+def correlate_dense(dense: np.ndarray) -> np.ndarray:
+    """correlate.cpp:350-431."""
+    out = np.empty((dense.shape[0], dense.shape[0]), dtype="float32")
+    _check(lib().mco_correlate_dense_f32(_p(dense, "float32"), _i64(dense.shape[0]), _i64(dense.shape[1]), _i64(dense.shape[1]), _p(out, "float32")))
+    return out
+
+
+def cross_correlate_dense(first: np.ndarray, second: np.ndarray) -> np.ndarray:
+    """correlate.cpp:433-494."""
+    out = np.empty((first.shape[0], second.shape[0]), dtype="float32")
+    _check(lib().mco_cross_correlate_dense_f32(
+        _p(first, "float32"), _i64(first.shape[0]), _p(second, "float32"), _i64(second.shape[0]), _i64(first.shape[1]), _p(out, "float32")))
+    return out
+
+
+def pairs_correlate_dense(first: np.ndarray, second: np.ndarray) -> np.ndarray:
+    """correlate.cpp:496-527."""
+    out = np.empty(first.shape[0], dtype="float32")
+    _check(lib().mco_pairs_correlate_dense_f32(_p(first, "float32"), _p(second, "float32"), _i64(first.shape[0]), _i64(first.shape[1]), _p(out, "float32")))
+    return out
+
+
+def rank_matrix(matrix: np.ndarray, ascending: bool) -> np.ndarray:
+    """rank.cpp:79-87 (returns a ranked copy)."""
+    out = np.array(matrix, dtype="float32", order="C", copy=True)
+    _check(lib().mco_rank_matrix_f32(_p(out, "float32"), _i64(out.shape[0]), _i64(out.shape[1]), ctypes.c_int(int(ascending))))
+    return out
+
+
+def rank_rows(matrix: np.ndarray, rank: int) -> np.ndarray:
+    """rank.cpp:24-36."""
+    out = np.empty(matrix.shape[0], dtype="float32")
+    _check(lib().mco_rank_rows_f32(_p(matrix, "float32"), _i64(matrix.shape[0]), _i64(matrix.shape[1]), _p(out, "float32"), _i64(rank)))
+    return out
+
+
+def collect_top(degree: int, similarity: np.ndarray, ranks: bool) -> Tuple[np.ndarray, np.ndarray]:
+    """top_per.cpp:67-92; returns (indices int32[N*degree], data float32[N*degree])."""
+    rows = similarity.shape[0]
+    indices = np.empty(rows * degree, dtype="int32")
+    data = np.empty(rows * degree, dtype="float32")
+    _check(lib().mco_collect_top_f32(_i64(degree), _p(similarity, "float32"), _i64(rows), _i64(similarity.shape[1]),
+                                     _p(indices, "int32"), _p(data, "float32"), ctypes.c_int(int(ranks))))
+    return indices, data
+
+
+def collect_pruned(degree: int, data: np.ndarray, indices: np.ndarray, indptr: np.ndarray) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """prune_per.cpp:56-105; returns (data, indices, indptr) trimmed to indptr[-1]."""
+    bands = len(indptr) - 1
+    out_data = np.empty(max(bands * degree, 1), dtype="float32")
+    out_indices = np.empty(max(bands * degree, 1), dtype="int32")
+    out_indptr = np.empty(bands + 1, dtype="int32")
+    _check(lib().mco_collect_pruned_f32_i32_i32(_i64(degree), _p(data, "float32"), _p(indices, "int32"), _p(indptr, "int32"),
+                                                _i64(bands), _p(out_data, "float32"), _p(out_indices, "int32"), _p(out_indptr, "int32")))
+    nnz = int(out_indptr[-1])
+    return out_data[:nnz], out_indices[:nnz], out_indptr
+
+
+def relayout(data: np.ndarray, indices: np.ndarray, indptr: np.ndarray, bands_out: int) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """relayout.cpp:73-108 + :152-167 as sequenced by computation.py:251-303."""
+    out_data = np.empty_like(data)
+    out_indices = np.empty_like(indices)
+    out_indptr = np.empty(bands_out + 1, dtype="int32")
+    _check(lib().mco_relayout_f32_i32_i32(_p(data, "float32"), _p(indices, "int32"), _p(indptr, "int32"), _i64(len(indptr) - 1),
+                                          _i64(bands_out), _p(out_data, "float32"), _p(out_indices, "int32"), _p(out_indptr, "int32")))
+    return out_data, out_indices, out_indptr
+
+
+# ---------------------------------------------------------------------------------------------
+# numpy / scipy glue between the native calls
+# ---------------------------------------------------------------------------------------------
+
+
+def downsample_samples(total_per_cell: np.ndarray, min_samples: int = 750, min_quantile: float = 0.05, max_quantile: float = 0.5) -> int:
+    """tools/downsample.py:84-93 (defaults parameters.py: downsample_min_samples etc.)."""
+    return int(round(min(max(min_samples, np.quantile(total_per_cell, min_quantile)), np.quantile(total_per_cell, max_quantile))))
+
+
+def log_fraction(dense: np.ndarray, regularization: float = 1 / 7) -> np.ndarray:
+    """pipeline/direct.py:242-249 + utilities/computation.py:679-741 (base 2, normalization 0)."""
+    data = np.array(dense, dtype="float32", copy=True)
+    data += regularization
+    np.log2(data, out=data)
+    return data
+
+
+def knn_k(n_obs: int, cell_umis: np.ndarray, target_metacell_size: int = 48, target_metacell_umis: int = 160000,
+          knn_k_size_factor: float = 2.0, knn_k_umis_quantile: float = 0.1, min_knn_k: int = 30) -> int:
+    """pipeline/direct.py:251-267."""
+    by_size = int(round(n_obs / target_metacell_size))
+    by_median = int(round(knn_k_size_factor * target_metacell_umis / float(np.median(cell_umis))))
+    by_quantile = int(round(target_metacell_umis / np.quantile(cell_umis, knn_k_umis_quantile)))
+    return max(by_size, by_median, by_quantile, min_knn_k or 0)
+
+
+def similarity(dense: np.ndarray, method: str = "abs_pearson") -> np.ndarray:
+    """utilities/computation.py:454-467 (reproducible corrcoef) + tools/similarity.py:213-215."""
+    result = correlate_dense(np.ascontiguousarray(dense, dtype="float32"))
+    result[np.isnan(result)] = 0.0
+    np.fill_diagonal(result, 1.0)
+    if method == "abs_pearson":
+        np.absolute(result, out=result)
+    return result
+
+
+def rank_outgoing(sim: np.ndarray) -> np.ndarray:
+    """tools/knn_graph.py:285-297."""
+    work = np.copy(sim)
+    np.fill_diagonal(work, np.min(work) - 1)
+    ranks = rank_matrix(work, ascending=False)
+    assert np.all(np.diagonal(ranks) == sim.shape[0])
+    return ranks
+
+
+def balance_ranks(outgoing_ranks: np.ndarray, k: int, balanced_ranks_factor: float) -> sp.csr_matrix:
+    """tools/knn_graph.py:300-340.  The float32 operation order (multiply, sqrt, the 2**21 offset
+    round trip) is kept because it rounds."""
+    size = outgoing_ranks.shape[0]
+    dense = np.array(outgoing_ranks, dtype="float32", copy=True)
+    dense *= outgoing_ranks.transpose()
+    np.sqrt(dense, out=dense)
+    max_rank = k * balanced_ranks_factor
+    dense *= -1
+    dense += 2**21
+    max_index_of_each = np.asarray(dense.argmax(axis=1)).reshape(-1)
+    dense += max_rank + 1 - 2**21
+    rows = np.arange(size)
+    preserved = dense[rows, max_index_of_each]
+    preserved[preserved < 1] = 1
+    dense[dense < 0] = 0
+    np.fill_diagonal(dense, 0)
+    dense[rows, max_index_of_each] = preserved
+    return sp.csr_matrix(dense)
+
+
+def prune_per(compressed, top: int):
+    """utilities/computation.py:1356-1393."""
+    is_csr = compressed.format == "csr"
+    data, indices, indptr = collect_pruned(top, compressed.data, compressed.indices, compressed.indptr)
+    constructor = sp.csr_matrix if is_csr else sp.csc_matrix
+    return constructor((data, indices, indptr), shape=compressed.shape)
+
+
+def csc_to_csr(csc: sp.csc_matrix) -> sp.csr_matrix:
+    """utilities/computation.py:251-303 (_relayout_compressed)."""
+    data, indices, indptr = relayout(csc.data, csc.indices, csc.indptr, csc.shape[0])
+    return sp.csr_matrix((data, indices, indptr), shape=csc.shape)
+
+
+def csr_to_csc(csr: sp.csr_matrix) -> sp.csc_matrix:
+    data, indices, indptr = relayout(csr.data, csr.indices, csr.indptr, csr.shape[1])
+    return sp.csc_matrix((data, indices, indptr), shape=csr.shape)
+
+
+def prune_ranks(balanced: sp.csr_matrix, k: int, incoming_degree_factor: float, outgoing_degree_factor: float) -> sp.csr_matrix:
+    """tools/knn_graph.py:343-392."""
+    size = balanced.shape[0]
+    incoming_degree = min(int(round(k * incoming_degree_factor)), size - 1)
+    outgoing_degree = min(int(round(k * outgoing_degree_factor)), size - 1)
+    rows = np.arange(size)
+    max_index_of_each = np.asarray(balanced.argmax(axis=1)).reshape(-1)
+    preserved_values = np.asarray(balanced[rows, max_index_of_each]).reshape(-1)
+    assert np.min(preserved_values) > 0
+    preserved = sp.coo_matrix((preserved_values, (rows, max_index_of_each)), shape=balanced.shape)
+    # knn_graph.py:371: symmetric=True relayout is a reinterpretation of the same three arrays.
+    pruned = sp.csc_matrix((balanced.data, balanced.indices, balanced.indptr), shape=balanced.shape)
+    pruned = prune_per(pruned, incoming_degree)
+    pruned = csc_to_csr(pruned)
+    pruned = prune_per(pruned, outgoing_degree)
+    pruned = pruned.maximum(preserved)
+    pruned = pruned.maximum(preserved.transpose())
+    pruned = sp.csr_matrix(pruned)
+    pruned.sort_indices()
+    return pruned
+
+
+def weigh_edges(pruned: sp.csr_matrix) -> sp.csr_matrix:
+    """tools/knn_graph.py:395-407."""
+    totals = np.asarray(pruned.sum(axis=1)).reshape(-1).astype("float32")
+    scale = np.reciprocal(totals)
+    weights = sp.csr_matrix(pruned.multiply(scale[:, None]))
+    weights.sort_indices()
+    return weights
+
+
+def knn_graph(sim: np.ndarray, k: int, balanced_ranks_factor: float = float(np.sqrt(10)), incoming_degree_factor: float = 3.0,
+              outgoing_degree_factor: float = 1.0, min_outgoing_degree: int = 2):
+    """tools/knn_graph.py:251-275 (the k-growth loop).  Returns (outgoing_weights, pruned_ranks, balanced_ranks, k)."""
+    while True:
+        ranks = rank_outgoing(sim)
+        balanced = balance_ranks(ranks, k, balanced_ranks_factor)
+        pruned = prune_ranks(balanced, k, incoming_degree_factor, outgoing_degree_factor)
+        if np.min(np.diff(pruned.indptr)) >= min_outgoing_degree:
+            break
+        k += max(1, int(k / 10))
+    return weigh_edges(pruned), pruned, balanced, k
+
+
+# ---------------------------------------------------------------------------------------------
+# the compiled reference (oracle/_ref), when present
+# ---------------------------------------------------------------------------------------------
+
+
+def load_ref():
+    """Import oracle/_ref/extensions*.so (the unmodified reference C++), or return None."""
+    import glob
+    import importlib.util
+
+    found = glob.glob(os.path.join(_HERE, "_ref", "extensions*.so"))
+    if not found:
+        return None
+    spec = importlib.util.spec_from_file_location("extensions", found[0])
+    module = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(module)
+    return module
