@@ -1,0 +1,123 @@
+// Shared helpers for the sm_100a kernels of libmcb200.so (error plumbing, warp/block primitives,
+// monotone float keys).  Nothing in here is a public symbol; the C-ABI lives in include/mcb200.h.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#define MCB_OK 0
+#define MCB_ERR_CUDA 1
+#define MCB_ERR_ARG 2
+#define MCB_ERR_UNSUPPORTED 3
+
+namespace mcb {
+
+// Thread-local last error message, read through mcb_last_error().
+char* error_buffer();
+int fail(int code, const char* format, ...);
+
+#define MCB_CUDA(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t mcb_err__ = (expr);                                                             \
+        if (mcb_err__ != cudaSuccess)                                                               \
+            return ::mcb::fail(MCB_ERR_CUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr,          \
+                               cudaGetErrorString(mcb_err__));                                      \
+    } while (0)
+
+#define MCB_TRY(expr)                  \
+    do {                               \
+        int mcb_code__ = (expr);       \
+        if (mcb_code__ != MCB_OK)      \
+            return mcb_code__;         \
+    } while (0)
+
+#define MCB_REQUIRE(cond, ...)                           \
+    do {                                                 \
+        if (!(cond))                                     \
+            return ::mcb::fail(MCB_ERR_ARG, __VA_ARGS__); \
+    } while (0)
+
+// Device scratch that frees itself on the stream it was allocated on (stream-ordered pool).
+struct Scratch {
+    void* ptr = nullptr;
+    cudaStream_t stream = nullptr;
+    Scratch() = default;
+    Scratch(const Scratch&) = delete;
+    Scratch& operator=(const Scratch&) = delete;
+    int alloc(size_t bytes, cudaStream_t s) {
+        stream = s;
+        MCB_CUDA(cudaMallocAsync(&ptr, bytes ? bytes : 16, s));
+        return MCB_OK;
+    }
+    template <typename T>
+    T* as() const {
+        return reinterpret_cast<T*>(ptr);
+    }
+    ~Scratch() {
+        if (ptr)
+            cudaFreeAsync(ptr, stream);
+    }
+};
+
+int sm_count();
+
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+#ifdef __CUDACC__
+
+// Monotone map float -> uint32: a < b (as floats, no NaN)  <=>  key(a) < key(b); -0.0 < +0.0.
+__device__ __forceinline__ uint32_t float_to_ordered(float value) {
+    uint32_t bits = __float_as_uint(value);
+    return bits ^ ((bits & 0x80000000u) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float ordered_to_float(uint32_t key) {
+    uint32_t bits = key ^ ((key & 0x80000000u) ? 0x80000000u : 0xffffffffu);
+    return __uint_as_float(bits);
+}
+// As std::less on floats treats -0.0 == +0.0, canonicalise zeros before building keys.
+__device__ __forceinline__ float canonical_zero(float value) { return value == 0.0f ? 0.0f : value; }
+
+__device__ __forceinline__ int warp_inclusive_scan(int value, int lane) {
+#pragma unroll
+    for (int offset = 1; offset < 32; offset <<= 1) {
+        int other = __shfl_up_sync(0xffffffffu, value, offset);
+        if (lane >= offset)
+            value += other;
+    }
+    return value;
+}
+
+__device__ __forceinline__ int warp_reduce_sum(int value) {
+#pragma unroll
+    for (int offset = 16; offset > 0; offset >>= 1) value += __shfl_xor_sync(0xffffffffu, value, offset);
+    return value;
+}
+
+// Exclusive block scan of one int per thread; `warp_sums` is shared scratch of >= 33 ints.
+// Returns the exclusive prefix of this thread; *total receives the block total (all threads).
+__device__ __forceinline__ int block_exclusive_scan(int value, int* warp_sums, int* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = (blockDim.x + 31) >> 5;
+    int inclusive = warp_inclusive_scan(value, lane);
+    if (lane == 31)
+        warp_sums[warp] = inclusive;
+    __syncthreads();
+    if (warp == 0) {
+        int sum = lane < warps ? warp_sums[lane] : 0;
+        int scanned = warp_inclusive_scan(sum, lane);
+        warp_sums[lane] = scanned - sum;
+        if (lane == 31)
+            warp_sums[32] = scanned;
+    }
+    __syncthreads();
+    int result = warp_sums[warp] + inclusive - value;
+    *total = warp_sums[32];
+    __syncthreads();
+    return result;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace mcb

@@ -1,0 +1,236 @@
+// UMI downsampling (multinomial sampling without replacement), bit-exact with the reference's
+// downsample.cpp:81-113 (downsample_slice) for the same random_seed.
+//
+// What the reference does per row: build a binary sum tree over the row's counts and, `samples`
+// times, draw r = minstd() % remaining_total, walk the tree to the leaf holding the r-th
+// remaining UMI (gene order), and remove it (downsample.cpp:46-79, 107-112).  The walk is only a
+// way to find "the r-th remaining UMI", so any order-statistic structure gives identical output.
+//
+// B200 formulation (one CTA per row, BATCH draws decoded in parallel):
+//   * x_d = seed * 48271^(d+1) mod (2^31-1) is a closed form, so every draw's raw value is known
+//     up front, and so is its modulus T - d: r_d = x_d % (T - d).
+//   * r_d is a rank among the UMIs left after draws 0..d-1.  Inside a batch that starts at d0, the
+//     rank relative to the UMIs left at the START of the batch is obtained by replaying the earlier
+//     draws of the batch backwards:  q = r_d;  for j = d-1 .. d0:  q += (r_j <= q).
+//     (Draw j removed rank r_j in its own coordinate system; everything at or above it shifts.)
+//   * q is then located in the inclusive prefix sum of the remaining counts (binary search in
+//     shared memory), the leaf count is decremented atomically, and the prefix sum is rebuilt
+//     once per batch with a block scan.
+// The output is original - remaining, so no separate output accumulator is needed.
+#include "common.cuh"
+
+namespace mcb {
+
+namespace {
+
+constexpr int DS_THREADS = 256;  // == draws decoded per batch
+constexpr uint32_t MINSTD_A = 48271u;
+constexpr uint32_t MINSTD_M = 2147483647u;
+
+__device__ __forceinline__ uint32_t mulmod(uint32_t a, uint32_t b) {
+    return (uint32_t)(((uint64_t)a * (uint64_t)b) % MINSTD_M);
+}
+
+struct DownsampleParams {
+    const float* input;
+    float* output;
+    const int32_t* indptr;   // nullptr: dense rows of `columns` elements
+    const int32_t* samples;  // per row; nullptr: use `samples_all`
+    int32_t samples_all;
+    int64_t columns;
+    int64_t rows;
+    uint64_t seed;
+    int use_row_seed;        // 1: seed + 997 * row (matrix forms); 0: seed as given (array form)
+    uint32_t* workspace;     // 2 * capacity uint32 per CTA when rows do not fit shared memory
+    int64_t capacity;        // elements per array in `workspace` (0: shared memory only)
+    int smem_capacity;       // elements per array that fit shared memory
+    int* error_flag;
+};
+
+__global__ void __launch_bounds__(DS_THREADS) downsample_kernel(DownsampleParams p) {
+    extern __shared__ uint32_t smem[];
+    __shared__ uint32_t draws[DS_THREADS];
+    __shared__ uint32_t pow_a[DS_THREADS];  // 48271^(t+1) mod m
+    __shared__ int scan_scratch[34];
+    __shared__ unsigned long long total_shared;
+
+    const int tid = threadIdx.x;
+    {
+        // a^(tid+1) by square-and-multiply (8 bits of exponent)
+        uint32_t result = 1, base = MINSTD_A;
+        for (int e = tid + 1; e; e >>= 1) {
+            if (e & 1)
+                result = mulmod(result, base);
+            base = mulmod(base, base);
+        }
+        pow_a[tid] = result;
+    }
+    __syncthreads();
+    const uint32_t pow_batch = pow_a[DS_THREADS - 1];  // a^BATCH
+
+    for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
+        const int64_t lo = p.indptr ? (int64_t)p.indptr[row] : row * p.columns;
+        const int64_t hi = p.indptr ? (int64_t)p.indptr[row + 1] : lo + p.columns;
+        const int n = (int)(hi - lo);
+        const int32_t samples = p.samples ? p.samples[row] : p.samples_all;
+        const float* in = p.input + lo;
+        float* out = p.output + lo;
+
+        if (samples < 0 || n == 0)
+            continue;  // downsample.cpp:86-88: output left untouched
+        if (n == 1) {  // downsample.cpp:90-93
+            if (tid == 0)
+                out[0] = (double)samples < (double)in[0] ? (float)samples : in[0];
+            continue;
+        }
+
+        uint32_t* count;
+        uint32_t* cumulative;
+        if (n <= p.smem_capacity) {
+            count = smem;
+            cumulative = smem + p.smem_capacity;
+        } else if ((int64_t)n <= p.capacity) {
+            count = p.workspace + (int64_t)blockIdx.x * 2 * p.capacity;
+            cumulative = count + p.capacity;
+        } else {
+            if (tid == 0)
+                atomicExch(p.error_flag, 1);
+            continue;
+        }
+
+        // Items per thread for the prefix sums: odd, so stride-`items` accesses are conflict free.
+        const int items = ((n + DS_THREADS - 1) / DS_THREADS) | 1;
+        const int begin = min(tid * items, n), end = min(begin + items, n);
+
+        if (tid == 0)
+            total_shared = 0;
+        __syncthreads();
+        {
+            unsigned long long partial = 0;
+            for (int i = tid; i < n; i += DS_THREADS) {
+                uint32_t c = (uint32_t)in[i];  // float -> size_t truncation (downsample.cpp:24)
+                count[i] = c;
+                partial += c;
+            }
+            for (int offset = 16; offset > 0; offset >>= 1) partial += __shfl_xor_sync(0xffffffffu, partial, offset);
+            if ((tid & 31) == 0)
+                atomicAdd(&total_shared, partial);
+        }
+        __syncthreads();
+        const unsigned long long total64 = total_shared;
+        __syncthreads();
+        if (total64 <= (unsigned long long)samples) {  // downsample.cpp:100-105
+            if (out != in)
+                for (int i = tid; i < n; i += DS_THREADS) out[i] = in[i];
+            continue;
+        }
+        if (total64 >= 0xffffffffull) {
+            if (tid == 0)
+                atomicExch(p.error_flag, 2);
+            continue;
+        }
+        const uint32_t total = (uint32_t)total64;
+
+        uint64_t row_seed = p.seed;
+        if (p.use_row_seed)
+            row_seed = p.seed == 0 ? 0 : p.seed + (uint64_t)row * 997ull;
+        uint32_t state = (uint32_t)(row_seed % MINSTD_M);
+        if (state == 0)
+            state = 1;  // std::linear_congruential_engine::seed
+
+        for (int first = 0; first < samples; first += DS_THREADS) {
+            // (1) inclusive prefix sums of the remaining counts
+            {
+                int sum = 0;
+                for (int i = begin; i < end; ++i) sum += (int)count[i];
+                int block_total;
+                int running = block_exclusive_scan(sum, scan_scratch, &block_total);
+                for (int i = begin; i < end; ++i) {
+                    running += (int)count[i];
+                    cumulative[i] = (uint32_t)running;
+                }
+            }
+            // (2) raw draws of this batch
+            const int batch = min(DS_THREADS, samples - first);
+            if (tid < batch) {
+                uint32_t x = mulmod(state, pow_a[tid]);
+                draws[tid] = x % (total - (uint32_t)(first + tid));  // downsample.cpp:111
+            }
+            state = mulmod(state, pow_batch);
+            __syncthreads();
+            // (3) ranks relative to the start of the batch, (4) locate and remove
+            if (tid < batch) {
+                uint32_t q = draws[tid];
+                const int top = (tid & ~31) + 31;
+                for (int j = min(top, batch - 1); j >= 0; --j) {
+                    uint32_t earlier = draws[j];
+                    q += (j < tid && earlier <= q) ? 1u : 0u;
+                }
+                int left = 0, right = n - 1;  // smallest i with cumulative[i] > q
+                while (left < right) {
+                    int middle = (left + right) >> 1;
+                    if (cumulative[middle] > q)
+                        right = middle;
+                    else
+                        left = middle + 1;
+                }
+                atomicSub(&count[left], 1u);
+            }
+            __syncthreads();
+        }
+        for (int i = tid; i < n; i += DS_THREADS) out[i] = (float)((uint32_t)in[i] - count[i]);
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
+                      int32_t samples_all, int64_t rows, int64_t columns, int64_t max_row_size, uint64_t seed,
+                      int use_row_seed, cudaStream_t stream) {
+    if (rows == 0)
+        return MCB_OK;
+    DownsampleParams p{};
+    p.input = input;
+    p.output = output;
+    p.indptr = indptr;
+    p.samples = samples;
+    p.samples_all = samples_all;
+    p.columns = columns;
+    p.rows = rows;
+    p.seed = seed;
+    p.use_row_seed = use_row_seed;
+
+    // Shared-memory capacity classes: 8 B per element; smaller classes allow more CTAs per SM.
+    int smem_capacity = 2048;
+    while (smem_capacity < max_row_size && smem_capacity < 24576) smem_capacity *= 2;
+    if (smem_capacity > 24576)
+        smem_capacity = 24576;
+    p.smem_capacity = smem_capacity;
+    const size_t smem_bytes = (size_t)smem_capacity * 8;
+
+    int64_t grid = rows;
+    Scratch workspace, flag;
+    MCB_TRY(flag.alloc(sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(flag.ptr, 0, sizeof(int), stream));
+    p.error_flag = flag.as<int>();
+    if (max_row_size > smem_capacity) {
+        grid = rows < (int64_t)sm_count() * 2 ? rows : (int64_t)sm_count() * 2;
+        p.capacity = max_row_size;
+        MCB_TRY(workspace.alloc((size_t)grid * 2 * (size_t)max_row_size * sizeof(uint32_t), stream));
+        p.workspace = workspace.as<uint32_t>();
+    }
+    MCB_CUDA(cudaFuncSetAttribute(downsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    downsample_kernel<<<(unsigned)grid, DS_THREADS, smem_bytes, stream>>>(p);
+    MCB_CUDA(cudaGetLastError());
+    int host_flag = 0;
+    MCB_CUDA(cudaMemcpyAsync(&host_flag, flag.ptr, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    if (host_flag == 1)
+        return fail(MCB_ERR_ARG, "downsample: a row is wider than the stated max_row_size");
+    if (host_flag == 2)
+        return fail(MCB_ERR_UNSUPPORTED, "downsample: a row totals 2^32 UMIs or more");
+    return MCB_OK;
+}
+
+}  // namespace mcb
