@@ -60,6 +60,35 @@ int mcb_dev_downsample_dense_f32_f32(const float* input, float* output, const in
 int mcb_host_downsample_array_f32_f32(const float* input, float* output, int64_t size, int32_t samples,
                                       uint64_t random_seed);
 
+/* ---- correlate.cpp --------------------------------------------------------------------------- */
+
+/* correlate_dense<F>  (correlate.cpp:350-431): all-pairs Pearson r between the rows of
+ * input[rows, columns] (row stride in elements >= columns).  output: float32 [rows, rows],
+ * symmetric, unit diagonal, 0 for constant rows, clamped to [-1, 1]; NaN results are stored as 0
+ * (the reference's caller does that at computation.py:465).
+ * float32 input runs on the tensor cores (tcgen05, 3xTF32 split); float64 input in float64 FMA. */
+int mcb_host_correlate_dense_f32(const float* input, int64_t rows, int64_t columns, int64_t row_stride, float* output);
+int mcb_host_correlate_dense_f64(const double* input, int64_t rows, int64_t columns, int64_t row_stride, float* output);
+/* Device form; absolute != 0 stores |r| (fuses tools/similarity.py:214-215 "abs_pearson"). */
+int mcb_dev_correlate_dense_f32(const float* input, int64_t rows, int64_t columns, int64_t row_stride, float* output,
+                                int64_t out_stride, int absolute, void* stream);
+
+/* cross_correlate_dense<F>  (correlate.cpp:433-494): output float32 [first_rows, second_rows]. */
+int mcb_host_cross_correlate_dense_f32(const float* first, int64_t first_rows, int64_t first_stride, const float* second,
+                                       int64_t second_rows, int64_t second_stride, int64_t columns, float* output);
+int mcb_host_cross_correlate_dense_f64(const double* first, int64_t first_rows, int64_t first_stride, const double* second,
+                                       int64_t second_rows, int64_t second_stride, int64_t columns, float* output);
+int mcb_dev_cross_correlate_dense_f32(const float* first, int64_t first_rows, const float* second, int64_t second_rows,
+                                      int64_t columns, float* output, int64_t out_stride, void* stream);
+
+/* pairs_correlate_dense<F>  (correlate.cpp:496-527): output[i] = r(first[i, :], second[i, :]). */
+int mcb_host_pairs_correlate_dense_f32(const float* first, int64_t first_stride, const float* second, int64_t second_stride,
+                                       int64_t rows, int64_t columns, float* output);
+int mcb_host_pairs_correlate_dense_f64(const double* first, int64_t first_stride, const double* second, int64_t second_stride,
+                                       int64_t rows, int64_t columns, float* output);
+int mcb_dev_pairs_correlate_dense_f32(const float* first, const float* second, int64_t rows, int64_t columns, float* output,
+                                      void* stream);
+
 /* @@APPEND@@ */
 
 #ifdef __cplusplus
