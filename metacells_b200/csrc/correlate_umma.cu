@@ -5,16 +5,26 @@
 //
 // Replaces correlate_dense / cross_correlate_dense (reference correlate.cpp:350-494).
 //
-// Kernel shape (one 128 x 128 output tile per CTA, 192 threads):
+// Persistent kernel, one CTA per SM, 192 threads, 128 x 128 output tiles taken from a host-built
+// tile list (super-blocks of 8 x 8 tiles so that a wave of CTAs re-uses row panels out of L2;
+// symmetric case: lower-triangle tiles only, as the reference computes only the lower triangle
+// of pairs, correlate.cpp:381-403):
 //   warp 0      TMA producer: per k-block of 32 floats loads four 128 x 32 tiles (A_hi, A_lo, B_hi,
 //               B_lo; 128-byte swizzle) into a 3-stage ring, signalling `full[stage]`.
-//   warp 1      allocates 128 TMEM columns; one lane issues 12 tcgen05.mma per k-block
-//               (4 k-steps of 8 x 3 split terms) and tcgen05.commit's the stage back to `empty`.
-//   warps 2..5  epilogue: tcgen05.ld the fp32 accumulator (lane = tile row), clamp to [-1, 1],
-//               NaN -> 0, optional |r|, diagonal = 1, store the tile and (symmetric case, off
-//               diagonal tiles) its mirror image, so only the lower triangle of tiles is computed,
-//               as the reference computes only the lower triangle of pairs (correlate.cpp:381-403).
+//   warp 1      allocates 256 TMEM columns (two 128-column accumulators); one lane issues 12
+//               tcgen05.mma per k-block (4 k-steps of 8 x 3 split terms), tcgen05.commit's the
+//               stage back to `empty`, and after every CHUNK k-blocks commits `acc_full[buffer]`
+//               and switches to the other accumulator.
+//   warps 2..5  drain + epilogue: the tensor core adds into its FP32 accumulator with truncation,
+//               which over the ~10^3 MMA steps of one dot product costs ~1e-5 (measured).  So each
+//               chunk's partial sum is moved TMEM -> registers (tcgen05.ld, lane = tile row) and
+//               summed there in round-to-nearest FP32, while the MMA warp already fills the other
+//               accumulator.  At the end of a tile: clamp to [-1, 1], NaN -> 0, optional |r|,
+//               diagonal = 1, store the tile and (symmetric case, off-diagonal tiles) its mirror.
 #include <cuda.h>
+
+#include <algorithm>
+#include <vector>
 
 #include "common.cuh"
 
@@ -29,7 +39,8 @@ constexpr int STAGES = 3;
 constexpr int TILE_BYTES = BM * BK * 4;          // 16 KiB
 constexpr int STAGE_BYTES = 4 * TILE_BYTES;      // A_hi, A_lo, B_hi, B_lo
 constexpr int UMMA_THREADS = 192;
-constexpr int TMEM_COLUMNS = 128;
+constexpr int TMEM_COLUMNS = 256;  // two accumulators of BN columns
+constexpr int CHUNK = 4;           // k-blocks accumulated in TMEM between two drains (K = 128)
 constexpr size_t UMMA_SMEM = (size_t)STAGES * STAGE_BYTES + 1024 /* alignment slack */ + 256 /* barriers */;
 
 // kind::tf32, D = F32, A/B = TF32, both K-major, M = 128, N = 128 (cute::UMMA::InstrDescriptor).
@@ -73,6 +84,9 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
         "l"(desc_a), "l"(desc_b), "r"(INSTR_DESC), "r"(accumulate)
         : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -81,14 +95,16 @@ struct UmmaParams {
     float* output;
     int64_t out_stride;
     int64_t rows_a, rows_b;
+    const int2* tiles;  // (tile_i, tile_j) in processing order
+    int tiles_count;
     int k_blocks;
-    int tiles_b;    // tiles along B (cross case)
     int symmetric;  // lower-triangle tiles, mirrored store, unit diagonal
     int absolute;   // store |r|
 };
 
 __device__ __forceinline__ float finish(float r, int absolute) {
-    r = fminf(fmaxf(r, -1.0f), 1.0f);  // also maps NaN to -1 then ... handled below
+    r = (r != r) ? 0.0f : r;           // computation.py:465 maps NaN to 0
+    r = fminf(fmaxf(r, -1.0f), 1.0f);  // correlate.cpp:199-200
     return absolute ? fabsf(r) : r;
 }
 
@@ -103,30 +119,22 @@ __global__ void __launch_bounds__(UMMA_THREADS, 1)
     const uint32_t bar_base = base + STAGES * STAGE_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
-    const uint32_t tmem_full_bar = bar_base + 8u * (2 * STAGES);
-    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 1);
+    auto acc_full_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
+    auto acc_empty_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    int tile_i, tile_j;
-    if (p.symmetric) {
-        const int t = blockIdx.x;
-        int i = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
-        while ((int64_t)i * (i + 1) / 2 > t) --i;
-        while ((int64_t)(i + 1) * (i + 2) / 2 <= t) ++i;
-        tile_i = i;
-        tile_j = t - (int)((int64_t)i * (i + 1) / 2);
-    } else {
-        tile_i = blockIdx.x / p.tiles_b;
-        tile_j = blockIdx.x % p.tiles_b;
-    }
+    const int chunks_per_tile = (p.k_blocks + CHUNK - 1) / CHUNK;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full_bar(s), 1);
             mbar_init(empty_bar(s), 1);
         }
-        mbar_init(tmem_full_bar, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(acc_full_bar(b), 1);
+            mbar_init(acc_empty_bar(b), 4);  // one arrival per drain warp
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a_hi) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a_lo) : "memory");
@@ -145,68 +153,132 @@ __global__ void __launch_bounds__(UMMA_THREADS, 1)
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < p.k_blocks; ++kb) {
-                const int s = kb % STAGES;
-                if (kb >= STAGES)
-                    mbar_wait(empty_bar(s), ((kb / STAGES) - 1) & 1);
-                const uint32_t stage = base + s * STAGE_BYTES;
-                mbar_expect_tx(full_bar(s), STAGE_BYTES);
-                tma_load_2d(stage + 0 * TILE_BYTES, &map_a_hi, full_bar(s), kb * BK, tile_i * BM);
-                tma_load_2d(stage + 1 * TILE_BYTES, &map_a_lo, full_bar(s), kb * BK, tile_i * BM);
-                tma_load_2d(stage + 2 * TILE_BYTES, &map_b_hi, full_bar(s), kb * BK, tile_j * BN);
-                tma_load_2d(stage + 3 * TILE_BYTES, &map_b_lo, full_bar(s), kb * BK, tile_j * BN);
+            uint32_t it = 0;  // k-blocks issued so far by this CTA
+            for (int t = blockIdx.x; t < p.tiles_count; t += gridDim.x) {
+                const int2 tile = p.tiles[t];
+                for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
+                    const uint32_t s = it % STAGES;
+                    if (it >= STAGES)
+                        mbar_wait(empty_bar(s), ((it / STAGES) - 1) & 1);
+                    const uint32_t stage = base + s * STAGE_BYTES;
+                    mbar_expect_tx(full_bar(s), STAGE_BYTES);
+                    tma_load_2d(stage + 0 * TILE_BYTES, &map_a_hi, full_bar(s), kb * BK, tile.x * BM);
+                    tma_load_2d(stage + 1 * TILE_BYTES, &map_a_lo, full_bar(s), kb * BK, tile.x * BM);
+                    tma_load_2d(stage + 2 * TILE_BYTES, &map_b_hi, full_bar(s), kb * BK, tile.y * BN);
+                    tma_load_2d(stage + 3 * TILE_BYTES, &map_b_lo, full_bar(s), kb * BK, tile.y * BN);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            for (int kb = 0; kb < p.k_blocks; ++kb) {
-                const int s = kb % STAGES;
-                mbar_wait(full_bar(s), (kb / STAGES) & 1);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t stage = base + s * STAGE_BYTES;
-                const uint64_t a_hi = umma_desc(stage + 0 * TILE_BYTES), a_lo = umma_desc(stage + 1 * TILE_BYTES);
-                const uint64_t b_hi = umma_desc(stage + 2 * TILE_BYTES), b_lo = umma_desc(stage + 3 * TILE_BYTES);
+            uint32_t it = 0, chunk_index = 0;
+            for (int t = blockIdx.x; t < p.tiles_count; t += gridDim.x) {
+                for (int kb0 = 0; kb0 < p.k_blocks; kb0 += CHUNK, ++chunk_index) {
+                    const uint32_t buffer = chunk_index & 1;
+                    if (chunk_index >= 2)
+                        mbar_wait(acc_empty_bar(buffer), ((chunk_index >> 1) - 1) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t tmem_d = tmem_base + buffer * BN;
+                    const int kb1 = min(kb0 + CHUNK, p.k_blocks);
+                    for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                        const uint32_t s = it % STAGES;
+                        mbar_wait(full_bar(s), (it / STAGES) & 1);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t stage = base + s * STAGE_BYTES;
+                        const uint64_t a_hi = umma_desc(stage + 0 * TILE_BYTES), a_lo = umma_desc(stage + 1 * TILE_BYTES);
+                        const uint64_t b_hi = umma_desc(stage + 2 * TILE_BYTES), b_lo = umma_desc(stage + 3 * TILE_BYTES);
 #pragma unroll
-                for (int k = 0; k < BK / 8; ++k) {
-                    const uint64_t advance = (uint64_t)((k * 8 * 4) >> 4);  // bytes >> 4 inside the swizzle row
-                    // small cross terms first, the dominant hi.hi term last
-                    umma_tf32(tmem_base, a_lo + advance, b_hi + advance, (kb | k) ? 1u : 0u);
-                    umma_tf32(tmem_base, a_hi + advance, b_lo + advance, 1u);
-                    umma_tf32(tmem_base, a_hi + advance, b_hi + advance, 1u);
+                        for (int k = 0; k < BK / 8; ++k) {
+                            const uint64_t advance = (uint64_t)((k * 8 * 4) >> 4);  // bytes >> 4 inside the swizzle row
+                            umma_tf32(tmem_d, a_lo + advance, b_hi + advance, (kb > kb0 || k > 0) ? 1u : 0u);
+                            umma_tf32(tmem_d, a_hi + advance, b_lo + advance, 1u);
+                            umma_tf32(tmem_d, a_hi + advance, b_hi + advance, 1u);
+                        }
+                        umma_commit(empty_bar(s));
+                    }
+                    umma_commit(acc_full_bar(buffer));
                 }
-                umma_commit(empty_bar(s));
             }
-            umma_commit(tmem_full_bar);
         }
     } else {
         const int quarter = warp & 3;  // TMEM lanes 32 * quarter .. + 31 are visible to this warp
-        mbar_wait(tmem_full_bar, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int row_in_tile = quarter * 32 + lane;
-        const int64_t global_row = (int64_t)tile_i * BM + row_in_tile;
-        const bool mirror = p.symmetric && tile_i != tile_j;
-        for (int chunk = 0; chunk < BN / 16; ++chunk) {
-            uint32_t v[16];
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 16);
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-                  "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                : "r"(taddr)
-                : "memory");
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        uint32_t chunk_index = 0;
+        for (int t = blockIdx.x; t < p.tiles_count; t += gridDim.x) {
+            const int2 tile = p.tiles[t];
+            float acc[BN];
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const int64_t global_col = (int64_t)tile_j * BN + chunk * 16 + c;
-                float r = __uint_as_float(v[c]);
-                r = (r != r) ? 0.0f : r;  // computation.py:465 maps NaN to 0
-                r = finish(r, p.absolute);
-                if (p.symmetric && global_row == global_col)
-                    r = 1.0f;
-                if (global_row < p.rows_a && global_col < p.rows_b) {
-                    p.output[global_row * p.out_stride + global_col] = r;
-                    if (mirror)
-                        p.output[global_col * p.out_stride + global_row] = r;
+            for (int c = 0; c < BN; ++c) acc[c] = 0.0f;
+            for (int chunk = 0; chunk < chunks_per_tile; ++chunk, ++chunk_index) {
+                const uint32_t buffer = chunk_index & 1;
+                mbar_wait(acc_full_bar(buffer), (chunk_index >> 1) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                for (int part = 0; part < BN / 16; ++part) {
+                    uint32_t v[16];
+                    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buffer * BN + (uint32_t)(part * 16);
+                    asm volatile(
+                        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                        : "r"(taddr)
+                        : "memory");
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) acc[part * 16 + c] += __uint_as_float(v[c]);
+                }
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(acc_empty_bar(buffer));
+            }
+            // tile epilogue
+            const int64_t global_row = (int64_t)tile.x * BM + row_in_tile;
+            const int64_t col0 = (int64_t)tile.y * BN;
+            const bool mirror = p.symmetric && tile.x != tile.y;
+            const bool row_ok = global_row < p.rows_a;
+#pragma unroll
+            for (int c = 0; c < BN; ++c) {
+                float r = finish(acc[c], p.absolute);
+                if (p.symmetric && global_row == col0 + c)
+                    r = 1.0f;  // correlate.cpp:374-376
+                acc[c] = r;
+            }
+            const bool diagonal_tile = p.symmetric && tile.x == tile.y;
+            if (row_ok) {
+                float* out_row = p.output + global_row * p.out_stride + col0;
+                if (diagonal_tile) {
+                    // (i, j) and (j, i) of a diagonal tile are accumulated in different term orders; keep
+                    // the lower triangle only and mirror it, so the result is exactly symmetric.
+                    float* mirror_at = p.output + col0 * p.out_stride + global_row;
+#pragma unroll
+                    for (int c = 0; c < BN; ++c) {
+                        if (c <= row_in_tile)
+                            out_row[c] = acc[c];
+                        if (c < row_in_tile)
+                            *mirror_at = acc[c];
+                        mirror_at += p.out_stride;
+                    }
+                } else if (col0 + BN <= p.rows_b && ((reinterpret_cast<uintptr_t>(out_row) & 15) == 0)) {
+#pragma unroll
+                    for (int c = 0; c < BN; c += 4)
+                        *reinterpret_cast<float4*>(out_row + c) = make_float4(acc[c], acc[c + 1], acc[c + 2], acc[c + 3]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < BN; ++c)
+                        if (col0 + c < p.rows_b)
+                            out_row[c] = acc[c];
+                }
+            }
+            if (mirror) {
+                // lanes hold consecutive rows: for a fixed column the warp writes 128 contiguous bytes
+                float* mirror_at = p.output + col0 * p.out_stride + global_row;
+                const int valid = row_ok ? (int)min((int64_t)BN, p.rows_b - col0) : 0;
+#pragma unroll
+                for (int c = 0; c < BN; ++c) {
+                    if (c < valid)
+                        *mirror_at = acc[c];
+                    mirror_at += p.out_stride;
                 }
             }
         }
@@ -259,6 +331,18 @@ int make_map(CUtensorMap* map, const float* data, int64_t rows, int64_t padded) 
 
 }  // namespace
 
+// Processing order of the output tiles: super-blocks of SUPER x SUPER tiles, so that the CTAs
+// running at the same time share row panels through L2 instead of streaming the whole operand.
+static void tile_order(int64_t tiles_a, int64_t tiles_b, int symmetric, std::vector<int2>& order) {
+    const int64_t SUPER = 8;
+    for (int64_t si = 0; si < tiles_a; si += SUPER)
+        for (int64_t sj = 0; sj < (symmetric ? si + 1 : tiles_b); sj += SUPER)
+            for (int64_t i = si; i < std::min(si + SUPER, tiles_a); ++i)
+                for (int64_t j = sj; j < std::min(sj + SUPER, tiles_b); ++j)
+                    if (!symmetric || j <= i)
+                        order.push_back(make_int2((int)i, (int)j));
+}
+
 // a_* / b_*: prepared rows [rows, padded] (padded a multiple of 32).  For the symmetric case pass the
 // same arrays for a and b.  output: [rows_a, out_stride >= rows_b].
 int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, const float* b_hi, const float* b_lo,
@@ -272,18 +356,25 @@ int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, 
     MCB_TRY(make_map(&map_a_lo, a_lo, rows_a, padded));
     MCB_TRY(make_map(&map_b_hi, b_hi, rows_b, padded));
     MCB_TRY(make_map(&map_b_lo, b_lo, rows_b, padded));
+    const int64_t tiles_a = ceil_div(rows_a, BM), tiles_b = ceil_div(rows_b, BN);
+    MCB_REQUIRE(tiles_a * tiles_b < (1ll << 30), "correlate: too many tiles");
+    std::vector<int2> order;
+    tile_order(tiles_a, tiles_b, symmetric, order);
+    Scratch tiles;
+    MCB_TRY(tiles.alloc(order.size() * sizeof(int2), stream));
+    // pageable source: the copy is staged before the call returns, so `order` may go out of scope
+    MCB_CUDA(cudaMemcpyAsync(tiles.ptr, order.data(), order.size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
     UmmaParams p{};
     p.output = output;
     p.out_stride = out_stride;
     p.rows_a = rows_a;
     p.rows_b = rows_b;
+    p.tiles = tiles.as<int2>();
+    p.tiles_count = (int)order.size();
     p.k_blocks = (int)(padded / BK);
     p.symmetric = symmetric;
     p.absolute = absolute;
-    const int64_t tiles_a = ceil_div(rows_a, BM), tiles_b = ceil_div(rows_b, BN);
-    p.tiles_b = (int)tiles_b;
-    const int64_t grid = symmetric ? tiles_a * (tiles_a + 1) / 2 : tiles_a * tiles_b;
-    MCB_REQUIRE(grid < (1ll << 31), "correlate: too many tiles");
+    const int grid = (int)std::min<int64_t>((int64_t)order.size(), sm_count());
     MCB_CUDA(cudaFuncSetAttribute(correlate_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UMMA_SMEM));
     correlate_umma_kernel<<<(unsigned)grid, UMMA_THREADS, UMMA_SMEM, stream>>>(map_a_hi, map_a_lo, map_b_hi, map_b_lo, p);
     MCB_CUDA(cudaGetLastError());

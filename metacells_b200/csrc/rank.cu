@@ -1,0 +1,400 @@
+// Per-row ordering kernels: rank_matrix (rank.cpp:38-87), rank_rows (rank.cpp:5-36) and
+// collect_top (top_per.cpp:5-92).
+//
+// Tie rule (documented in oracle/mc_oracle.c): the reference orders with unstable std::sort /
+// std::nth_element on value-only comparators, so the order of exactly equal values is an artefact
+// of libstdc++'s introsort.  Here equal values are ordered by their position (lower first).
+//
+//   rank_matrix   one CTA (1024 threads) per row; stable LSD radix sort of (key, position) in
+//                 shared memory: 4 passes of 8 bits; every warp owns a contiguous segment of the
+//                 current order and ranks its elements with __match_any_sync, so a pass needs a
+//                 32 x 256 table of per-warp digit counts and no atomics.  Keys stay put in shared
+//                 memory; only 16-bit positions ping-pong, so a 24k-wide row (the largest pile,
+//                 parameters.py:115) fits one SM.  The last pass writes the ranks straight to the
+//                 row in global memory: algorithmic traffic is one read and one write of the matrix.
+//   rank_rows     one CTA per row; 4-pass radix select of the rank-th smallest value.
+//   collect_top   one CTA per row; radix select of the degree-th largest value, then an ordered
+//                 compaction (indices come out ascending, as top_per.cpp:35 sorts them).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace mcb {
+
+namespace {
+
+constexpr int RM_THREADS = 1024;
+constexpr int RM_WARPS = RM_THREADS / 32;
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+    uint32_t mask;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(mask));
+    return mask;
+}
+
+// ascending order of `sort_key`  ==  requested order of the values
+__device__ __forceinline__ uint32_t sort_key(float value, bool ascending) {
+    uint32_t key = float_to_ordered(canonical_zero(value));
+    return ascending ? key : ~key;
+}
+
+struct RankMatrixParams {
+    float* matrix;
+    int64_t rows, columns, row_stride;
+    int ascending;
+    int segment;          // elements per warp, a multiple of 32
+    int smem_capacity;    // elements that fit the shared-memory layout (0: use the workspace)
+    uint8_t* workspace;   // per CTA: keys u32[capacity] + 2 x positions u16[capacity]
+    int64_t workspace_stride;
+};
+
+__global__ void __launch_bounds__(RM_THREADS, 1) rank_matrix_kernel(RankMatrixParams p) {
+    extern __shared__ __align__(16) uint8_t rm_smem[];
+    __shared__ int scan_scratch[34];
+
+    uint32_t* hist = reinterpret_cast<uint32_t*>(rm_smem);  // [RM_WARPS][256]
+    const int n = (int)p.columns;
+    const int capacity = p.segment * RM_WARPS;  // >= n
+    uint8_t* buffers = p.smem_capacity ? rm_smem + RM_WARPS * 256 * sizeof(uint32_t)
+                                       : p.workspace + (int64_t)blockIdx.x * p.workspace_stride;
+    uint32_t* keys = reinterpret_cast<uint32_t*>(buffers);
+    uint16_t* order_a = reinterpret_cast<uint16_t*>(buffers + (size_t)capacity * 4);
+    uint16_t* order_b = order_a + capacity;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lower_lanes = lanemask_lt();
+    uint32_t* my_hist = hist + warp * 256;
+    const int seg_begin = warp * p.segment, seg_end = min(seg_begin + p.segment, n);
+
+    for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
+        float* values = p.matrix + row * p.row_stride;
+        uint16_t* source = order_a;
+        uint16_t* target = order_b;
+        for (int pass = 0; pass < 4; ++pass) {
+            const int shift = 8 * pass;
+            for (int i = tid; i < RM_WARPS * 256; i += RM_THREADS) hist[i] = 0;
+            __syncthreads();
+            // (1) per-warp digit counts over this warp's segment of the current order
+            for (int base = seg_begin; base < seg_end; base += 32) {
+                const int i = base + lane;
+                uint32_t digit = 0xffffffffu;
+                if (i < seg_end) {
+                    uint32_t key;
+                    if (pass == 0) {
+                        key = sort_key(values[i], p.ascending != 0);
+                        keys[i] = key;
+                    } else {
+                        key = keys[source[i]];
+                    }
+                    digit = (key >> shift) & 255u;
+                }
+                const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+                if (i < seg_end && (peers & lower_lanes) == 0)
+                    my_hist[digit] += __popc(peers);
+                __syncwarp();
+            }
+            __syncthreads();
+            // (2) exclusive scan in (digit, warp) order
+            {
+                int total = 0;
+                if (tid < 256)
+                    for (int w = 0; w < RM_WARPS; ++w) total += (int)hist[w * 256 + tid];
+                int block_total;
+                const int start = block_exclusive_scan(tid < 256 ? total : 0, scan_scratch, &block_total);
+                if (tid < 256) {
+                    uint32_t running = (uint32_t)start;
+                    for (int w = 0; w < RM_WARPS; ++w) {
+                        const uint32_t count = hist[w * 256 + tid];
+                        hist[w * 256 + tid] = running;
+                        running += count;
+                    }
+                }
+            }
+            __syncthreads();
+            // (3) stable scatter
+            for (int base = seg_begin; base < seg_end; base += 32) {
+                const int i = base + lane;
+                uint32_t digit = 0xffffffffu;
+                uint32_t position = 0;
+                if (i < seg_end) {
+                    position = pass == 0 ? (uint32_t)i : (uint32_t)source[i];
+                    digit = (keys[position] >> shift) & 255u;
+                }
+                const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+                uint32_t slot = 0;
+                if (i < seg_end)
+                    slot = my_hist[digit] + __popc(peers & lower_lanes);
+                __syncwarp();
+                if (i < seg_end) {
+                    if ((peers & lower_lanes) == 0)
+                        my_hist[digit] += __popc(peers);
+                    if (pass == 3)
+                        values[position] = (float)(slot + 1);  // rank.cpp:73-75
+                    else
+                        target[slot] = (uint16_t)position;
+                }
+                __syncwarp();
+            }
+            __syncthreads();
+            uint16_t* swap = source;
+            source = target;
+            target = swap;
+        }
+    }
+}
+
+}  // namespace
+
+// In place: every row of matrix[rows, columns] (row stride in elements) becomes its 1-based ranks.
+int rank_matrix_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream) {
+    if (rows == 0 || columns == 0)
+        return MCB_OK;
+    MCB_REQUIRE(columns <= 65535, "rank_matrix: rows wider than 65535 elements are not supported (got %lld)", (long long)columns);
+    RankMatrixParams p{};
+    p.matrix = matrix;
+    p.rows = rows;
+    p.columns = columns;
+    p.row_stride = row_stride;
+    p.ascending = ascending;
+    p.segment = (int)(ceil_div(ceil_div(columns, RM_WARPS), 32) * 32);
+    const int64_t capacity = (int64_t)p.segment * RM_WARPS;
+    const size_t hist_bytes = RM_WARPS * 256 * sizeof(uint32_t);
+    const size_t buffer_bytes = (size_t)capacity * 8;
+    const size_t smem_limit = 227 * 1024 - 2048;  // static shared memory of the kernel comes on top
+    int64_t grid = rows;
+    size_t smem_bytes = hist_bytes;
+    Scratch workspace;
+    if (hist_bytes + buffer_bytes <= smem_limit) {
+        p.smem_capacity = (int)capacity;
+        smem_bytes += buffer_bytes;
+    } else {
+        grid = std::min<int64_t>(rows, sm_count());
+        p.workspace_stride = (int64_t)((buffer_bytes + 255) / 256 * 256);
+        MCB_TRY(workspace.alloc((size_t)grid * p.workspace_stride, stream));
+        p.workspace = workspace.as<uint8_t>();
+    }
+    MCB_CUDA(cudaFuncSetAttribute(rank_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    rank_matrix_kernel<<<(unsigned)grid, RM_THREADS, smem_bytes, stream>>>(p);
+    MCB_CUDA(cudaGetLastError());
+    return MCB_OK;
+}
+
+namespace {
+
+constexpr int SEL_THREADS = 512;
+
+// Shared state of one block-wide radix select.
+struct SelectState {
+    int hist[256];
+    uint32_t prefix;
+    int rank;
+};
+
+// The key of 0-based rank `rank` in ascending key order among key_at(0..n-1).  On return
+// *residual is the rank of that key inside its group of equal keys (so `rank - *residual` keys
+// are strictly smaller).  All threads of the block must call; all get the same result.
+template <typename KeyAt>
+__device__ uint32_t block_radix_select(KeyAt key_at, int n, int rank, SelectState* state, int* residual) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t lower_lanes = lanemask_lt();
+    if (tid == 0) {
+        state->prefix = 0;
+        state->rank = rank;
+    }
+    uint32_t known_mask = 0;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = tid; i < 256; i += blockDim.x) state->hist[i] = 0;
+        __syncthreads();
+        const uint32_t prefix = state->prefix;
+        const int rounds = (n + (int)blockDim.x - 1) / (int)blockDim.x;
+        for (int round = 0; round < rounds; ++round) {
+            const int i = round * (int)blockDim.x + tid;
+            uint32_t digit = 0xffffffffu;
+            if (i < n) {
+                const uint32_t key = key_at(i);
+                if ((key & known_mask) == prefix)
+                    digit = (key >> shift) & 255u;
+            }
+            const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+            if (digit != 0xffffffffu && (peers & lower_lanes) == 0)
+                atomicAdd(&state->hist[digit], __popc(peers));
+        }
+        __syncthreads();
+        if (tid < 32) {
+            // lane owns 8 consecutive bins
+            int counts[8], sum = 0;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                counts[b] = state->hist[lane * 8 + b];
+                sum += counts[b];
+            }
+            const int inclusive = warp_inclusive_scan(sum, lane);
+            int before = inclusive - sum;
+            const int wanted = state->rank;
+            __syncwarp();
+            if (wanted >= before && wanted < inclusive) {
+#pragma unroll
+                for (int b = 0; b < 8; ++b) {
+                    if (wanted >= before && wanted < before + counts[b]) {
+                        state->prefix = prefix | ((uint32_t)(lane * 8 + b) << shift);
+                        state->rank = wanted - before;
+                    }
+                    before += counts[b];
+                }
+            }
+        }
+        known_mask |= 255u << shift;
+        __syncthreads();
+    }
+    *residual = state->rank;
+    const uint32_t result = state->prefix;
+    __syncthreads();
+    return result;
+}
+
+// rank.cpp:5-36: output[row] = the value of 0-based rank `rank` in ascending order.
+__global__ void __launch_bounds__(SEL_THREADS) rank_rows_kernel(const float* __restrict__ matrix, int64_t rows, int64_t columns,
+                                                               int64_t row_stride, float* __restrict__ output, int rank,
+                                                               int cache_capacity) {
+    extern __shared__ __align__(16) uint8_t sel_smem[];
+    __shared__ SelectState state;
+    uint32_t* cache = reinterpret_cast<uint32_t*>(sel_smem);
+    const int n = (int)columns;
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const float* values = matrix + row * row_stride;
+        int residual;
+        uint32_t key;
+        if (n <= cache_capacity) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) cache[i] = sort_key(values[i], true);
+            __syncthreads();
+            key = block_radix_select([&](int i) { return cache[i]; }, n, rank, &state, &residual);
+        } else {
+            key = block_radix_select([&](int i) { return sort_key(values[i], true); }, n, rank, &state, &residual);
+        }
+        if (threadIdx.x == 0)
+            output[row] = ordered_to_float(key);
+    }
+}
+
+struct CollectTopParams {
+    const float* similarity;
+    int64_t rows, columns, row_stride;
+    int degree;
+    int32_t* out_indices;
+    float* out_data;
+    int ranks;
+    int cache_capacity;
+};
+
+// top_per.cpp:5-64.  Shared memory: keys cache u32[cache_capacity] + kept keys u32[degree].
+__global__ void __launch_bounds__(SEL_THREADS) collect_top_kernel(CollectTopParams p) {
+    extern __shared__ __align__(16) uint8_t sel_smem[];
+    __shared__ SelectState state;
+    __shared__ int scan_scratch[34];
+    __shared__ int carry[2];
+    uint32_t* cache = reinterpret_cast<uint32_t*>(sel_smem);
+    uint32_t* kept_keys = cache + p.cache_capacity;
+    const int n = (int)p.columns, tid = threadIdx.x;
+    for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
+        const float* values = p.similarity + row * p.row_stride;
+        int32_t* row_indices = p.out_indices + row * p.degree;
+        float* row_data = p.out_data + row * p.degree;
+        const bool cached = n <= p.cache_capacity;
+        if (cached) {
+            for (int i = tid; i < n; i += blockDim.x) cache[i] = sort_key(values[i], false);
+            __syncthreads();
+        }
+        auto key_at = [&](int i) { return cached ? cache[i] : sort_key(values[i], false); };
+        int residual;
+        const uint32_t threshold = block_radix_select(key_at, n, p.degree - 1, &state, &residual);
+        const int ties_wanted = residual + 1;  // equal-to-threshold elements to keep, lowest positions first
+        if (tid == 0) {
+            carry[0] = 0;  // kept so far
+            carry[1] = 0;  // ties seen so far
+        }
+        __syncthreads();
+        for (int base = 0; base < n; base += blockDim.x) {
+            const int i = base + tid;
+            const uint32_t key = i < n ? key_at(i) : 0xffffffffu;
+            const int is_tie = (i < n && key == threshold) ? 1 : 0;
+            int ties_total, kept_total;
+            const int ties_before = carry[1] + block_exclusive_scan(is_tie, scan_scratch, &ties_total);
+            const int keep = (i < n && (key < threshold || (is_tie && ties_before < ties_wanted))) ? 1 : 0;
+            const int slot = carry[0] + block_exclusive_scan(keep, scan_scratch, &kept_total);
+            if (keep) {
+                row_indices[slot] = i;
+                if (p.ranks)
+                    kept_keys[slot] = key;
+                else
+                    row_data[slot] = values[i];
+            }
+            __syncthreads();
+            if (tid == 0) {
+                carry[0] += kept_total;
+                carry[1] += ties_total;
+            }
+            __syncthreads();
+        }
+        if (p.ranks) {
+            // top_per.cpp:44-63: 1-based rank in ASCENDING value order among the kept values (keys are
+            // descending, so a larger key is a smaller value); equal values by position.
+            for (int e = tid; e < p.degree; e += blockDim.x) {
+                const uint32_t mine = kept_keys[e];
+                int before = 0;
+                for (int f = 0; f < p.degree; ++f) {
+                    const uint32_t other = kept_keys[f];
+                    before += (other > mine || (other == mine && f < e)) ? 1 : 0;
+                }
+                row_data[e] = (float)(before + 1);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+int rank_rows_launch(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank,
+                     cudaStream_t stream) {
+    if (rows == 0)
+        return MCB_OK;
+    MCB_REQUIRE(rank >= 0 && rank < columns, "rank_rows: rank %lld is out of range for %lld columns", (long long)rank, (long long)columns);
+    MCB_REQUIRE(columns < (1ll << 31), "rank_rows: too many columns");
+    int cache_capacity = columns <= 16384 ? (int)columns : (columns <= 48 * 1024 ? (int)columns : 0);
+    const size_t smem_bytes = (size_t)cache_capacity * 4;
+    MCB_CUDA(cudaFuncSetAttribute(rank_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
+    rank_rows_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(matrix, rows, columns, row_stride, output, (int)rank,
+                                                                        cache_capacity);
+    MCB_CUDA(cudaGetLastError());
+    return MCB_OK;
+}
+
+int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                       int32_t* out_indices, float* out_data, int ranks, cudaStream_t stream) {
+    if (rows == 0)
+        return MCB_OK;
+    MCB_REQUIRE(degree > 0 && degree < columns, "collect_top: degree %lld must be in 1..columns-1 (%lld columns)",
+                (long long)degree, (long long)columns);  // top_per.cpp:81-82
+    MCB_REQUIRE(columns < (1ll << 31), "collect_top: too many columns");
+    CollectTopParams p{};
+    p.similarity = similarity;
+    p.rows = rows;
+    p.columns = columns;
+    p.row_stride = row_stride;
+    p.degree = (int)degree;
+    p.out_indices = out_indices;
+    p.out_data = out_data;
+    p.ranks = ranks;
+    const size_t kept_bytes = ranks ? (size_t)degree * 4 : 0;
+    MCB_REQUIRE(kept_bytes <= 96 * 1024, "collect_top: degree %lld is too large for the ranks mode", (long long)degree);
+    p.cache_capacity = ((size_t)columns * 4 + kept_bytes <= 200 * 1024) ? (int)columns : 0;
+    const size_t smem_bytes = (size_t)p.cache_capacity * 4 + kept_bytes;
+    MCB_CUDA(cudaFuncSetAttribute(collect_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
+    collect_top_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(p);
+    MCB_CUDA(cudaGetLastError());
+    return MCB_OK;
+}
+
+}  // namespace mcb
