@@ -1,0 +1,189 @@
+// C-ABI entry points for the ordering / compressed-matrix functions and the fused k-NN graph builder.
+#include <cmath>
+#include <memory>
+#include <utility>
+
+#include "common.cuh"
+#include "../../include/mcb200.h"
+
+namespace mcb {
+int rank_matrix_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream);
+int rank_rows_launch(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank,
+                     cudaStream_t stream);
+int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                       int32_t* out_indices, float* out_data, int ranks, cudaStream_t stream);
+int collect_pruned_launch(int64_t degree, const float* data, const int32_t* indices, const int32_t* indptr, int64_t bands,
+                          float* out_data, int32_t* out_indices, int32_t* out_indptr, cudaStream_t stream);
+int collect_compressed_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t bands, float* out_data,
+                              int32_t* out_indices, int32_t* cursor, cudaStream_t stream);
+int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t* indptr, int64_t bands, int64_t widest_band,
+                                   cudaStream_t stream);
+int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream);
+
+struct BalancedRanks {
+    Scratch data, indices, indptr, best_index, best_value;
+    int64_t nnz = 0;
+};
+struct PrunedRanks {
+    Scratch data, indices, indptr;
+    int64_t nnz = 0;
+    int32_t min_degree = 0;
+};
+int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRanks* out, cudaStream_t stream);
+int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incoming_degree, int64_t outgoing_degree,
+                       PrunedRanks* out, cudaStream_t stream);
+int weigh_edges_launch(const float* data, const int32_t* indptr, int64_t n, float* weights, int32_t* min_degree_host,
+                       cudaStream_t stream);
+}  // namespace mcb
+
+using namespace mcb;
+
+// A device-resident CSR graph (see mcb200.h).
+struct mcb_graph {
+    int64_t n = 0, nnz = 0, k = 0;
+    Scratch weights, ranks, indices, indptr;
+    cudaStream_t stream = nullptr;
+};
+
+namespace {
+
+template <typename T>
+int to_device(Scratch& device, const T* host, size_t count, cudaStream_t stream) {
+    MCB_TRY(device.alloc(count * sizeof(T), stream));
+    if (count)
+        MCB_CUDA(cudaMemcpyAsync(device.ptr, host, count * sizeof(T), cudaMemcpyHostToDevice, stream));
+    return MCB_OK;
+}
+template <typename T>
+int to_host(T* host, const Scratch& device, size_t count, cudaStream_t stream) {
+    if (count)
+        MCB_CUDA(cudaMemcpyAsync(host, device.ptr, count * sizeof(T), cudaMemcpyDeviceToHost, stream));
+    return MCB_OK;
+}
+
+// tools/knn_graph.py:251-275: rank, balance, prune; grow k until every row keeps min_outgoing_degree edges.
+int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor, double incoming_degree_factor,
+                     double outgoing_degree_factor, int64_t min_outgoing_degree, cudaStream_t stream, mcb_graph* graph) {
+    MCB_REQUIRE(n >= 2, "knn_graph: needs at least 2 elements (got %lld)", (long long)n);
+    MCB_REQUIRE(k >= 1 && balanced_ranks_factor > 0 && incoming_degree_factor > 0 && outgoing_degree_factor > 0 &&
+                    min_outgoing_degree >= 1,
+                "knn_graph: bad parameters");  // knn_graph.py:216-220
+    Scratch work;
+    MCB_TRY(work.alloc((size_t)n * n * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpyAsync(work.ptr, similarity, (size_t)n * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    // The ranks do not depend on k: computed once (the reference recomputes them every round, knn_graph.py:252).
+    MCB_TRY(rank_outgoing_launch(work.as<float>(), n, stream));
+    std::unique_ptr<PrunedRanks> pruned_holder;
+    for (;;) {
+        const double max_rank = (double)k * balanced_ranks_factor;                   // knn_graph.py:313
+        const float shift = (float)(max_rank + 1.0 - 2097152.0);                     // knn_graph.py:325
+        int64_t incoming = (int64_t)std::nearbyint((double)k * incoming_degree_factor);  // Python round(): half to even
+        int64_t outgoing = (int64_t)std::nearbyint((double)k * outgoing_degree_factor);
+        incoming = incoming < n - 1 ? incoming : n - 1;
+        outgoing = outgoing < n - 1 ? outgoing : n - 1;
+        BalancedRanks balanced;
+        MCB_TRY(balance_ranks_launch(work.as<float>(), n, shift, &balanced, stream));
+        pruned_holder.reset(new PrunedRanks());
+        PrunedRanks& pruned = *pruned_holder;
+        MCB_TRY(prune_ranks_launch(balanced, n, incoming, outgoing, &pruned, stream));
+        int32_t min_degree = 0;
+        MCB_TRY(weigh_edges_launch(pruned.data.as<float>(), pruned.indptr.as<int32_t>(), n, nullptr, &min_degree, stream));
+        if (min_degree >= min_outgoing_degree)
+            break;
+        k += (k / 10) > 1 ? (k / 10) : 1;  // knn_graph.py:268
+    }
+    PrunedRanks& pruned = *pruned_holder;
+    graph->n = n;
+    graph->nnz = pruned.nnz;
+    graph->k = k;
+    graph->stream = stream;
+    MCB_TRY(graph->weights.alloc((size_t)pruned.nnz * sizeof(float), stream));
+    MCB_TRY(weigh_edges_launch(pruned.data.as<float>(), pruned.indptr.as<int32_t>(), n, graph->weights.as<float>(), nullptr, stream));
+    std::swap(graph->ranks.ptr, pruned.data.ptr);
+    std::swap(graph->ranks.stream, pruned.data.stream);
+    std::swap(graph->indices.ptr, pruned.indices.ptr);
+    std::swap(graph->indices.stream, pruned.indices.stream);
+    std::swap(graph->indptr.ptr, pruned.indptr.ptr);
+    std::swap(graph->indptr.stream, pruned.indptr.stream);
+    return MCB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+/* ---- rank.cpp / top_per.cpp ------------------------------------------------------------------ */
+
+int mcb_dev_rank_matrix_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, void* stream) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "rank_matrix: bad shape");
+    return rank_matrix_launch(matrix, rows, columns, row_stride, ascending, (cudaStream_t)stream);
+}
+
+int mcb_host_rank_matrix_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "rank_matrix: bad shape");
+    if (rows == 0 || columns == 0)
+        return MCB_OK;
+    cudaStream_t stream = nullptr;
+    Scratch device;
+    MCB_TRY(device.alloc((size_t)rows * columns * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpy2DAsync(device.ptr, columns * sizeof(float), matrix, row_stride * sizeof(float), columns * sizeof(float), rows,
+                               cudaMemcpyHostToDevice, stream));
+    MCB_TRY(rank_matrix_launch(device.as<float>(), rows, columns, columns, ascending, stream));
+    MCB_CUDA(cudaMemcpy2DAsync(matrix, row_stride * sizeof(float), device.ptr, columns * sizeof(float), columns * sizeof(float), rows,
+                               cudaMemcpyDeviceToHost, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_host_rank_rows_f32(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "rank_rows: bad shape");
+    MCB_REQUIRE(rank >= 0 && rank < columns, "rank_rows: rank %lld out of range", (long long)rank);  // rank.cpp:33
+    if (rows == 0)
+        return MCB_OK;
+    cudaStream_t stream = nullptr;
+    Scratch device, result;
+    MCB_TRY(device.alloc((size_t)rows * columns * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpy2DAsync(device.ptr, columns * sizeof(float), matrix, row_stride * sizeof(float), columns * sizeof(float), rows,
+                               cudaMemcpyHostToDevice, stream));
+    MCB_TRY(result.alloc((size_t)rows * sizeof(float), stream));
+    MCB_TRY(rank_rows_launch(device.as<float>(), rows, columns, columns, result.as<float>(), rank, stream));
+    MCB_TRY(to_host(output, result, (size_t)rows, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_dev_rank_rows_f32(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank,
+                          void* stream) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "rank_rows: bad shape");
+    return rank_rows_launch(matrix, rows, columns, row_stride, output, rank, (cudaStream_t)stream);
+}
+
+int mcb_dev_collect_top_f32(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                            int32_t* out_indices, float* out_data, int ranks, void* stream) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "collect_top: bad shape");
+    return collect_top_launch(degree, similarity, rows, columns, row_stride, out_indices, out_data, ranks, (cudaStream_t)stream);
+}
+
+int mcb_host_collect_top_f32(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                             int32_t* out_indices, float* out_data, int ranks) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "collect_top: bad shape");
+    MCB_REQUIRE(degree > 0 && degree < columns, "collect_top: degree %lld must be in 1..columns-1", (long long)degree);
+    if (rows == 0)
+        return MCB_OK;
+    cudaStream_t stream = nullptr;
+    Scratch device, indices, data;
+    MCB_TRY(device.alloc((size_t)rows * columns * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpy2DAsync(device.ptr, columns * sizeof(float), similarity, row_stride * sizeof(float), columns * sizeof(float),
+                               rows, cudaMemcpyHostToDevice, stream));
+    MCB_TRY(indices.alloc((size_t)rows * degree * sizeof(int32_t), stream));
+    MCB_TRY(data.alloc((size_t)rows * degree * sizeof(float), stream));
+    MCB_TRY(collect_top_launch(degree, device.as<float>(), rows, columns, columns, indices.as<int32_t>(), data.as<float>(), ranks, stream));
+    MCB_TRY(to_host(out_indices, indices, (size_t)rows * degree, stream));
+    MCB_TRY(to_host(out_data, data, (size_t)rows * degree, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+/* @@API_KNN_PART2@@ */
+
+}  // extern "C"
