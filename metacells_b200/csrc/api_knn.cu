@@ -1,4 +1,5 @@
 // C-ABI entry points for the ordering / compressed-matrix functions and the fused k-NN graph builder.
+#include <algorithm>
 #include <cmath>
 #include <memory>
 #include <utility>
@@ -184,6 +185,131 @@ int mcb_host_collect_top_f32(int64_t degree, const float* similarity, int64_t ro
     return MCB_OK;
 }
 
-/* @@API_KNN_PART2@@ */
+/* ---- prune_per.cpp / relayout.cpp -------------------------------------------------------------- */
+
+int mcb_dev_collect_pruned_f32_i32_i32(int64_t degree, const float* data, const int32_t* indices, const int32_t* indptr,
+                                       int64_t bands, float* out_data, int32_t* out_indices, int32_t* out_indptr, void* stream) {
+    MCB_REQUIRE(bands >= 0, "collect_pruned: negative bands count");
+    return collect_pruned_launch(degree, data, indices, indptr, bands, out_data, out_indices, out_indptr, (cudaStream_t)stream);
+}
+
+int mcb_host_collect_pruned_f32_i32_i32(int64_t degree, const float* data, const int32_t* indices, const int32_t* indptr,
+                                        int64_t bands, float* out_data, int32_t* out_indices, int32_t* out_indptr) {
+    MCB_REQUIRE(bands >= 0 && degree >= 0, "collect_pruned: bad arguments");
+    cudaStream_t stream = nullptr;
+    const int64_t nnz = bands > 0 ? indptr[bands] : 0;
+    Scratch d_data, d_indices, d_indptr, o_data, o_indices, o_indptr;
+    MCB_TRY(to_device(d_data, data, (size_t)nnz, stream));
+    MCB_TRY(to_device(d_indices, indices, (size_t)nnz, stream));
+    MCB_TRY(to_device(d_indptr, indptr, (size_t)bands + 1, stream));
+    MCB_TRY(o_data.alloc((size_t)nnz * sizeof(float), stream));
+    MCB_TRY(o_indices.alloc((size_t)nnz * sizeof(int32_t), stream));
+    MCB_TRY(o_indptr.alloc((size_t)(bands + 1) * sizeof(int32_t), stream));
+    MCB_TRY(collect_pruned_launch(degree, d_data.as<float>(), d_indices.as<int32_t>(), d_indptr.as<int32_t>(), bands,
+                                  o_data.as<float>(), o_indices.as<int32_t>(), o_indptr.as<int32_t>(), stream));
+    MCB_TRY(to_host(out_indptr, o_indptr, (size_t)bands + 1, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    const int64_t out_nnz = out_indptr[bands];
+    MCB_TRY(to_host(out_data, o_data, (size_t)out_nnz, stream));
+    MCB_TRY(to_host(out_indices, o_indices, (size_t)out_nnz, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_host_collect_compressed_f32_i32_i32(const float* data, const int32_t* indices, const int32_t* indptr, int64_t bands,
+                                            float* out_data, int32_t* out_indices, int32_t* out_indptr_shifted,
+                                            int64_t out_bands) {
+    MCB_REQUIRE(bands >= 0 && out_bands >= 0, "collect_compressed: bad arguments");
+    if (bands == 0)
+        return MCB_OK;
+    cudaStream_t stream = nullptr;
+    const int64_t nnz = indptr[bands];
+    for (int64_t e = 0; e < nnz; ++e)
+        MCB_REQUIRE(indices[e] >= 0 && indices[e] < out_bands, "collect_compressed: index %d out of range at %lld", indices[e], (long long)e);
+    Scratch d_data, d_indices, d_indptr, o_data, o_indices, cursor;
+    MCB_TRY(to_device(d_data, data, (size_t)nnz, stream));
+    MCB_TRY(to_device(d_indices, indices, (size_t)nnz, stream));
+    MCB_TRY(to_device(d_indptr, indptr, (size_t)bands + 1, stream));
+    MCB_TRY(to_device(cursor, out_indptr_shifted, (size_t)out_bands, stream));
+    MCB_TRY(o_data.alloc((size_t)nnz * sizeof(float), stream));
+    MCB_TRY(o_indices.alloc((size_t)nnz * sizeof(int32_t), stream));
+    MCB_TRY(collect_compressed_launch(d_data.as<float>(), d_indices.as<int32_t>(), d_indptr.as<int32_t>(), bands, o_data.as<float>(),
+                                      o_indices.as<int32_t>(), cursor.as<int32_t>(), stream));
+    MCB_TRY(to_host(out_data, o_data, (size_t)nnz, stream));
+    MCB_TRY(to_host(out_indices, o_indices, (size_t)nnz, stream));
+    MCB_TRY(to_host(out_indptr_shifted, cursor, (size_t)out_bands, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_host_sort_compressed_indices_f32_i32_i32(float* data, int32_t* indices, const int32_t* indptr, int64_t bands) {
+    MCB_REQUIRE(bands >= 0, "sort_compressed_indices: negative bands count");
+    if (bands == 0)
+        return MCB_OK;
+    cudaStream_t stream = nullptr;
+    const int64_t nnz = indptr[bands];
+    int64_t widest = 0;
+    for (int64_t b = 0; b < bands; ++b) widest = std::max<int64_t>(widest, indptr[b + 1] - indptr[b]);
+    Scratch d_data, d_indices, d_indptr;
+    MCB_TRY(to_device(d_data, data, (size_t)nnz, stream));
+    MCB_TRY(to_device(d_indices, indices, (size_t)nnz, stream));
+    MCB_TRY(to_device(d_indptr, indptr, (size_t)bands + 1, stream));
+    MCB_TRY(sort_compressed_indices_launch(d_data.as<float>(), d_indices.as<int32_t>(), d_indptr.as<int32_t>(), bands, widest, stream));
+    MCB_TRY(to_host(data, d_data, (size_t)nnz, stream));
+    MCB_TRY(to_host(indices, d_indices, (size_t)nnz, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+/* ---- tools/knn_graph.py:203-407 -------------------------------------------------------------------- */
+
+int mcb_dev_knn_graph_f32(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor,
+                          double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                          void* stream, mcb_graph** out) {
+    MCB_REQUIRE(out != nullptr, "knn_graph: null result pointer");
+    std::unique_ptr<mcb_graph> graph(new mcb_graph());
+    MCB_TRY(knn_graph_device(similarity, n, k, balanced_ranks_factor, incoming_degree_factor, outgoing_degree_factor,
+                             min_outgoing_degree, (cudaStream_t)stream, graph.get()));
+    *out = graph.release();
+    return MCB_OK;
+}
+
+int mcb_host_knn_graph_f32(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor,
+                           double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                           mcb_graph** out) {
+    MCB_REQUIRE(out != nullptr && n >= 2, "knn_graph: bad arguments");
+    cudaStream_t stream = nullptr;
+    Scratch device;
+    MCB_TRY(to_device(device, similarity, (size_t)n * n, stream));
+    return mcb_dev_knn_graph_f32(device.as<float>(), n, k, balanced_ranks_factor, incoming_degree_factor, outgoing_degree_factor,
+                                 min_outgoing_degree, stream, out);
+}
+
+int64_t mcb_graph_size(const mcb_graph* graph) { return graph ? graph->n : 0; }
+int64_t mcb_graph_nnz(const mcb_graph* graph) { return graph ? graph->nnz : 0; }
+int64_t mcb_graph_k(const mcb_graph* graph) { return graph ? graph->k : 0; }
+
+int mcb_graph_device_arrays(const mcb_graph* graph, const float** weights, const float** ranks, const int32_t** indices,
+                            const int32_t** indptr) {
+    MCB_REQUIRE(graph != nullptr, "graph: null handle");
+    if (weights) *weights = graph->weights.as<float>();
+    if (ranks) *ranks = graph->ranks.as<float>();
+    if (indices) *indices = graph->indices.as<int32_t>();
+    if (indptr) *indptr = graph->indptr.as<int32_t>();
+    return MCB_OK;
+}
+
+int mcb_graph_read(const mcb_graph* graph, float* weights, float* ranks, int32_t* indices, int32_t* indptr) {
+    MCB_REQUIRE(graph != nullptr, "graph: null handle");
+    cudaStream_t stream = graph->stream;
+    if (weights) MCB_TRY(to_host(weights, graph->weights, (size_t)graph->nnz, stream));
+    if (ranks) MCB_TRY(to_host(ranks, graph->ranks, (size_t)graph->nnz, stream));
+    if (indices) MCB_TRY(to_host(indices, graph->indices, (size_t)graph->nnz, stream));
+    if (indptr) MCB_TRY(to_host(indptr, graph->indptr, (size_t)graph->n + 1, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+void mcb_graph_free(mcb_graph* graph) { delete graph; }
 
 }  // extern "C"
