@@ -89,6 +89,73 @@ int mcb_host_pairs_correlate_dense_f64(const double* first, int64_t first_stride
 int mcb_dev_pairs_correlate_dense_f32(const float* first, const float* second, int64_t rows, int64_t columns, float* output,
                                       void* stream);
 
+/* ---- rank.cpp ----------------------------------------------------------------------------------- */
+
+/* rank_matrix<float32>  (rank.cpp:38-87): in place, every row becomes its 1-based ranks
+ * (ascending != 0: smallest value gets rank 1).  Equal values rank by position (lower first). */
+int mcb_host_rank_matrix_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending);
+int mcb_dev_rank_matrix_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, void* stream);
+
+/* rank_rows<float32>  (rank.cpp:5-36): output[row] = value of 0-based `rank` in ascending order. */
+int mcb_host_rank_rows_f32(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank);
+int mcb_dev_rank_rows_f32(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank,
+                          void* stream);
+
+/* ---- top_per.cpp -------------------------------------------------------------------------------- */
+
+/* collect_top<float32>  (top_per.cpp:5-92): per row the `degree` largest values; out_indices
+ * (ascending per row) and out_data have rows * degree entries; ranks != 0 stores the 1-based
+ * ascending rank among the kept values instead of the values. */
+int mcb_host_collect_top_f32(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                             int32_t* out_indices, float* out_data, int ranks);
+int mcb_dev_collect_top_f32(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                            int32_t* out_indices, float* out_data, int ranks, void* stream);
+
+/* ---- prune_per.cpp ------------------------------------------------------------------------------ */
+
+/* collect_pruned<float32,int32,int32>  (prune_per.cpp:56-105): out_indptr has bands + 1 entries;
+ * out_data / out_indices need room for sum(min(band size, degree)) entries. */
+int mcb_host_collect_pruned_f32_i32_i32(int64_t degree, const float* data, const int32_t* indices, const int32_t* indptr,
+                                        int64_t bands, float* out_data, int32_t* out_indices, int32_t* out_indptr);
+int mcb_dev_collect_pruned_f32_i32_i32(int64_t degree, const float* data, const int32_t* indices, const int32_t* indptr,
+                                       int64_t bands, float* out_data, int32_t* out_indices, int32_t* out_indptr, void* stream);
+
+/* ---- relayout.cpp ------------------------------------------------------------------------------- */
+
+/* collect_compressed<float32,int32,int32>  (relayout.cpp:73-108).  out_indptr_shifted has out_bands
+ * entries: on entry the start of every output band, on return its end (the caller passes
+ * output_indptr[1:], computation.py:268-292).  The order inside an output band is unspecified,
+ * as in the reference; follow with sort_compressed_indices. */
+int mcb_host_collect_compressed_f32_i32_i32(const float* data, const int32_t* indices, const int32_t* indptr, int64_t bands,
+                                            float* out_data, int32_t* out_indices, int32_t* out_indptr_shifted,
+                                            int64_t out_bands);
+/* sort_compressed_indices<float32,int32,int32>  (relayout.cpp:152-167): in place. */
+int mcb_host_sort_compressed_indices_f32_i32_i32(float* data, int32_t* indices, const int32_t* indptr, int64_t bands);
+
+/* ---- tools/knn_graph.py:203-407 (numpy/scipy glue of the reference, fused on the device) -------- */
+
+/* A device-resident CSR graph: `weights` (obs_outgoing_weights) and `ranks` (obs_pruned_ranks)
+ * share indices / indptr. */
+typedef struct mcb_graph mcb_graph;
+
+/* compute_obs_obs_knn_graph on a float32 similarity matrix [n, n]: rank (knn_graph.py:285-297),
+ * balance (:300-340), prune (:343-392), weigh (:395-407), growing k until every row keeps
+ * min_outgoing_degree edges (:251-268).  Free the result with mcb_graph_free. */
+int mcb_host_knn_graph_f32(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor,
+                           double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                           mcb_graph** out);
+int mcb_dev_knn_graph_f32(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor,
+                          double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                          void* stream, mcb_graph** out);
+int64_t mcb_graph_size(const mcb_graph* graph);
+int64_t mcb_graph_nnz(const mcb_graph* graph);
+int64_t mcb_graph_k(const mcb_graph* graph); /* the k finally used */
+/* Copy to host buffers (any may be NULL): weights/ranks/indices have nnz entries, indptr size + 1. */
+int mcb_graph_read(const mcb_graph* graph, float* weights, float* ranks, int32_t* indices, int32_t* indptr);
+int mcb_graph_device_arrays(const mcb_graph* graph, const float** weights, const float** ranks, const int32_t** indices,
+                            const int32_t** indptr);
+void mcb_graph_free(mcb_graph* graph);
+
 /* @@APPEND@@ */
 
 #ifdef __cplusplus

@@ -119,4 +119,71 @@ def pairs_correlate_dense_float64_t(first, second, output):
     _pairs_correlate_dense(first, second, output, "f64", "float64")
 
 
+# ---- rank.cpp / top_per.cpp -------------------------------------------------------------------
+
+
+def rank_matrix_float32_t(matrix, ascending):
+    """rank.cpp:79-87: in place."""
+    call("mcb_host_rank_matrix_f32", host_ptr(matrix, "float32", "matrix", True), ("i64", matrix.shape[0]),
+         ("i64", matrix.shape[1]), ("i64", row_stride(matrix)), ("int", int(bool(ascending))))
+
+
+def rank_rows_float32_t(input_matrix, output, rank):
+    """rank.cpp:24-36."""
+    if len(output) != input_matrix.shape[0]:
+        raise ValueError("output must have one entry per row")
+    call("mcb_host_rank_rows_f32", host_ptr(input_matrix, "float32", "input"), ("i64", input_matrix.shape[0]),
+         ("i64", input_matrix.shape[1]), ("i64", row_stride(input_matrix)), host_ptr(output, "float32", "output", True),
+         ("i64", int(rank)))
+
+
+def collect_top_float32_t(degree, similarity, output_indices, output_data, ranks):
+    """top_per.cpp:67-92."""
+    rows = similarity.shape[0]
+    if len(output_indices) != rows * degree or len(output_data) != rows * degree:
+        raise ValueError("outputs must have rows * degree entries")
+    call("mcb_host_collect_top_f32", ("i64", int(degree)), host_ptr(similarity, "float32", "similarity"), ("i64", rows),
+         ("i64", similarity.shape[1]), ("i64", row_stride(similarity)), host_ptr(output_indices, "int32", "output_indices", True),
+         host_ptr(output_data, "float32", "output_data", True), ("int", int(bool(ranks))))
+
+
+# ---- prune_per.cpp / relayout.cpp -------------------------------------------------------------
+
+
+def collect_pruned_float32_t_int32_t_int32_t(pruned_degree, input_data, input_indices, input_indptr, output_data,
+                                             output_indices, output_indptr):
+    """prune_per.cpp:56-105."""
+    bands = len(input_indptr) - 1
+    if len(output_indptr) != bands + 1:
+        raise ValueError("output indptr must have bands + 1 entries")
+    if len(input_data) != len(input_indices) or len(input_data) != int(input_indptr[-1]):
+        raise ValueError("data / indices / indptr sizes disagree")
+    needed = int(np.minimum(np.diff(input_indptr), pruned_degree).sum())
+    if len(output_data) < needed or len(output_indices) < needed:
+        raise ValueError("output arrays are too small")
+    call("mcb_host_collect_pruned_f32_i32_i32", ("i64", int(pruned_degree)), host_ptr(input_data, "float32", "input_data"),
+         host_ptr(input_indices, "int32", "input_indices"), host_ptr(input_indptr, "int32", "input_indptr"), ("i64", bands),
+         host_ptr(output_data, "float32", "output_data", True), host_ptr(output_indices, "int32", "output_indices", True),
+         host_ptr(output_indptr, "int32", "output_indptr", True))
+
+
+def collect_compressed_float32_t_int32_t_int32_t(input_data, input_indices, input_indptr, output_data, output_indices,
+                                                 output_indptr):
+    """relayout.cpp:73-108; `output_indptr` is the caller's ``indptr[1:]`` holding the band starts."""
+    if len(output_data) != len(input_data) or len(output_indices) != len(input_indices):
+        raise ValueError("output arrays must match the input sizes")
+    call("mcb_host_collect_compressed_f32_i32_i32", host_ptr(input_data, "float32", "input_data"),
+         host_ptr(input_indices, "int32", "input_indices"), host_ptr(input_indptr, "int32", "input_indptr"),
+         ("i64", len(input_indptr) - 1), host_ptr(output_data, "float32", "output_data", True),
+         host_ptr(output_indices, "int32", "output_indices", True), host_ptr(output_indptr, "int32", "output_indptr", True),
+         ("i64", len(output_indptr)))
+
+
+def sort_compressed_indices_float32_t_int32_t_int32_t(data, indices, indptr, elements_count):
+    """relayout.cpp:152-167: in place."""
+    del elements_count  # only used by the reference for an assertion
+    call("mcb_host_sort_compressed_indices_f32_i32_i32", host_ptr(data, "float32", "data", True),
+         host_ptr(indices, "int32", "indices", True), host_ptr(indptr, "int32", "indptr"), ("i64", len(indptr) - 1))
+
+
 # @@APPEND@@
