@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""bench.py -- the per-pile k-NN graph hot path (BASELINE.json metric: k-NN graph cells/sec per pile).
+
+A step = one pass of the hot path over one synthetic pile (SURVEY.md section 8d generator):
+downsample -> feature genes -> log-fraction -> abs_pearson similarity (tcgen05) -> rank -> balance ->
+prune -> weights.  `value` is measured with the UMI matrix already resident in HBM; `e2e` goes through
+the reference-facing host entry points with pinned host buffers (H2D of the CSR pile and D2H of the
+graph inside the timed region).  N > 1: every rank builds the graph of its own pile (piles are
+independent, divide_and_conquer.py:1264-1283), no data-path collective: weak scaling.
+
+    python bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      the reference's own CPU implementation of the path
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "knn_graph_cells_per_sec_per_pile"
+UNIT = "cells/s"
+SEED = 123456
+
+
+def parse_args():
+    parser = argparse.ArgumentParser()
+    parser.add_argument("--gpus", type=int, default=1)
+    parser.add_argument("--steps", type=int, default=5)
+    parser.add_argument("--warmup", type=int, default=3)
+    parser.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    parser.add_argument("--cells", type=int, default=16000)
+    parser.add_argument("--genes", type=int, default=27000)
+    parser.add_argument("--features", type=int, default=2000)
+    parser.add_argument("--cpu-cells", type=int, default=8000, help="cells of the bounded CPU-baseline sample")
+    parser.add_argument("--no-cpu-baseline", action="store_true")
+    return parser.parse_args()
+
+
+def workload_name(args, cells):
+    return (f"pile k-NN graph: {cells} cells x {args.genes} genes synthetic UMIs, {args.features} feature genes "
+            f"(downsample+log-fraction+correlate+rank+balance+prune_per)")
+
+
+def make_pile(cells, genes, seed):
+    from synth import synth_umis
+
+    from metacells_b200 import pipeline, tools as tl
+
+    umis = synth_umis(cells, genes, seed=seed)
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    samples = int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(cell_umis, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
+                            np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
+    k = pipeline.knn_k_of_pile(cells, cell_umis)
+    return umis, samples, k
+
+
+# ---- clocks ------------------------------------------------------------------------------------------
+
+
+class ClockSampler:
+    """nvidia-smi samples during the timed region (B200_PROFILING.md clocks line)."""
+
+    QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.process = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.process = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.process = None
+
+    def _read(self):
+        for line in self.process.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.process is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.process.terminate()
+        try:
+            self.process.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.process.kill()
+        clocks, maxima, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            parts = [part.strip() for part in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                clocks.append(float(parts[0]))
+                maxima.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, flag in zip(names, parts[2:6]):
+                if flag.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(clocks)) if clocks else None, "sm_max_mhz": max(maxima) if maxima else None,
+                "samples": len(clocks), "reasons": sorted(reasons)}
+
+
+# ---- CPU: the reference's own implementation of the path ------------------------------------------------
+
+
+def cpu_threads():
+    try:
+        import psutil
+
+        return psutil.cpu_count(logical=False) or os.cpu_count() or 1  # as utilities/parallel.py:127 does
+    except ImportError:
+        return os.cpu_count() or 1
+
+
+def cpu_step_factory(args):
+    """Returns (step, description): step() runs the whole path once on the host cores."""
+    from oracle import oracle
+
+    ref = oracle.load_ref()
+    threads = cpu_threads() if ref is not None else 1
+    if ref is not None:
+        ref.set_threads_count(threads)
+    cells = min(args.cpu_cells, args.cells)
+    umis, _, k = make_pile(cells, args.genes, SEED)
+    timings = {}
+
+    def step():
+        oracle.cpu_pile_knn_graph(umis, args.features, k, SEED, ref=ref, timings=timings)
+        return cells
+
+    info = {"cores": threads, "kind": "reference" if ref is not None else "port",
+            "sample": f"one {cells}-cell pile of the same generator ({args.genes} genes, {args.features} feature genes, k={k}), whole path"}
+    return step, info, timings
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    step, info, timings = cpu_step_factory(args)
+    for _ in range(args.warmup):
+        step()
+    timings.clear()
+    start = time.perf_counter()
+    cells = 0
+    for _ in range(args.steps):
+        cells += step()
+    elapsed = time.perf_counter() - start
+    value = cells / elapsed
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1000.0 * elapsed / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "impl": "reference",
+        "config": {"workload": workload_name(args, min(args.cpu_cells, args.cells)), "timing": "host wall clock"},
+        "cpu_baseline": dict(info, value=value, unit=UNIT),
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "stage_seconds_per_step": {name: seconds / max(args.steps, 1) for name, seconds in timings.items()},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- GPU arm ---------------------------------------------------------------------------------------------
+
+
+class Library:
+    """ctypes access to the C-ABI entry points the bench drives directly."""
+
+    def __init__(self):
+        from metacells_b200 import _lib
+
+        self.lib = _lib.lib()
+        self.check = _lib.check
+        for name in ("mcb_launch_count", "mcb_graph_nnz", "mcb_graph_k", "mcb_pile_nnz"):
+            getattr(self.lib, name).restype = ctypes.c_int64
+        self.lib.mcb_launch_count.restype = ctypes.c_longlong
+
+    def call(self, name, *arguments):
+        function = getattr(self.lib, name)
+        function.restype = ctypes.c_int
+        self.check(function(*arguments))
+
+    def profile(self, name):
+        total, count = ctypes.c_double(0), ctypes.c_longlong(0)
+        self.call("mcb_profile_read", name.encode(), ctypes.byref(total), ctypes.byref(count))
+        return total.value, count.value
+
+    def profile_names(self):
+        buffer = ctypes.create_string_buffer(4096)
+        self.call("mcb_profile_names", buffer, ctypes.c_longlong(4096))
+        return [name for name in buffer.value.decode().split("\n") if name]
+
+
+def p(pointer):
+    return ctypes.c_void_p(pointer)
+
+
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    from metacells_b200 import pipeline, tools as tl
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: there is no CPU fallback for the metacells_b200 hot path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    library = Library()
+    library.call("mcb_set_device", ctypes.c_int(local_rank))
+    device = torch.device("cuda", local_rank)
+
+    umis, samples, k = make_pile(args.cells, args.genes, SEED + rank)  # one pile per rank
+    cells, genes = umis.shape
+    table = pipeline.log_fraction_table(samples)
+    brf, idf, odf, mod = tl.KNN_BALANCED_RANKS_FACTOR, tl.KNN_INCOMING_DEGREE_FACTOR, tl.KNN_OUTGOING_DEGREE_FACTOR, tl.KNN_MIN_OUTGOING_DEGREE
+
+    # host side: pinned CSR and pinned result buffers (e2e); device side: the resident CSR (value)
+    pinned = {name: torch.from_numpy(array).pin_memory() for name, array in
+              (("data", umis.data), ("indices", umis.indices), ("indptr", umis.indptr))}
+    resident = {name: tensor.to(device) for name, tensor in pinned.items()}
+    capacity = cells * (int(round(k * odf)) + 64)
+    result = {"weights": torch.empty(capacity, dtype=torch.float32).pin_memory(),
+              "indices": torch.empty(capacity, dtype=torch.int32).pin_memory(),
+              "indptr": torch.empty(cells + 1, dtype=torch.int32).pin_memory()}
+    gene_totals = np.empty(genes, dtype="float32")
+    stream = torch.cuda.current_stream(device)
+
+    def hot_path(pile):
+        """The path on an existing pile handle; returns the graph handle."""
+        library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
+        library.call("mcb_pile_gene_totals", pile, p(gene_totals.ctypes.data))
+        feature_genes = np.sort(np.argsort(-gene_totals, kind="stable")[:args.features]).astype("int32")
+        graph = ctypes.c_void_p()
+        outside = ctypes.c_int(0)
+        library.call("mcb_pile_knn_graph", pile, p(feature_genes.ctypes.data), ctypes.c_int64(len(feature_genes)),
+                     p(table.ctypes.data), ctypes.c_int64(len(table)), ctypes.c_float(np.float32(1 / 7)), ctypes.c_int(1),
+                     ctypes.c_int64(k), ctypes.c_double(brf), ctypes.c_double(idf), ctypes.c_double(odf), ctypes.c_int64(mod),
+                     ctypes.byref(outside), ctypes.byref(graph))
+        return graph
+
+    def step_resident():
+        pile = ctypes.c_void_p()
+        library.call("mcb_pile_create_dev", p(resident["data"].data_ptr()), p(resident["indices"].data_ptr()),
+                     p(resident["indptr"].data_ptr()), ctypes.c_int64(cells), ctypes.c_int64(genes), p(stream.cuda_stream),
+                     ctypes.byref(pile))
+        graph = hot_path(pile)
+        nnz = library.lib.mcb_graph_nnz(graph)
+        library.lib.mcb_graph_free(graph)
+        library.lib.mcb_pile_free(pile)
+        return nnz
+
+    def step_e2e():
+        pile = ctypes.c_void_p()
+        library.call("mcb_pile_create_host", p(pinned["data"].data_ptr()), p(pinned["indices"].data_ptr()),
+                     p(pinned["indptr"].data_ptr()), ctypes.c_int64(cells), ctypes.c_int64(genes), ctypes.byref(pile))
+        graph = hot_path(pile)
+        nnz = library.lib.mcb_graph_nnz(graph)
+        if nnz > capacity:
+            raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
+        library.call("mcb_graph_read", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
+                     p(result["indptr"].data_ptr()))
+        library.lib.mcb_graph_free(graph)
+        library.lib.mcb_pile_free(pile)
+        return nnz
+
+    def barrier():
+        torch.cuda.synchronize(device)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(device)
+
+    def timed(step, steps):
+        """K steps between events on the launching stream; returns (max-over-ranks ms, nnz)."""
+        begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        begin.record(stream)
+        nnz = 0
+        for _ in range(steps):
+            nnz = step()
+        end.record(stream)
+        barrier()
+        elapsed = torch.tensor([begin.elapsed_time(end)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
+        return float(elapsed.item()), nnz
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    step_e2e()
+    library.call("mcb_profile_reset")
+    library.call("mcb_profile_enable", ctypes.c_int(1))
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches_before = library.lib.mcb_launch_count()
+    resident_ms, nnz = timed(step_resident, args.steps)
+    launches = library.lib.mcb_launch_count() - launches_before
+    clocks = sampler.stop()
+    kernel_ms = {name: library.profile(name) for name in library.profile_names()}
+    library.call("mcb_profile_enable", ctypes.c_int(0))
+    library.call("mcb_profile_reset")
+    e2e_ms, _ = timed(step_e2e, args.steps)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as handle:
+            peaks = json.load(handle)
+    # FP32-emulated tensor peak := dense TF32 peak / 3 (3 MMAs per algorithmic FMA) = (bf16 / 2) / 3; the
+    # correlate kernel runs inside a long step, so the sustained figure applies (B200_PROFILING.md).
+    bf16 = peaks.get("bf16_tflops_sustained")
+    peak_source = "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (tf32) / 3 (3xTF32)"
+    if bf16 is None:
+        bf16, peak_source = 1400.0, "fallback 1.4 PFLOP/s sustained bf16 (B200_PROFILING.md) / 2 / 3"
+    peak = bf16 / 6.0
+    umma_ms, umma_count = kernel_ms.get("correlate_umma", (0.0, 0))
+    flops = float(cells) * cells * args.features  # algorithmic: 2 * g * N (N - 1) / 2 ~= N^2 g
+    achieved = flops / (umma_ms / umma_count * 1e-3) / 1e12 if umma_count else None
+    line = {
+        "metric": METRIC, "value": world * cells * args.steps / (resident_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": resident_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args, cells), "cells": cells, "genes": genes, "feature_genes": args.features, "k": k,
+                   "downsample_samples": samples, "umis_nnz": int(umis.nnz), "graph_nnz": int(nnz), "piles_per_step": world,
+                   "l2": "inputs larger than L2 (CSR pile 0.45 GB, similarity and rank matrices 1 GB each per step)"},
+        "clocks": clocks,
+        "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
+                "h2d_bytes_per_step": int(umis.data.nbytes + umis.indices.nbytes + umis.indptr.nbytes + table.nbytes + 4 * args.features),
+                "d2h_bytes_per_step": int(nnz * 8 + (cells + 1) * 4 + genes * 4)},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "tensor", "kernel": "correlate_umma_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": peak_source,
+                     "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms / umma_count if umma_count else None},
+        "kernel_ms_per_step": {name: total / args.steps for name, (total, _) in sorted(kernel_ms.items())},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        step, info, _ = cpu_step_factory(args)
+        start = time.perf_counter()
+        cpu_cells = step()
+        line["cpu_baseline"] = dict(info, value=cpu_cells / (time.perf_counter() - start), unit=UNIT)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

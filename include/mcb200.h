@@ -37,6 +37,14 @@ int mcb_device_count(void);
 /* Select the CUDA device of the calling thread; fails unless it is compute capability 10.x. */
 int mcb_set_device(int device);
 int mcb_synchronize(void* stream);
+/* Number of kernels this library has launched in the calling process so far. */
+long long mcb_launch_count(void);
+/* Optional per-kernel timing: when enabled every launch is bracketed by CUDA events on its own
+ * stream; mcb_profile_read sums the recorded milliseconds of one kernel name (synchronises). */
+int mcb_profile_enable(int enable);
+int mcb_profile_read(const char* name, double* total_ms, long long* count);
+int mcb_profile_names(char* buffer, long long size);
+int mcb_profile_reset(void);
 
 /* ---- downsample.cpp ------------------------------------------------------------------------- */
 
@@ -155,6 +163,35 @@ int mcb_graph_read(const mcb_graph* graph, float* weights, float* ranks, int32_t
 int mcb_graph_device_arrays(const mcb_graph* graph, const float** weights, const float** ranks, const int32_t** indices,
                             const int32_t** indptr);
 void mcb_graph_free(mcb_graph* graph);
+
+/* ---- pipeline/direct.py:214-283: one pile, device resident -------------------------------------- */
+
+/* A pile = the cells x genes UMI matrix (CSR float32/int32/int32) of compute_direct_metacells,
+ * uploaded once (create_host) or borrowed from device memory (create_dev; the arrays must outlive
+ * the pile).  All later calls run on the pile's stream and keep every intermediate in HBM. */
+typedef struct mcb_pile mcb_pile;
+int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
+                         mcb_pile** out);
+int mcb_pile_create_dev(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
+                        void* stream, mcb_pile** out);
+int64_t mcb_pile_nnz(const mcb_pile* pile);
+/* tools/downsample.py:99 -> downsample_compressed (downsample.cpp:171-192), every cell to `samples`. */
+int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed);
+int mcb_pile_read_downsampled(mcb_pile* pile, float* data); /* nnz values, same structure as the input */
+/* Per-gene totals of the (downsampled, if done) matrix to a host array of `genes` floats. */
+int mcb_pile_gene_totals(mcb_pile* pile, float* totals);
+/* direct.py:242-249 + tools/similarity.py:178-246: dense slice of `feature_genes` (host, ascending
+ * gene indices), log2(x + regularization) through `log_table` (host; log_table[c] = np.log2(c +
+ * regularization) for c = 0 .. table_size-1), Pearson (absolute != 0: |r|) into similarity_dev
+ * [cells, cells] (device).  *outside_table (host, may be NULL) reports values the table missed. */
+int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
+                        int64_t table_size, float regularization, int absolute, float* similarity_dev, int* outside_table);
+/* ... followed by compute_obs_obs_knn_graph (see mcb_dev_knn_graph_f32). */
+int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
+                       int64_t table_size, float regularization, int absolute, int64_t k, double balanced_ranks_factor,
+                       double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                       int* outside_table, mcb_graph** out);
+void mcb_pile_free(mcb_pile* pile);
 
 /* @@APPEND@@ */
 

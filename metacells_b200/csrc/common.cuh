@@ -27,6 +27,20 @@ int fail(int code, const char* format, ...);
                                cudaGetErrorString(mcb_err__));                                      \
     } while (0)
 
+// After every kernel launch: counts the launch (mcb_launch_count) and surfaces launch errors.
+#define MCB_LAUNCH_CHECK()                                                                           \
+    do {                                                                                            \
+        ::mcb::count_launch();                                                                      \
+        MCB_CUDA(cudaGetLastError());                                                               \
+    } while (0)
+
+// Runs a kernel launch statement inside a ProfileScope (timed only when mcb_profile_enable(1)).
+#define MCB_PROFILED(name, stream, ...)                    \
+    do {                                                   \
+        ::mcb::ProfileScope mcb_scope__((name), (stream)); \
+        __VA_ARGS__;                                       \
+    } while (0)
+
 #define MCB_TRY(expr)                  \
     do {                               \
         int mcb_code__ = (expr);       \
@@ -63,6 +77,15 @@ struct Scratch {
 };
 
 int sm_count();
+void count_launch();
+
+// Optional per-kernel timing (mcb_profile_enable): CUDA events around a launch on its own stream.
+struct ProfileScope {
+    int slot = -1;
+    cudaStream_t stream = nullptr;
+    ProfileScope(const char* name, cudaStream_t stream);
+    ~ProfileScope();
+};
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

@@ -172,8 +172,8 @@ int prepare_rows_f32(const float* input, int64_t rows, int64_t columns, int64_t 
                      float* lo, double* f64, cudaStream_t stream) {
     if (rows == 0)
         return MCB_OK;
-    prepare_rows_kernel<float><<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(input, rows, columns, row_stride, padded, hi, lo, f64);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("correlate_prepare", stream, prepare_rows_kernel<float><<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(input, rows, columns, row_stride, padded, hi, lo, f64));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -181,8 +181,8 @@ int prepare_rows_f64(const double* input, int64_t rows, int64_t columns, int64_t
                      float* lo, double* f64, cudaStream_t stream) {
     if (rows == 0)
         return MCB_OK;
-    prepare_rows_kernel<double><<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(input, rows, columns, row_stride, padded, hi, lo, f64);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("correlate_prepare", stream, prepare_rows_kernel<double><<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(input, rows, columns, row_stride, padded, hi, lo, f64));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -191,8 +191,8 @@ int dot_rows_f64(const double* x, const double* y, int64_t rows_x, int64_t rows_
     if (rows_x == 0 || rows_y == 0)
         return MCB_OK;
     dim3 grid((unsigned)ceil_div(rows_y, DT), (unsigned)ceil_div(rows_x, DT));
-    dot_rows_f64_kernel<<<grid, 256, 0, stream>>>(x, y, rows_x, rows_y, padded, output, out_stride, symmetric);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("correlate_f64", stream, dot_rows_f64_kernel<<<grid, 256, 0, stream>>>(x, y, rows_x, rows_y, padded, output, out_stride, symmetric));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -200,7 +200,7 @@ int pairs_rows_f32(const float* first, const float* second, int64_t rows, int64_
     if (rows == 0)
         return MCB_OK;
     pairs_kernel<float><<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(first, second, rows, columns, output);
-    MCB_CUDA(cudaGetLastError());
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -208,7 +208,7 @@ int pairs_rows_f64(const double* first, const double* second, int64_t rows, int6
     if (rows == 0)
         return MCB_OK;
     pairs_kernel<double><<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(first, second, rows, columns, output);
-    MCB_CUDA(cudaGetLastError());
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 

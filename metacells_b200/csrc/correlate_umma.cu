@@ -376,8 +376,8 @@ int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, 
     p.absolute = absolute;
     const int grid = (int)std::min<int64_t>((int64_t)order.size(), sm_count());
     MCB_CUDA(cudaFuncSetAttribute(correlate_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UMMA_SMEM));
-    correlate_umma_kernel<<<(unsigned)grid, UMMA_THREADS, UMMA_SMEM, stream>>>(map_a_hi, map_a_lo, map_b_hi, map_b_lo, p);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("correlate_umma", stream, correlate_umma_kernel<<<(unsigned)grid, UMMA_THREADS, UMMA_SMEM, stream>>>(map_a_hi, map_a_lo, map_b_hi, map_b_lo, p));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 

@@ -221,8 +221,8 @@ int downsample_launch(const float* input, float* output, const int32_t* indptr, 
         p.workspace = workspace.as<uint32_t>();
     }
     MCB_CUDA(cudaFuncSetAttribute(downsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    downsample_kernel<<<(unsigned)grid, DS_THREADS, smem_bytes, stream>>>(p);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("downsample", stream, downsample_kernel<<<(unsigned)grid, DS_THREADS, smem_bytes, stream>>>(p));
+    MCB_LAUNCH_CHECK();
     int host_flag = 0;
     MCB_CUDA(cudaMemcpyAsync(&host_flag, flag.ptr, sizeof(int), cudaMemcpyDeviceToHost, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));

@@ -349,11 +349,11 @@ int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream) {
     Scratch min_key;
     MCB_TRY(min_key.alloc(sizeof(uint32_t), stream));
     MCB_CUDA(cudaMemsetAsync(min_key.ptr, 0xff, sizeof(uint32_t), stream));
-    min_matrix_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n * n, 1024), (int64_t)sm_count() * 8), 256, 0, stream>>>(
-        work, n, n, n, min_key.as<uint32_t>());
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("min_matrix", stream, min_matrix_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n * n, 1024), (int64_t)sm_count() * 8), 256, 0, stream>>>(
+        work, n, n, n, min_key.as<uint32_t>()));
+    MCB_LAUNCH_CHECK();
     fill_diagonal_below_min_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, stream>>>(work, n, n, min_key.as<uint32_t>());
-    MCB_CUDA(cudaGetLastError());
+    MCB_LAUNCH_CHECK();
     return rank_matrix_launch(work, n, n, n, 0, stream);
 }
 
@@ -382,11 +382,11 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     p.shift = shift;
     p.counts = counts.as<int32_t>();
     p.row_best = row_best.as<unsigned long long>();
-    balance_kernel<false><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p);
-    MCB_CUDA(cudaGetLastError());
-    balance_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(p, row_sizes.as<int32_t>(), out->best_index.as<int32_t>(),
-                                                                     out->best_value.as<float>());
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("balance_count", stream, balance_kernel<false><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p));
+    MCB_LAUNCH_CHECK();
+    MCB_PROFILED("balance_rows", stream, balance_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(p, row_sizes.as<int32_t>(), out->best_index.as<int32_t>(),
+                                                                     out->best_value.as<float>()));
+    MCB_LAUNCH_CHECK();
     MCB_TRY(exclusive_scan_i32(row_sizes.as<int32_t>(), out->indptr.as<int32_t>(), n, nullptr, stream));
     int32_t nnz = 0;
     MCB_TRY(read_i32(out->indptr.as<int32_t>() + n, &nnz, stream));
@@ -397,8 +397,8 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     p.out_data = out->data.as<float>();
     p.out_indices = out->indices.as<int32_t>();
     p.best_index = out->best_index.as<int32_t>();
-    balance_kernel<true><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("balance_fill", stream, balance_kernel<true><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -445,12 +445,12 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     MCB_CUDA(cudaMemsetAsync(reverse_counts.ptr, 0, (size_t)n * sizeof(int32_t), stream));
     const unsigned row_blocks = (unsigned)ceil_div(n, 256), warp_blocks = (unsigned)ceil_div(n, 8);
     reverse_count_kernel<<<row_blocks, 256, 0, stream>>>(balanced.best_index.as<int32_t>(), n, reverse_counts.as<int32_t>());
-    MCB_CUDA(cudaGetLastError());
+    MCB_LAUNCH_CHECK();
     MCB_TRY(exclusive_scan_i32(reverse_counts.as<int32_t>(), reverse_ptr.as<int32_t>(), n, nullptr, stream));
     MCB_CUDA(cudaMemcpyAsync(reverse_cursor.ptr, reverse_ptr.ptr, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
     reverse_scatter_kernel<<<row_blocks, 256, 0, stream>>>(balanced.best_index.as<int32_t>(), n, reverse_cursor.as<int32_t>(),
                                                           reverse_list.as<int32_t>());
-    MCB_CUDA(cudaGetLastError());
+    MCB_LAUNCH_CHECK();
     MergeParams m{};
     m.data = out_data.as<float>();
     m.indices = out_indices.as<int32_t>();
@@ -461,8 +461,8 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     m.reverse_ptr = reverse_ptr.as<int32_t>();
     m.reverse_list = reverse_list.as<int32_t>();
     m.out_sizes = sizes.as<int32_t>();
-    merge_preserved_kernel<false><<<warp_blocks, 256, 0, stream>>>(m);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("merge_count", stream, merge_preserved_kernel<false><<<warp_blocks, 256, 0, stream>>>(m));
+    MCB_LAUNCH_CHECK();
     MCB_TRY(out->indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
     MCB_TRY(exclusive_scan_i32(sizes.as<int32_t>(), out->indptr.as<int32_t>(), n, nullptr, stream));
     int32_t nnz = 0;
@@ -473,8 +473,8 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     m.out_indptr = out->indptr.as<int32_t>();
     m.out_data = out->data.as<float>();
     m.out_indices = out->indices.as<int32_t>();
-    merge_preserved_kernel<true><<<warp_blocks, 256, 0, stream>>>(m);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("merge_fill", stream, merge_preserved_kernel<true><<<warp_blocks, 256, 0, stream>>>(m));
+    MCB_LAUNCH_CHECK();
     return sort_compressed_indices_launch(out->data.as<float>(), out->indices.as<int32_t>(), out->indptr.as<int32_t>(), n,
                                           -1, stream);
 }
@@ -486,11 +486,11 @@ int weigh_edges_launch(const float* data, const int32_t* indptr, int64_t n, floa
     MCB_TRY(scale.alloc((size_t)n * sizeof(float), stream));
     MCB_TRY(min_size.alloc(sizeof(int32_t), stream));
     MCB_CUDA(cudaMemsetAsync(min_size.ptr, 0x7f, sizeof(int32_t), stream));
-    row_scale_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, stream>>>(data, indptr, n, scale.as<float>(), min_size.as<int32_t>());
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("row_scale", stream, row_scale_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, stream>>>(data, indptr, n, scale.as<float>(), min_size.as<int32_t>()));
+    MCB_LAUNCH_CHECK();
     if (weights) {
-        scale_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(data, indptr, n, scale.as<float>(), weights);
-        MCB_CUDA(cudaGetLastError());
+        MCB_PROFILED("scale_rows", stream, scale_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(data, indptr, n, scale.as<float>(), weights));
+        MCB_LAUNCH_CHECK();
     }
     if (min_degree_host)
         MCB_TRY(read_i32(min_size.as<int32_t>(), min_degree_host, stream));

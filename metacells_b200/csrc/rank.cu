@@ -163,8 +163,8 @@ int rank_matrix_launch(float* matrix, int64_t rows, int64_t columns, int64_t row
         p.workspace = workspace.as<uint8_t>();
     }
     MCB_CUDA(cudaFuncSetAttribute(rank_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    rank_matrix_kernel<<<(unsigned)grid, RM_THREADS, smem_bytes, stream>>>(p);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("rank_matrix", stream, rank_matrix_kernel<<<(unsigned)grid, RM_THREADS, smem_bytes, stream>>>(p));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -284,9 +284,9 @@ int rank_rows_launch(const float* matrix, int64_t rows, int64_t columns, int64_t
     const size_t smem_bytes = (size_t)cache_capacity * 4;
     MCB_CUDA(cudaFuncSetAttribute(rank_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
-    rank_rows_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(matrix, rows, columns, row_stride, output, (int)rank,
-                                                                        cache_capacity);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("rank_rows", stream, rank_rows_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(matrix, rows, columns, row_stride, output, (int)rank,
+                                                                        cache_capacity));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -312,8 +312,8 @@ int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, in
     const size_t smem_bytes = (size_t)p.cache_capacity * 4 + kept_bytes;
     MCB_CUDA(cudaFuncSetAttribute(collect_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
-    collect_top_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(p);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("collect_top", stream, collect_top_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(p));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 

@@ -1,4 +1,11 @@
 // Library runtime: error reporting, device selection and cached device properties.
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
 #include "common.cuh"
 #include "../../include/mcb200.h"
 
@@ -28,9 +35,96 @@ int sm_count() {
     return cached;
 }
 
+namespace {
+std::atomic<long long> g_launches{0};
+std::atomic<int> g_profile{0};
+struct ProfileRecord {
+    std::string name;
+    cudaEvent_t start, stop;
+};
+std::mutex g_profile_mutex;
+std::vector<ProfileRecord> g_records;
+}  // namespace
+
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+ProfileScope::ProfileScope(const char* name, cudaStream_t s) : stream(s) {
+    if (!g_profile.load(std::memory_order_relaxed))
+        return;
+    ProfileRecord record;
+    record.name = name;
+    if (cudaEventCreate(&record.start) != cudaSuccess || cudaEventCreate(&record.stop) != cudaSuccess)
+        return;
+    cudaEventRecord(record.start, stream);
+    std::lock_guard<std::mutex> lock(g_profile_mutex);
+    g_records.push_back(record);
+    slot = (int)g_records.size() - 1;
+}
+
+ProfileScope::~ProfileScope() {
+    if (slot < 0)
+        return;
+    std::lock_guard<std::mutex> lock(g_profile_mutex);
+    if (slot < (int)g_records.size())
+        cudaEventRecord(g_records[slot].stop, stream);
+}
+
 }  // namespace mcb
 
 extern "C" {
+
+long long mcb_launch_count(void) { return mcb::g_launches.load(); }
+
+int mcb_profile_enable(int enable) {
+    mcb::g_profile.store(enable ? 1 : 0);
+    return MCB_OK;
+}
+
+// Sum of the recorded durations of `name` (milliseconds) and their count; synchronises the device.
+int mcb_profile_read(const char* name, double* total_ms, long long* count) {
+    MCB_CUDA(cudaDeviceSynchronize());
+    std::lock_guard<std::mutex> lock(mcb::g_profile_mutex);
+    double total = 0;
+    long long n = 0;
+    for (auto& record : mcb::g_records)
+        if (record.name == name) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, record.start, record.stop) == cudaSuccess) {
+                total += ms;
+                ++n;
+            }
+        }
+    if (total_ms) *total_ms = total;
+    if (count) *count = n;
+    return MCB_OK;
+}
+
+// Names seen so far, separated by newlines, into buffer (truncated to size - 1 characters).
+int mcb_profile_names(char* buffer, long long size) {
+    std::lock_guard<std::mutex> lock(mcb::g_profile_mutex);
+    std::string names;
+    for (auto& record : mcb::g_records)
+        if (("\n" + names).find("\n" + record.name + "\n") == std::string::npos)
+            names += record.name + "\n";
+    if (buffer && size > 0) {
+        const size_t n = std::min<size_t>(names.size(), (size_t)size - 1);
+        memcpy(buffer, names.data(), n);
+        buffer[n] = 0;
+    }
+    return MCB_OK;
+}
+
+int mcb_profile_reset(void) {
+    MCB_CUDA(cudaDeviceSynchronize());
+    std::lock_guard<std::mutex> lock(mcb::g_profile_mutex);
+    for (auto& record : mcb::g_records) {
+        cudaEventDestroy(record.start);
+        cudaEventDestroy(record.stop);
+    }
+    mcb::g_records.clear();
+    return MCB_OK;
+}
+
 
 const char* mcb_last_error(void) { return mcb::error_buffer(); }
 

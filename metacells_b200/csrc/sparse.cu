@@ -210,8 +210,8 @@ __global__ void max_band_kernel(const int32_t* __restrict__ indptr, int64_t band
 }  // namespace
 
 int exclusive_scan_i32(const int32_t* input, int32_t* output, int64_t count, int32_t* total_out, cudaStream_t stream) {
-    exclusive_scan_kernel<<<1, 1024, 0, stream>>>(input, output, count, total_out);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("exclusive_scan", stream, exclusive_scan_kernel<<<1, 1024, 0, stream>>>(input, output, count, total_out));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -223,7 +223,7 @@ int collect_pruned_launch(int64_t degree, const float* data, const int32_t* indi
     MCB_TRY(sizes.alloc((size_t)(bands ? bands : 1) * sizeof(int32_t), stream));
     if (bands > 0) {
         pruned_sizes_kernel<<<(unsigned)ceil_div(bands, 256), 256, 0, stream>>>(indptr, bands, (int32_t)degree, sizes.as<int32_t>());
-        MCB_CUDA(cudaGetLastError());
+        MCB_LAUNCH_CHECK();
     }
     MCB_TRY(exclusive_scan_i32(sizes.as<int32_t>(), out_indptr, bands, nullptr, stream));
     if (bands == 0)
@@ -240,8 +240,8 @@ int collect_pruned_launch(int64_t degree, const float* data, const int32_t* indi
     p.cache_capacity = 8192;
     const size_t smem_bytes = (size_t)p.cache_capacity * 4;
     const int64_t grid = std::min<int64_t>(bands, (int64_t)sm_count() * 6);
-    prune_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(p);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("prune_bands", stream, prune_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(p));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -251,8 +251,8 @@ int collect_compressed_launch(const float* data, const int32_t* indices, const i
     if (bands == 0)
         return MCB_OK;
     const int64_t grid = std::min<int64_t>(ceil_div(bands * 32, 256), (int64_t)sm_count() * 16);
-    scatter_bands_kernel<<<(unsigned)grid, 256, 0, stream>>>(data, indices, indptr, bands, out_data, out_indices, cursor);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("relayout_scatter", stream, scatter_bands_kernel<<<(unsigned)grid, 256, 0, stream>>>(data, indices, indptr, bands, out_data, out_indices, cursor));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -266,7 +266,7 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
         MCB_TRY(widest.alloc(sizeof(int32_t), stream));
         MCB_CUDA(cudaMemsetAsync(widest.ptr, 0, sizeof(int32_t), stream));
         max_band_kernel<<<(unsigned)std::min<int64_t>(ceil_div(bands, 256), 1024), 256, 0, stream>>>(indptr, bands, widest.as<int32_t>());
-        MCB_CUDA(cudaGetLastError());
+        MCB_LAUNCH_CHECK();
         int32_t host = 0;
         MCB_CUDA(cudaMemcpyAsync(&host, widest.ptr, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
@@ -282,9 +282,9 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
     if (padded > smem_capacity)
         MCB_TRY(workspace.alloc((size_t)grid * padded * 8, stream));
     MCB_CUDA(cudaFuncSetAttribute(sort_bands_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    sort_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(data, indices, indptr, bands, smem_capacity,
-                                                                          workspace.as<unsigned long long>(), padded);
-    MCB_CUDA(cudaGetLastError());
+    MCB_PROFILED("sort_bands", stream, sort_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(data, indices, indptr, bands, smem_capacity,
+                                                                          workspace.as<unsigned long long>(), padded));
+    MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
 
@@ -297,9 +297,9 @@ int relayout_launch(const float* data, const int32_t* indices, const int32_t* in
     MCB_TRY(cursor.alloc((size_t)(bands_out + 1) * sizeof(int32_t), stream));
     MCB_CUDA(cudaMemsetAsync(counts.ptr, 0, (size_t)(bands_out + 1) * sizeof(int32_t), stream));
     if (nnz > 0) {
-        count_indices_kernel<<<(unsigned)std::min<int64_t>(ceil_div(nnz, 256), (int64_t)sm_count() * 16), 256, 0, stream>>>(
-            indices, nnz, counts.as<int32_t>());
-        MCB_CUDA(cudaGetLastError());
+        MCB_PROFILED("relayout_count", stream, count_indices_kernel<<<(unsigned)std::min<int64_t>(ceil_div(nnz, 256), (int64_t)sm_count() * 16), 256, 0, stream>>>(
+            indices, nnz, counts.as<int32_t>()));
+        MCB_LAUNCH_CHECK();
     }
     MCB_TRY(exclusive_scan_i32(counts.as<int32_t>(), out_indptr, bands_out, nullptr, stream));
     MCB_CUDA(cudaMemcpyAsync(cursor.ptr, out_indptr, (size_t)(bands_out ? bands_out : 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));

@@ -1,0 +1,157 @@
+"""The per-pile k-NN graph of ``compute_direct_metacells`` (pipeline/direct.py:26-283), device
+resident: the UMI matrix is uploaded once, downsampled, sliced to the feature genes, log-transformed,
+correlated, ranked, balanced and pruned in HBM, and only the graph comes back.
+
+``Pile`` wraps the ``mcb_pile`` handle of include/mcb200.h.  Feature-gene selection
+(pipeline/select.py) is outside the hot path: the caller passes the gene indices, or uses the
+``top_total_genes`` stand-in (the genes with the largest downsampled totals).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import numpy as np
+import scipy.sparse as sp
+
+from . import tools as tl
+from ._lib import check, lib
+
+__all__ = ["Pile", "compute_pile_knn_graph", "knn_k_of_pile", "log_fraction_table"]
+
+# metacells/parameters.py
+CELLS_SIMILARITY_VALUE_REGULARIZATION = 1 / 7
+TARGET_METACELL_SIZE = 48
+TARGET_METACELL_UMIS = 160000
+KNN_K_SIZE_FACTOR = 2.0
+KNN_K_UMIS_QUANTILE = 0.1
+MIN_KNN_K = 30
+
+
+def log_fraction_table(max_count: int, regularization: float = CELLS_SIMILARITY_VALUE_REGULARIZATION) -> np.ndarray:
+    """``np.log2(float32(c) + regularization)`` for c = 0 .. max_count, computed by numpy itself in
+    float32 exactly as direct.py:245-249 does element by element."""
+    table = np.arange(max_count + 1, dtype="float32")
+    table += regularization
+    np.log2(table, out=table)
+    return table
+
+
+def knn_k_of_pile(cells_count: int, cell_umis: np.ndarray, *, target_metacell_size: int = TARGET_METACELL_SIZE,
+                  target_metacell_umis: int = TARGET_METACELL_UMIS, knn_k_size_factor: float = KNN_K_SIZE_FACTOR,
+                  knn_k_umis_quantile: float = KNN_K_UMIS_QUANTILE, min_knn_k: Optional[int] = MIN_KNN_K) -> int:
+    """pipeline/direct.py:251-267."""
+    by_size = int(round(cells_count / target_metacell_size))
+    by_median = int(round(knn_k_size_factor * target_metacell_umis / float(np.median(cell_umis))))
+    by_quantile = int(round(target_metacell_umis / np.quantile(cell_umis, knn_k_umis_quantile)))
+    return max(by_size, by_median, by_quantile, min_knn_k or 0)
+
+
+def _ptr(array: np.ndarray) -> ctypes.c_void_p:
+    return ctypes.c_void_p(array.ctypes.data)
+
+
+class Pile:
+    """A device-resident pile (cells x genes UMI CSR matrix)."""
+
+    def __init__(self, umis: sp.csr_matrix):
+        umis = sp.csr_matrix(umis)
+        self._data = np.ascontiguousarray(umis.data, dtype="float32")
+        self._indices = np.ascontiguousarray(umis.indices, dtype="int32")
+        self._indptr = np.ascontiguousarray(umis.indptr, dtype="int32")
+        self.shape = umis.shape
+        self._handle = ctypes.c_void_p()
+        function = lib().mcb_pile_create_host
+        function.restype = ctypes.c_int
+        check(function(_ptr(self._data), _ptr(self._indices), _ptr(self._indptr), ctypes.c_int64(umis.shape[0]),
+                       ctypes.c_int64(umis.shape[1]), ctypes.byref(self._handle)))
+        self.samples: Optional[int] = None
+
+    def close(self) -> None:
+        if getattr(self, "_handle", None):
+            lib().mcb_pile_free(self._handle)
+            self._handle = None
+
+    def __del__(self):
+        self.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *_):
+        self.close()
+
+    def downsample(self, samples: int, random_seed: int) -> None:
+        """tools/downsample.py:99."""
+        function = lib().mcb_pile_downsample
+        function.restype = ctypes.c_int
+        check(function(self._handle, ctypes.c_int32(int(samples)), ctypes.c_uint64(int(random_seed))))
+        self.samples = int(samples)
+
+    def downsampled(self) -> sp.csr_matrix:
+        data = np.empty(len(self._data), dtype="float32")
+        function = lib().mcb_pile_read_downsampled
+        function.restype = ctypes.c_int
+        check(function(self._handle, _ptr(data)))
+        return sp.csr_matrix((data, self._indices.copy(), self._indptr.copy()), shape=self.shape)
+
+    def gene_totals(self) -> np.ndarray:
+        totals = np.empty(self.shape[1], dtype="float32")
+        function = lib().mcb_pile_gene_totals
+        function.restype = ctypes.c_int
+        check(function(self._handle, _ptr(totals)))
+        return totals
+
+    def top_total_genes(self, features: int) -> np.ndarray:
+        """The ``features`` genes with the largest totals (ties: lower gene index), ascending."""
+        totals = self.gene_totals()
+        return np.sort(np.argsort(-totals, kind="stable")[:features]).astype("int32")
+
+    def knn_graph(self, feature_genes: np.ndarray, *, k: int, method: str = "abs_pearson",
+                  regularization: float = CELLS_SIMILARITY_VALUE_REGULARIZATION,
+                  balanced_ranks_factor: float = tl.KNN_BALANCED_RANKS_FACTOR,
+                  incoming_degree_factor: float = tl.KNN_INCOMING_DEGREE_FACTOR,
+                  outgoing_degree_factor: float = tl.KNN_OUTGOING_DEGREE_FACTOR,
+                  min_outgoing_degree: int = tl.KNN_MIN_OUTGOING_DEGREE, max_count: Optional[int] = None) -> tl.KnnGraph:
+        """direct.py:242-283: log-fraction of the feature genes, similarity, balanced k-NN graph."""
+        if method not in ("pearson", "abs_pearson"):
+            raise NotImplementedError("only pearson / abs_pearson are on the hot path")
+        feature_genes = np.ascontiguousarray(feature_genes, dtype="int32")
+        if max_count is None:
+            max_count = int(self.samples if self.samples is not None else self._data.max(initial=0))
+        table = log_fraction_table(min(max_count, 1 << 20), regularization)
+        handle = ctypes.c_void_p()
+        outside = ctypes.c_int(0)
+        function = lib().mcb_pile_knn_graph
+        function.restype = ctypes.c_int
+        check(function(self._handle, _ptr(feature_genes), ctypes.c_int64(len(feature_genes)), _ptr(table),
+                       ctypes.c_int64(len(table)), ctypes.c_float(np.float32(regularization)),
+                       ctypes.c_int(int(method == "abs_pearson")), ctypes.c_int64(int(k)), ctypes.c_double(balanced_ranks_factor),
+                       ctypes.c_double(incoming_degree_factor), ctypes.c_double(outgoing_degree_factor),
+                       ctypes.c_int64(int(min_outgoing_degree)), ctypes.byref(outside), ctypes.byref(handle)))
+        graph = tl.KnnGraph(handle)
+        graph.outside_table = bool(outside.value)
+        return graph
+
+
+def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature_genes: Optional[np.ndarray] = None,
+                           k: Optional[int] = None, random_seed: int = 123456) -> Tuple[sp.csr_matrix, dict]:
+    """The k-NN graph part of ``compute_direct_metacells`` for one pile: downsample (tools/downsample.py),
+    feature genes, log-fraction, ``abs_pearson`` similarity, ``compute_obs_obs_knn_graph``.
+    Returns ``(obs_outgoing_weights, details)``."""
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")  # direct.py:214-218
+    samples = int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(cell_umis, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
+                            np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
+    if k is None:
+        k = knn_k_of_pile(umis.shape[0], cell_umis)
+    with Pile(umis) as pile:
+        pile.downsample(samples, random_seed)
+        if feature_genes is None:
+            feature_genes = pile.top_total_genes(features)
+        graph = pile.knn_graph(feature_genes, k=k)
+        try:
+            weights, pruned = graph.to_scipy()
+            details = {"k": graph.k, "samples": samples, "feature_genes": feature_genes, "pruned_ranks": pruned}
+        finally:
+            graph.close()
+    return weights, details

@@ -296,3 +296,107 @@ def load_ref():
     module = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(module)
     return module
+
+
+# ---------------------------------------------------------------------------------------------
+# the whole per-pile path on the CPU (bench.py's cpu_baseline / --impl reference leg)
+# ---------------------------------------------------------------------------------------------
+
+
+def cpu_pile_knn_graph(umis: sp.csr_matrix, features: int, k: int, seed: int, ref=None, timings: Optional[dict] = None):
+    """downsample -> feature genes -> log-fraction -> abs_pearson similarity -> balanced k-NN graph,
+    sequenced as pipeline/direct.py:214-283 does.  With ``ref`` (oracle/_ref, the unmodified reference
+    natives, multi-threaded) every native call goes to the reference; otherwise to the C port of
+    this directory (single thread).  Returns the outgoing weights CSR matrix."""
+    import time
+
+    def lap(name, start):
+        if timings is not None:
+            timings[name] = timings.get(name, 0.0) + time.perf_counter() - start
+
+    start = time.perf_counter()
+    totals = np.asarray(umis.sum(axis=1)).reshape(-1)
+    samples = np.full(umis.shape[0], downsample_samples(totals), dtype="int32")
+    if ref is not None:
+        down_data = np.empty_like(umis.data)
+        ref.downsample_compressed_float32_t_int32_t_float32_t(umis.data, umis.indptr, down_data, samples, seed)
+    else:
+        down_data = downsample_compressed(umis.data, umis.indptr, samples, seed)
+    down = sp.csr_matrix((down_data, umis.indices, umis.indptr), shape=umis.shape)
+    lap("downsample", start)
+
+    start = time.perf_counter()
+    gene_totals = np.asarray(down.sum(axis=0)).reshape(-1)
+    genes = np.sort(np.argsort(-gene_totals, kind="stable")[:features])
+    dense = log_fraction(down[:, genes].toarray())
+    lap("log_fraction", start)
+
+    start = time.perf_counter()
+    if ref is not None:
+        sim = np.empty((dense.shape[0], dense.shape[0]), dtype="float32")
+        ref.correlate_dense_float32_t(dense, sim)
+    else:
+        sim = correlate_dense(dense)
+    sim[np.isnan(sim)] = 0.0
+    np.fill_diagonal(sim, 1.0)
+    np.absolute(sim, out=sim)
+    lap("correlate", start)
+
+    def ref_prune(compressed, top):
+        bands = compressed.shape[0]
+        out_data = np.empty(bands * top, dtype="float32")
+        out_indices = np.empty(bands * top, dtype="int32")
+        out_indptr = np.empty(bands + 1, dtype="int32")
+        ref.collect_pruned_float32_t_int32_t_int32_t(top, compressed.data, compressed.indices, compressed.indptr, out_data, out_indices, out_indptr)
+        nnz = out_indptr[-1]
+        constructor = sp.csr_matrix if compressed.format == "csr" else sp.csc_matrix
+        return constructor((out_data[:nnz], out_indices[:nnz], out_indptr), shape=compressed.shape)
+
+    def ref_csc_to_csr(csc):
+        size = csc.shape[0]
+        counts = np.bincount(csc.indices, minlength=size)
+        indptr = np.zeros(size + 1, dtype="int32")
+        np.cumsum(counts[:-1], out=indptr[2:])
+        data = np.empty_like(csc.data)
+        indices = np.empty_like(csc.indices)
+        ref.collect_compressed_float32_t_int32_t_int32_t(csc.data, csc.indices, csc.indptr, data, indices, indptr[1:])
+        ref.sort_compressed_indices_float32_t_int32_t_int32_t(data, indices, indptr, size)
+        return sp.csr_matrix((data, indices, indptr), shape=csc.shape)
+
+    size = sim.shape[0]
+    while True:
+        start = time.perf_counter()
+        if ref is not None:
+            ranks = np.copy(sim)
+            np.fill_diagonal(ranks, np.min(ranks) - 1)
+            ref.rank_matrix_float32_t(ranks, False)
+        else:
+            ranks = rank_outgoing(sim)
+        lap("rank_matrix", start)
+        start = time.perf_counter()
+        balanced = balance_ranks(ranks, k, float(np.sqrt(10)))
+        lap("balance_ranks", start)
+        start = time.perf_counter()
+        if ref is not None:
+            incoming = min(int(round(k * 3.0)), size - 1)
+            outgoing = min(int(round(k * 1.0)), size - 1)
+            rows = np.arange(size)
+            best = np.asarray(balanced.argmax(axis=1)).reshape(-1)
+            preserved = sp.coo_matrix((np.asarray(balanced[rows, best]).reshape(-1), (rows, best)), shape=balanced.shape)
+            pruned = sp.csc_matrix((balanced.data, balanced.indices, balanced.indptr), shape=balanced.shape)
+            pruned = ref_prune(pruned, incoming)
+            pruned = ref_csc_to_csr(pruned)
+            pruned = ref_prune(pruned, outgoing)
+            pruned = pruned.maximum(preserved).maximum(preserved.transpose())
+            pruned = sp.csr_matrix(pruned)
+            pruned.sort_indices()
+        else:
+            pruned = prune_ranks(balanced, k, 3.0, 1.0)
+        lap("prune_ranks", start)
+        if np.min(np.diff(pruned.indptr)) >= 2:
+            break
+        k += max(1, int(k / 10))
+    start = time.perf_counter()
+    weights = weigh_edges(pruned)
+    lap("weigh_edges", start)
+    return weights
