@@ -31,6 +31,7 @@ int correlate_f32_device(const float* first, int64_t first_rows, int64_t first_s
     MCB_TRY(a_hi.alloc((size_t)first_rows * padded * sizeof(float), stream));
     MCB_TRY(a_lo.alloc((size_t)first_rows * padded * sizeof(float), stream));
     MCB_TRY(prepare_rows_f32(first, first_rows, columns, first_stride, padded, a_hi.as<float>(), a_lo.as<float>(), nullptr, stream));
+    trace_lap("correlate: prepare", stream);
     const float* bh = a_hi.as<float>();
     const float* bl = a_lo.as<float>();
     if (!symmetric) {

@@ -69,11 +69,14 @@ int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balan
     MCB_REQUIRE(k >= 1 && balanced_ranks_factor > 0 && incoming_degree_factor > 0 && outgoing_degree_factor > 0 &&
                     min_outgoing_degree >= 1,
                 "knn_graph: bad parameters");  // knn_graph.py:216-220
+    trace_lap("knn: enter", stream);
     Scratch work;
     MCB_TRY(work.alloc((size_t)n * n * sizeof(float), stream));
     MCB_CUDA(cudaMemcpyAsync(work.ptr, similarity, (size_t)n * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
     // The ranks do not depend on k: computed once (the reference recomputes them every round, knn_graph.py:252).
+    trace_lap("knn: copy similarity", stream);
     MCB_TRY(rank_outgoing_launch(work.as<float>(), n, stream));
+    trace_lap("knn: rank_outgoing", stream);
     std::unique_ptr<PrunedRanks> pruned_holder;
     for (;;) {
         const double max_rank = (double)k * balanced_ranks_factor;                   // knn_graph.py:313
@@ -84,9 +87,11 @@ int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balan
         outgoing = outgoing < n - 1 ? outgoing : n - 1;
         BalancedRanks balanced;
         MCB_TRY(balance_ranks_launch(work.as<float>(), n, shift, &balanced, stream));
+        trace_lap("knn: balance_ranks", stream);
         pruned_holder.reset(new PrunedRanks());
         PrunedRanks& pruned = *pruned_holder;
         MCB_TRY(prune_ranks_launch(balanced, n, incoming, outgoing, &pruned, stream));
+        trace_lap("knn: prune_ranks", stream);
         int32_t min_degree = 0;
         MCB_TRY(weigh_edges_launch(pruned.data.as<float>(), pruned.indptr.as<int32_t>(), n, nullptr, &min_degree, stream));
         if (min_degree >= min_outgoing_degree)
@@ -100,6 +105,7 @@ int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balan
     graph->stream = stream;
     MCB_TRY(graph->weights.alloc((size_t)pruned.nnz * sizeof(float), stream));
     MCB_TRY(weigh_edges_launch(pruned.data.as<float>(), pruned.indptr.as<int32_t>(), n, graph->weights.as<float>(), nullptr, stream));
+    trace_lap("knn: weigh_edges", stream);
     std::swap(graph->ranks.ptr, pruned.data.ptr);
     std::swap(graph->ranks.stream, pruned.data.stream);
     std::swap(graph->indices.ptr, pruned.indices.ptr);

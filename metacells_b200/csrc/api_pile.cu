@@ -126,6 +126,7 @@ int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t fe
         MCB_REQUIRE(slot[feature_genes[f]] < 0, "pile: feature gene %d listed twice", feature_genes[f]);
         slot[feature_genes[f]] = (int32_t)f;
     }
+    trace_lap("similarity: enter", stream);
     Scratch d_slot, d_table, d_dense, d_flag;
     MCB_TRY(d_slot.alloc((size_t)pile->genes * sizeof(int32_t), stream));
     MCB_TRY(d_table.alloc((size_t)table_size * sizeof(float), stream));
@@ -137,8 +138,10 @@ int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t fe
     const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     MCB_TRY(log_fraction_dense_launch(values, pile->indices, pile->indptr, pile->cells, d_slot.as<int32_t>(), features,
                                       d_table.as<float>(), table_size, regularization, d_dense.as<float>(), d_flag.as<int>(), stream));
+    trace_lap("similarity: log_fraction", stream);
     MCB_TRY(mcb_dev_correlate_dense_f32(d_dense.as<float>(), pile->cells, features, features, similarity_dev, pile->cells, absolute,
                                         stream));
+    trace_lap("similarity: correlate", stream);
     int flag = 0;
     MCB_CUDA(cudaMemcpyAsync(&flag, d_flag.ptr, sizeof(int), cudaMemcpyDeviceToHost, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));

@@ -54,6 +54,10 @@ int fail(int code, const char* format, ...);
             return ::mcb::fail(MCB_ERR_ARG, __VA_ARGS__); \
     } while (0)
 
+// Once per device: keep freed scratch in the stream-ordered pool instead of returning it to the
+// driver at every synchronisation (the default release threshold is 0).
+int prepare_memory_pool();
+
 // Device scratch that frees itself on the stream it was allocated on (stream-ordered pool).
 struct Scratch {
     void* ptr = nullptr;
@@ -63,6 +67,7 @@ struct Scratch {
     Scratch& operator=(const Scratch&) = delete;
     int alloc(size_t bytes, cudaStream_t s) {
         stream = s;
+        MCB_TRY(::mcb::prepare_memory_pool());
         MCB_CUDA(cudaMallocAsync(&ptr, bytes ? bytes : 16, s));
         return MCB_OK;
     }
@@ -77,6 +82,9 @@ struct Scratch {
 };
 
 int sm_count();
+// Developer aid: with MCB_TRACE=1 in the environment, synchronises `stream` and prints the host time
+// since the previous call on stderr.
+void trace_lap(const char* name, cudaStream_t stream);
 void count_launch();
 
 // Optional per-kernel timing (mcb_profile_enable): CUDA events around a launch on its own stream.

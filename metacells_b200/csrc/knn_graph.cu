@@ -426,8 +426,10 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     MCB_TRY(row_data.alloc((size_t)in_nnz * sizeof(float), stream));
     MCB_TRY(row_indices.alloc((size_t)in_nnz * sizeof(int32_t), stream));
     MCB_TRY(row_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
+    trace_lap("prune: incoming", stream);
     MCB_TRY(relayout_launch(in_data.as<float>(), in_indices.as<int32_t>(), in_indptr.as<int32_t>(), n, n, in_nnz,
                             row_data.as<float>(), row_indices.as<int32_t>(), row_indptr.as<int32_t>(), stream));
+    trace_lap("prune: relayout", stream);
     // (3) knn_graph.py:380: keep the best `outgoing_degree` per row
     Scratch out_data, out_indices, out_indptr;
     MCB_TRY(out_data.alloc((size_t)in_nnz * sizeof(float), stream));
@@ -435,6 +437,7 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     MCB_TRY(out_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
     MCB_TRY(collect_pruned_launch(outgoing_degree, row_data.as<float>(), row_indices.as<int32_t>(), row_indptr.as<int32_t>(), n,
                                   out_data.as<float>(), out_indices.as<int32_t>(), out_indptr.as<int32_t>(), stream));
+    trace_lap("prune: outgoing", stream);
     // (4) knn_graph.py:383-388: maximum with the preserved edges and their transpose
     Scratch reverse_counts, reverse_ptr, reverse_cursor, reverse_list, sizes;
     MCB_TRY(reverse_counts.alloc((size_t)n * sizeof(int32_t), stream));

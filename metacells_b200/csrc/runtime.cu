@@ -1,6 +1,8 @@
 // Library runtime: error reporting, device selection and cached device properties.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -45,6 +47,32 @@ struct ProfileRecord {
 std::mutex g_profile_mutex;
 std::vector<ProfileRecord> g_records;
 }  // namespace
+
+int prepare_memory_pool() {
+    static std::atomic<unsigned long long> prepared{0};  // bit per device
+    int device = 0;
+    MCB_CUDA(cudaGetDevice(&device));
+    const unsigned long long bit = 1ull << (device & 63);
+    if (prepared.load(std::memory_order_relaxed) & bit)
+        return MCB_OK;
+    cudaMemPool_t pool;
+    MCB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    unsigned long long threshold = ~0ull;
+    MCB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+    prepared.fetch_or(bit);
+    return MCB_OK;
+}
+
+void trace_lap(const char* name, cudaStream_t stream) {
+    static const bool enabled = getenv("MCB_TRACE") != nullptr;
+    if (!enabled)
+        return;
+    static thread_local std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
+    cudaStreamSynchronize(stream);
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[mcb trace] %-28s %8.3f ms\n", name, std::chrono::duration<double, std::milli>(now - last).count());
+    last = now;
+}
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
