@@ -17,6 +17,8 @@
 //     shared memory), the leaf count is decremented atomically, and the prefix sum is rebuilt
 //     once per batch with a block scan.
 // The output is original - remaining, so no separate output accumulator is needed.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace mcb {
@@ -183,6 +185,199 @@ __global__ void __launch_bounds__(DS_THREADS) downsample_kernel(DownsampleParams
     }
 }
 
+// ---- warp-per-row kernel -------------------------------------------------------------------------
+//
+// Same sampling process, different bookkeeping: the row's T UMIs are one bit each (gene order), a set
+// bit = drawn.  "The r-th remaining UMI" is the r-th clear bit.  Draws are decoded 32 at a time (one
+// per lane): ranks are rebased to the start of the batch by the backward replay described above
+// (31 steps over shuffles instead of 255 over shared memory), located through the per-word prefix
+// sums of clear bits (binary search + find-n-th-set-bit), marked, and the prefix sums (T / 32 words)
+// are rebuilt by one warp scan.  The result is the population count of every gene's bit range.
+// One warp owns a row end to end, no block barriers; rows are handed out through an atomic counter.
+
+constexpr int DW_WARPS = 8;
+
+// Largest row total of the rows that will actually be sampled (sizes the per-warp bitmap).
+__global__ void __launch_bounds__(256) max_row_total_kernel(DownsampleParams p, unsigned long long* __restrict__ result) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= p.rows)
+        return;
+    const int64_t lo = p.indptr ? (int64_t)p.indptr[row] : row * p.columns;
+    const int64_t hi = p.indptr ? (int64_t)p.indptr[row + 1] : lo + p.columns;
+    const int32_t samples = p.samples ? p.samples[row] : p.samples_all;
+    unsigned long long total = 0;
+    for (int64_t i = lo + lane; i < hi; i += 32) total += (uint32_t)p.input[i];
+    for (int offset = 16; offset > 0; offset >>= 1) total += __shfl_xor_sync(0xffffffffu, total, offset);
+    if (lane == 0 && samples >= 0 && total > (unsigned long long)samples)
+        atomicMax(result, total);
+}
+
+struct WarpDownsampleParams {
+    DownsampleParams base;
+    int words_capacity;           // bitmap words per warp that fit shared memory
+    unsigned long long* next_row; // dynamic row counter
+};
+
+// x * y mod (2^31 - 1) for x, y < 2^31 - 1, by Mersenne folding.
+__device__ __forceinline__ uint32_t mulmod_mersenne(uint32_t x, uint32_t y) {
+    const uint64_t product = (uint64_t)x * (uint64_t)y;
+    uint32_t folded = (uint32_t)(product & MINSTD_M) + (uint32_t)(product >> 31);
+    folded = (folded & MINSTD_M) + (folded >> 31);
+    return folded >= MINSTD_M ? folded - MINSTD_M : folded;
+}
+
+// Position of the (n + 1)-th set bit of `mask` (n < popc(mask)).
+__device__ __forceinline__ int nth_set_bit(uint32_t mask, int n) {
+    int position = 0;
+#pragma unroll
+    for (int width = 16; width > 0; width >>= 1) {
+        const int low = __popc(mask & ((1u << width) - 1u));
+        if (n >= low) {
+            n -= low;
+            mask >>= width;
+            position += width;
+        }
+    }
+    return position;
+}
+
+__global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDownsampleParams wp) {
+    extern __shared__ uint32_t smem[];
+    const DownsampleParams& p = wp.base;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* bitmap = smem + (size_t)warp * 2 * wp.words_capacity;  // bit set = UMI drawn (or padding)
+    uint32_t* free_before = bitmap + wp.words_capacity;              // clear bits in words [0, w)
+
+    // a^(lane+1) and a^32
+    uint32_t pow_lane = 1, pow_warp = 1;
+    {
+        uint32_t base = MINSTD_A;
+        for (int e = lane + 1; e; e >>= 1) {
+            if (e & 1)
+                pow_lane = mulmod_mersenne(pow_lane, base);
+            base = mulmod_mersenne(base, base);
+        }
+        pow_warp = __shfl_sync(0xffffffffu, pow_lane, 31);
+    }
+
+    for (;;) {
+        unsigned long long claimed = 0;
+        if (lane == 0)
+            claimed = atomicAdd(wp.next_row, 1ull);
+        const int64_t row = (int64_t)__shfl_sync(0xffffffffu, claimed, 0);
+        if (row >= p.rows)
+            break;
+        const int64_t lo = p.indptr ? (int64_t)p.indptr[row] : row * p.columns;
+        const int64_t hi = p.indptr ? (int64_t)p.indptr[row + 1] : lo + p.columns;
+        const int n = (int)(hi - lo);
+        const int32_t samples = p.samples ? p.samples[row] : p.samples_all;
+        const float* in = p.input + lo;
+        float* out = p.output + lo;
+        if (samples < 0 || n == 0)
+            continue;  // downsample.cpp:86-88
+        if (n == 1) {  // downsample.cpp:90-93
+            if (lane == 0)
+                out[0] = (double)samples < (double)in[0] ? (float)samples : in[0];
+            continue;
+        }
+        unsigned long long total64 = 0;
+        for (int i = lane; i < n; i += 32) total64 += (uint32_t)in[i];
+        for (int offset = 16; offset > 0; offset >>= 1) total64 += __shfl_xor_sync(0xffffffffu, total64, offset);
+        if (total64 <= (unsigned long long)samples) {  // downsample.cpp:100-105
+            if (out != in)
+                for (int i = lane; i < n; i += 32) out[i] = in[i];
+            continue;
+        }
+        const int words = (int)((total64 + 31) >> 5);
+        if (total64 >= 0xffffffffull || words > wp.words_capacity) {
+            if (lane == 0)
+                atomicExch(p.error_flag, total64 >= 0xffffffffull ? 2 : 3);
+            continue;
+        }
+        const uint32_t total = (uint32_t)total64;
+        const int per_lane = (words + 31) >> 5;  // consecutive words owned by a lane in the scans
+
+        for (int w = lane; w < words; w += 32) bitmap[w] = 0;
+        __syncwarp();
+        if (lane == 0 && (total & 31u))
+            bitmap[words - 1] = ~0u << (total & 31u);  // padding bits count as drawn
+        __syncwarp();
+
+        uint64_t row_seed = p.seed;
+        if (p.use_row_seed)
+            row_seed = p.seed == 0 ? 0 : p.seed + (uint64_t)row * 997ull;
+        uint32_t state = (uint32_t)(row_seed % MINSTD_M);
+        if (state == 0)
+            state = 1;
+
+        for (int first = 0; first < samples; first += 32) {
+            // prefix sums of clear bits per word
+            {
+                const int begin = min(lane * per_lane, words), end = min(begin + per_lane, words);
+                int sum = 0;
+                for (int w = begin; w < end; ++w) sum += __popc(~bitmap[w]);
+                int running = warp_inclusive_scan(sum, lane) - sum;
+                for (int w = begin; w < end; ++w) {
+                    free_before[w] = (uint32_t)running;
+                    running += __popc(~bitmap[w]);
+                }
+            }
+            __syncwarp();
+            const int draw = first + lane;
+            const bool active = draw < samples;
+            uint32_t r = 0;
+            if (active)
+                r = mulmod_mersenne(state, pow_lane) % (total - (uint32_t)draw);  // downsample.cpp:111
+            state = mulmod_mersenne(state, pow_warp);
+            // rank among the UMIs left at the start of the batch
+            uint32_t q = r;
+#pragma unroll
+            for (int j = 30; j >= 0; --j) {
+                const uint32_t earlier = __shfl_sync(0xffffffffu, r, j);
+                q += (j < lane && earlier <= q) ? 1u : 0u;
+            }
+            if (active) {
+                int left = 0, right = words - 1;  // last word with free_before[w] <= q
+                while (left < right) {
+                    const int middle = (left + right + 1) >> 1;
+                    if (free_before[middle] <= q)
+                        left = middle;
+                    else
+                        right = middle - 1;
+                }
+                const int bit = nth_set_bit(~bitmap[left], (int)(q - free_before[left]));
+                atomicOr(&bitmap[left], 1u << bit);
+            }
+            __syncwarp();
+        }
+        if (lane == 0 && (total & 31u))
+            bitmap[words - 1] &= ~(~0u << (total & 31u));  // drop the padding again
+        __syncwarp();
+
+        // output: drawn UMIs of every gene = set bits in its range
+        uint32_t running = 0;
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + lane;
+            const uint32_t count = i < n ? (uint32_t)in[i] : 0u;
+            const uint32_t inclusive = (uint32_t)warp_inclusive_scan((int)count, lane);
+            uint32_t begin = running + inclusive - count, end = begin + count;
+            running += __shfl_sync(0xffffffffu, inclusive, 31);
+            uint32_t drawn = 0;
+            while (begin < end) {
+                const uint32_t w = begin >> 5, offset = begin & 31u;
+                const uint32_t take = min(32u - offset, end - begin);
+                const uint32_t mask = (take == 32u ? ~0u : ((1u << take) - 1u)) << offset;
+                drawn += __popc(bitmap[w] & mask);
+                begin += take;
+            }
+            if (i < n)
+                out[i] = (float)drawn;
+        }
+        __syncwarp();
+    }
+}
+
 }  // namespace
 
 int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
@@ -201,6 +396,45 @@ int downsample_launch(const float* input, float* output, const int32_t* indptr, 
     p.seed = seed;
     p.use_row_seed = use_row_seed;
 
+    Scratch workspace, flag, counters;
+    MCB_TRY(flag.alloc(sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(flag.ptr, 0, sizeof(int), stream));
+    p.error_flag = flag.as<int>();
+
+    // Preferred: one warp per row over a bitmap of the row's UMIs, when the largest row fits shared memory.
+    MCB_TRY(counters.alloc(2 * sizeof(unsigned long long), stream));
+    MCB_CUDA(cudaMemsetAsync(counters.ptr, 0, 2 * sizeof(unsigned long long), stream));
+    MCB_PROFILED("downsample_totals", stream,
+                 max_row_total_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(p, counters.as<unsigned long long>()));
+    MCB_LAUNCH_CHECK();
+    unsigned long long max_total = 0;
+    MCB_CUDA(cudaMemcpyAsync(&max_total, counters.ptr, sizeof(max_total), cudaMemcpyDeviceToHost, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    if (max_total == 0) {
+        // nothing to sample: every row is copied (or left untouched); the warp kernel does that too
+        max_total = 1;
+    }
+    const unsigned long long max_words = (max_total + 31) / 32;
+    if (max_words <= 28 * 1024) {
+        int capacity = 64;
+        while ((unsigned long long)capacity < max_words) capacity *= 2;
+        int warps = DW_WARPS;
+        while (warps > 1 && (size_t)warps * 2 * capacity * sizeof(uint32_t) > 200 * 1024) warps /= 2;
+        const size_t smem_bytes = (size_t)warps * 2 * capacity * sizeof(uint32_t);
+        WarpDownsampleParams wp{};
+        wp.base = p;
+        wp.words_capacity = capacity;
+        wp.next_row = counters.as<unsigned long long>() + 1;
+        int per_sm = (int)std::min<size_t>(16, (220 * 1024) / (smem_bytes + 1024));
+        per_sm = std::max(1, std::min(per_sm, 2048 / (warps * 32)));
+        const int64_t grid = std::min<int64_t>(ceil_div(rows, warps), (int64_t)sm_count() * per_sm);
+        MCB_CUDA(cudaFuncSetAttribute(downsample_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        MCB_PROFILED("downsample", stream, downsample_warp_kernel<<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
+        MCB_LAUNCH_CHECK();
+        return MCB_OK;
+    }
+
+    // Fallback for rows of more than ~900k UMIs: one CTA per row over per-gene counts.
     // Shared-memory capacity classes: 8 B per element; smaller classes allow more CTAs per SM.
     int smem_capacity = 2048;
     while (smem_capacity < max_row_size && smem_capacity < 24576) smem_capacity *= 2;
@@ -210,10 +444,6 @@ int downsample_launch(const float* input, float* output, const int32_t* indptr, 
     const size_t smem_bytes = (size_t)smem_capacity * 8;
 
     int64_t grid = rows;
-    Scratch workspace, flag;
-    MCB_TRY(flag.alloc(sizeof(int), stream));
-    MCB_CUDA(cudaMemsetAsync(flag.ptr, 0, sizeof(int), stream));
-    p.error_flag = flag.as<int>();
     if (max_row_size > smem_capacity) {
         grid = rows < (int64_t)sm_count() * 2 ? rows : (int64_t)sm_count() * 2;
         p.capacity = max_row_size;

@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(RM_THREADS, 1) rank_matrix_kernel(RankMatrixPa
             // (1) per-warp digit counts over this warp's segment of the current order
             for (int base = seg_begin; base < seg_end; base += 32) {
                 const int i = base + lane;
-                uint32_t digit = 0xffffffffu;
+                uint32_t digit = 0;
                 if (i < seg_end) {
                     uint32_t key;
                     if (pass == 0) {
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(RM_THREADS, 1) rank_matrix_kernel(RankMatrixPa
                     }
                     digit = (key >> shift) & 255u;
                 }
-                const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+                const uint32_t peers = warp_peers_8bit(digit, i < seg_end);
                 if (i < seg_end && (peers & lower_lanes) == 0)
                     my_hist[digit] += __popc(peers);
                 __syncwarp();
@@ -103,13 +103,13 @@ __global__ void __launch_bounds__(RM_THREADS, 1) rank_matrix_kernel(RankMatrixPa
             // (3) stable scatter
             for (int base = seg_begin; base < seg_end; base += 32) {
                 const int i = base + lane;
-                uint32_t digit = 0xffffffffu;
+                uint32_t digit = 0;
                 uint32_t position = 0;
                 if (i < seg_end) {
                     position = pass == 0 ? (uint32_t)i : (uint32_t)source[i];
                     digit = (keys[position] >> shift) & 255u;
                 }
-                const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+                const uint32_t peers = warp_peers_8bit(digit, i < seg_end);
                 uint32_t slot = 0;
                 if (i < seg_end)
                     slot = my_hist[digit] + __popc(peers & lower_lanes);

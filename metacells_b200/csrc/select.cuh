@@ -17,6 +17,20 @@ __device__ __forceinline__ uint32_t sort_key(float value, bool ascending) {
     return ascending ? key : ~key;
 }
 
+// The lanes of the warp whose (valid) 8-bit digit equals this lane's: eight ballots.  MATCH.ANY gives
+// the same mask in one instruction, but its latency grows with the number of distinct values in the
+// warp (~230 cycles for random digits, measured with ncu on B200), which made it the bottleneck.
+__device__ __forceinline__ uint32_t warp_peers_8bit(uint32_t digit, bool valid) {
+    uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (digit >> b) & 1u;
+        const uint32_t ballot = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? ballot : ~ballot;
+    }
+    return peers;
+}
+
 // Shared state of one block-wide radix select.
 struct SelectState {
     int hist[256];
@@ -43,14 +57,15 @@ __device__ uint32_t block_radix_select(KeyAt key_at, int n, int rank, SelectStat
         const int rounds = (n + (int)blockDim.x - 1) / (int)blockDim.x;
         for (int round = 0; round < rounds; ++round) {
             const int i = round * (int)blockDim.x + tid;
-            uint32_t digit = 0xffffffffu;
+            uint32_t digit = 0;
+            bool valid = false;
             if (i < n) {
                 const uint32_t key = key_at(i);
-                if ((key & known_mask) == prefix)
-                    digit = (key >> shift) & 255u;
+                valid = (key & known_mask) == prefix;
+                digit = (key >> shift) & 255u;
             }
-            const uint32_t peers = __match_any_sync(0xffffffffu, digit);
-            if (digit != 0xffffffffu && (peers & lower_lanes) == 0)
+            const uint32_t peers = warp_peers_8bit(digit, valid);
+            if (valid && (peers & lower_lanes) == 0)
                 atomicAdd(&state->hist[digit], __popc(peers));
         }
         __syncthreads();
