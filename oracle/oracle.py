@@ -22,11 +22,12 @@ _lib: Optional[ctypes.CDLL] = None
 
 
 def build(force: bool = False) -> str:
-    """Compile mc_oracle.c with gcc (seconds).  Building the checker is not using it."""
-    src = os.path.join(_HERE, "mc_oracle.c")
-    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+    """Compile mc_oracle.c + mc_partitions.c with gcc (seconds).  Building the checker is not using it."""
+    sources = [os.path.join(_HERE, name) for name in ("mc_oracle.c", "mc_partitions.c")]
+    newest = max(os.path.getmtime(src) for src in sources)
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < newest:
         cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
-        subprocess.check_call([cc, "-O2", "-fPIC", "-shared", "-o", _LIB_PATH, src, "-lm"])
+        subprocess.check_call([cc, "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", _LIB_PATH, *sources, "-lm"])
     return _LIB_PATH
 
 
@@ -277,6 +278,76 @@ def knn_graph(sim: np.ndarray, k: int, balanced_ranks_factor: float = float(np.s
             break
         k += max(1, int(k / 10))
     return weigh_edges(pruned), pruned, balanced, k
+
+
+# ---------------------------------------------------------------------------------------------
+# partitions.cpp (mc_partitions.c)
+# ---------------------------------------------------------------------------------------------
+
+
+class ReferenceAssert(RuntimeError):
+    """A FastAssert of the reference failed (the reference would print it and exit(1))."""
+
+
+def _partition_args(outgoing: sp.csr_matrix, incoming: sp.csc_matrix):
+    assert outgoing.shape[0] == outgoing.shape[1] == incoming.shape[0] == incoming.shape[1]
+    return (_p(outgoing.data, "float32"), _p(outgoing.indices, "int32"), _p(outgoing.indptr, "int32"),
+            _p(incoming.data, "float32"), _p(incoming.indices, "int32"), _p(incoming.indptr, "int32"), _i64(outgoing.shape[0]))
+
+
+def optimize_partitions(outgoing: sp.csr_matrix, incoming: sp.csc_matrix, random_seed: int, mass_of_nodes: np.ndarray,
+                        low_mass: float, target_mass: float, high_mass: float, low_size: float, target_size: float,
+                        high_size: float, cooldown_pass: float, cooldown_node: float, partition_of_nodes: np.ndarray,
+                        hot_partitions_mask: np.ndarray, cold_temperature: float, stats: Optional[np.ndarray] = None) -> float:
+    """partitions.cpp:1234-1302; ``partition_of_nodes`` is modified in place, the score is returned.
+    ``stats`` (int64[4], optional) receives passes / improve_node calls / moves / skipped visits."""
+    bounds = np.array([low_mass, target_mass, high_mass, low_size, target_size, high_size], dtype="float64")
+    score = ctypes.c_double()
+    if stats is not None:
+        stats[:] = 0
+    function = lib().mco_optimize_partitions
+    function.restype = ctypes.c_int
+    status = function(*_partition_args(outgoing, incoming), ctypes.c_uint32(random_seed % (1 << 32)),
+                      _p(mass_of_nodes, "float32"), _p(bounds, "float64"), ctypes.c_double(cooldown_pass),
+                      ctypes.c_double(cooldown_node), _p(partition_of_nodes, "int32"), _p(hot_partitions_mask, "int8"),
+                      ctypes.c_double(cold_temperature), ctypes.byref(score),
+                      _p(stats, "int64") if stats is not None else ctypes.c_void_p())
+    if status == 2:
+        raise ReferenceAssert("optimize_partitions: a FastAssert of the reference fails on this input")
+    _check(status)
+    return score.value
+
+
+def score_partitions(outgoing: sp.csr_matrix, incoming: sp.csc_matrix, mass_of_nodes: np.ndarray, low_mass: float,
+                     target_mass: float, high_mass: float, low_size: float, target_size: float, high_size: float,
+                     partition_of_nodes: np.ndarray, hot_partitions_mask: np.ndarray, with_orphans: bool = True) -> float:
+    """partitions.cpp:1304-1338."""
+    bounds = np.array([low_mass, target_mass, high_mass, low_size, target_size, high_size], dtype="float64")
+    score = ctypes.c_double()
+    function = lib().mco_score_partitions
+    function.restype = ctypes.c_int
+    status = function(*_partition_args(outgoing, incoming), _p(mass_of_nodes, "float32"), _p(bounds, "float64"),
+                      _p(partition_of_nodes, "int32"), _p(hot_partitions_mask, "int8"), ctypes.c_int(int(with_orphans)),
+                      ctypes.byref(score))
+    if status == 2:
+        raise ReferenceAssert("score_partitions: a FastAssert of the reference fails on this input")
+    _check(status)
+    return score.value
+
+
+def glibc_log(values: np.ndarray) -> np.ndarray:
+    """libm's double ``log`` (what extensions.h:135-138 calls), element by element."""
+    values = np.ascontiguousarray(values, dtype="float64")
+    out = np.empty_like(values)
+    lib().mco_log_array(_p(values, "float64"), _p(out, "float64"), _i64(values.size))
+    return out
+
+
+def std_shuffle(count: int, seed: int, rounds: int = 1) -> np.ndarray:
+    """``std::shuffle`` of ``iota(count)`` with ``std::minstd_rand(seed)``, applied ``rounds`` times (libstdc++ 13)."""
+    indices = np.arange(count, dtype="int64")
+    lib().mco_shuffle(_p(indices, "int64"), _i64(count), ctypes.c_uint32(seed), _i64(rounds))
+    return indices
 
 
 # ---------------------------------------------------------------------------------------------
