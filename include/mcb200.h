@@ -193,6 +193,52 @@ int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t fea
                        int* outside_table, mcb_graph** out);
 void mcb_pile_free(mcb_pile* pile);
 
+/* ---- partitions.cpp ----------------------------------------------------------------------------- */
+
+/* optimize_partitions (partitions.cpp:1234-1302; bound as xt.optimize_partitions, tools/candidates.py:853-873).
+ * The graph is given twice, as outgoing CSR and incoming CSC (float32 data, sorted int32 indices, int32
+ * indptr of nodes + 1 entries); mass_of_nodes float32[nodes]; partition_of_nodes int32[nodes] holds the
+ * initial partition (every index >= 0, no empty partition) and receives the optimised one;
+ * hot_partitions_mask int8[mask_count >= partitions], 0 = the nodes of that partition start at
+ * cold_temperature.  *score receives the value the reference returns.  Bit-identical to the reference
+ * for a given random_seed (std::minstd_rand / std::shuffle / glibc log are reproduced).  Where the
+ * reference's FastAssert would exit(1), returns MCB_ERR_ARG with the assert's text in mcb_last_error().
+ * stats (nullable, int64[8], host): passes, improve_node calls, moves, skipped visits, batches, 0, 0, 0.
+ * At most 65535 nodes. */
+int mcb_host_optimize_partitions(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
+                                 const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,
+                                 int64_t nodes, uint32_t random_seed, const float* mass_of_nodes, double low_mass,
+                                 double target_mass, double high_mass, double low_size, double target_size, double high_size,
+                                 double cooldown_pass, double cooldown_node, int32_t* partition_of_nodes,
+                                 const int8_t* hot_partitions_mask, int64_t mask_count, double cold_temperature, int64_t* stats,
+                                 double* score);
+/* As above on device arrays (score and stats stay host pointers); synchronises the stream. */
+int mcb_dev_optimize_partitions(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
+                                const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,
+                                int64_t nodes, uint32_t random_seed, const float* mass_of_nodes, double low_mass,
+                                double target_mass, double high_mass, double low_size, double target_size, double high_size,
+                                double cooldown_pass, double cooldown_node, int32_t* partition_of_nodes,
+                                const int8_t* hot_partitions_mask, int64_t mask_count, double cold_temperature, int64_t* stats,
+                                double* score, void* stream);
+
+/* score_partitions (partitions.cpp:1304-1338, the 16-argument C++ signature). */
+int mcb_host_score_partitions(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
+                              const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,
+                              int64_t nodes, const float* mass_of_nodes, double low_mass, double target_mass, double high_mass,
+                              double low_size, double target_size, double high_size, const int32_t* partition_of_nodes,
+                              const int8_t* hot_partitions_mask, int64_t mask_count, int with_orphans, double* score);
+int mcb_dev_score_partitions(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
+                             const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,
+                             int64_t nodes, const float* mass_of_nodes, double low_mass, double target_mass, double high_mass,
+                             double low_size, double target_size, double high_size, const int32_t* partition_of_nodes,
+                             const int8_t* hot_partitions_mask, int64_t mask_count, int with_orphans, double* score,
+                             void* stream);
+
+/* The double-precision log the scores are built from: glibc 2.39's log() (extensions.h:135-138 calls libm),
+ * evaluated on the device bit for bit (csrc/glibc_log.cuh).  Host arrays; exported so the parity tests
+ * can pin it against libm. */
+int mcb_host_glibc_log_f64(const double* values, double* logs, int64_t count);
+
 /* @@APPEND@@ */
 
 #ifdef __cplusplus

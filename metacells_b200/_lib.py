@@ -49,6 +49,7 @@ _CTYPES: Dict[str, object] = {
     "i64": ctypes.c_int64,
     "u64": ctypes.c_uint64,
     "i32": ctypes.c_int32,
+    "u32": ctypes.c_uint32,
     "int": ctypes.c_int,
     "f32": ctypes.c_float,
     "f64": ctypes.c_double,

@@ -186,4 +186,66 @@ def sort_compressed_indices_float32_t_int32_t_int32_t(data, indices, indptr, ele
          host_ptr(indices, "int32", "indices", True), host_ptr(indptr, "int32", "indptr"), ("i64", len(indptr) - 1))
 
 
+# ---- partitions.cpp ---------------------------------------------------------------------------
+
+#: Filled by every ``optimize_partitions`` call: passes, improve_node calls, moves, skipped visits, batches.
+last_optimize_stats = np.zeros(8, dtype="int64")
+
+
+def _graph_arguments(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices, incoming_indptr):
+    nodes = len(outgoing_indptr) - 1
+    if len(incoming_indptr) - 1 != nodes:
+        raise ValueError("outgoing and incoming graphs have different node counts")
+    if len(outgoing_weights) != len(outgoing_indices) or len(outgoing_weights) != int(outgoing_indptr[-1]):
+        raise ValueError("outgoing data / indices / indptr sizes disagree")
+    if len(incoming_weights) != len(incoming_indices) or len(incoming_weights) != int(incoming_indptr[-1]):
+        raise ValueError("incoming data / indices / indptr sizes disagree")
+    return nodes, [host_ptr(outgoing_weights, "float32", "outgoing_weights"), host_ptr(outgoing_indices, "int32", "outgoing_indices"),
+                   host_ptr(outgoing_indptr, "int32", "outgoing_indptr"), host_ptr(incoming_weights, "float32", "incoming_weights"),
+                   host_ptr(incoming_indices, "int32", "incoming_indices"), host_ptr(incoming_indptr, "int32", "incoming_indptr"),
+                   ("i64", nodes)]
+
+
+def optimize_partitions(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices, incoming_indptr,
+                        random_seed, mass_of_nodes, low_mass, target_mass, high_mass, low_size, target_size, high_size,
+                        cooldown_pass, cooldown_node, partition_of_nodes, hot_partitions_mask, cold_temperature):
+    """partitions.cpp:1234-1302 (called at tools/candidates.py:853-873): ``partition_of_nodes`` is optimised in
+    place, the score is returned."""
+    nodes, graph = _graph_arguments(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices,
+                                    incoming_indptr)
+    if len(mass_of_nodes) != nodes or len(partition_of_nodes) != nodes:
+        raise ValueError("mass_of_nodes / partition_of_nodes must have one entry per node")
+    return call_f64("mcb_host_optimize_partitions", *graph, ("u32", int(random_seed) % (1 << 32)),
+                    host_ptr(mass_of_nodes, "float32", "mass_of_nodes"), ("f64", low_mass), ("f64", target_mass),
+                    ("f64", high_mass), ("f64", low_size), ("f64", target_size), ("f64", high_size), ("f64", cooldown_pass),
+                    ("f64", cooldown_node), host_ptr(partition_of_nodes, "int32", "partition_of_nodes", True),
+                    host_ptr(hot_partitions_mask, "int8", "hot_partitions_mask"), ("i64", len(hot_partitions_mask)),
+                    ("f64", cold_temperature), host_ptr(last_optimize_stats, "int64", "stats", True))
+
+
+def score_partitions(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices, incoming_indptr,
+                     mass_of_nodes, low_mass, target_mass, high_mass, low_size, target_size, high_size, partition_of_nodes,
+                     hot_partitions_mask, with_orphans):
+    """partitions.cpp:1304-1338 (the 16-argument C++ signature; the reference's Python caller at
+    tools/candidates.py:923-941 passes a 17th, which pybind11 rejects: SURVEY.md 8(c) quirk iii)."""
+    nodes, graph = _graph_arguments(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices,
+                                    incoming_indptr)
+    if len(mass_of_nodes) != nodes or len(partition_of_nodes) != nodes:
+        raise ValueError("mass_of_nodes / partition_of_nodes must have one entry per node")
+    return call_f64("mcb_host_score_partitions", *graph, host_ptr(mass_of_nodes, "float32", "mass_of_nodes"),
+                    ("f64", low_mass), ("f64", target_mass), ("f64", high_mass), ("f64", low_size), ("f64", target_size),
+                    ("f64", high_size), host_ptr(partition_of_nodes, "int32", "partition_of_nodes"),
+                    host_ptr(hot_partitions_mask, "int8", "hot_partitions_mask"), ("i64", len(hot_partitions_mask)),
+                    ("int", int(bool(with_orphans))))
+
+
+def glibc_log(values):
+    """glibc's double ``log`` evaluated on the device (what the partition scores are built from)."""
+    values = np.ascontiguousarray(values, dtype="float64")
+    logs = np.empty_like(values)
+    call("mcb_host_glibc_log_f64", host_ptr(values, "float64", "values"), host_ptr(logs, "float64", "logs", True),
+         ("i64", values.size))
+    return logs
+
+
 # @@APPEND@@

@@ -18,7 +18,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from oracle import oracle  # noqa: E402
-from synth import synth_umis  # noqa: E402
+from synth import metacell_bounds, random_partition_graph, seeds_count_for, synth_umis  # noqa: E402
 
 SEED = 123456
 
@@ -110,6 +110,46 @@ def main() -> None:
     np.fill_diagonal(work, work.min() - 1)
     ref.rank_matrix_float32_t(work, False)
     np.savez_compressed(os.path.join(HERE, "knn.npz"), similarity=sim, outgoing_ranks=work)
+    # ---- partitions.cpp: a small pile's graph, seeds from the reference's choose_seeds, then the reference's
+    # optimize_partitions / score_partitions for several seeds, hot masks and cold temperatures ------------
+    umis = synth_umis(600, 3000, seed=SEED)
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    outgoing = oracle.cpu_pile_knn_graph(umis, 400, 20, SEED, ref=ref)
+    outgoing.sort_indices()
+    incoming = sp.csc_matrix(outgoing)
+    incoming.sort_indices()
+    bounds = metacell_bounds(48, 48 * float(np.median(cell_umis)))
+    seeds = np.full(600, -1, dtype="int32")
+    seeds_count = ref.choose_seeds(outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices,
+                                   incoming.indptr, SEED, seeds_count_for(float(cell_umis.sum()), 600, bounds), 0.8, 1.0, seeds)
+    cases = {}
+    hot_all = np.ones(max(seeds_count, 2), dtype="int8")
+    hot_some = hot_all.copy()
+    hot_some[::3] = 0
+    for name, (seed, mask, cold, cooldown_pass, cooldown_node) in {
+        "a": (SEED, hot_all, 0.98, 0.02, 0.25), "b": (1, hot_some, 0.5, 0.02, 0.25), "c": (0, hot_all, 1.0, 0.1, 0.0),
+    }.items():
+        partition = seeds.copy()
+        score = ref.optimize_partitions(outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices,
+                                        incoming.indptr, seed, cell_umis, *bounds, cooldown_pass, cooldown_node, partition, mask,
+                                        cold)
+        scored = ref.score_partitions(outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices,
+                                      incoming.indptr, cell_umis, *bounds, partition, mask, False)
+        cases[f"{name}_params"] = np.array([seed, cold, cooldown_pass, cooldown_node], dtype="float64")
+        cases[f"{name}_mask"] = mask
+        cases[f"{name}_partition"] = partition
+        cases[f"{name}_scores"] = np.array([score, scored], dtype="float64")
+    np.savez_compressed(os.path.join(HERE, "partitions.npz"), data=outgoing.data, indices=outgoing.indices, indptr=outgoing.indptr,
+                        cell_umis=cell_umis, bounds=np.array(bounds), seeds=seeds, **cases)
+
+    # a random clustered graph with two partitions only (the hot_mask of the reference's caller has >= 2 entries)
+    outgoing, incoming, masses, initial = random_partition_graph(300, 12, 2, SEED)
+    bounds = (30000.0, 400000.0, 600000.0, 20.0, 150.0, 250.0)
+    partition = initial.copy()
+    mask = np.ones(2, dtype="int8")
+    score = ref.optimize_partitions(outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices,
+                                    incoming.indptr, 7, masses, *bounds, 0.05, 0.25, partition, mask, 0.95)
+    np.savez_compressed(os.path.join(HERE, "partitions_two.npz"), partition=partition, score=np.array([score]))
     print("golden fixtures written to", HERE)
 
 
