@@ -203,7 +203,8 @@ void mcb_pile_free(mcb_pile* pile);
  * cold_temperature.  *score receives the value the reference returns.  Bit-identical to the reference
  * for a given random_seed (std::minstd_rand / std::shuffle / glibc log are reproduced).  Where the
  * reference's FastAssert would exit(1), returns MCB_ERR_ARG with the assert's text in mcb_last_error().
- * stats (nullable, int64[8], host): passes, improve_node calls, moves, skipped visits, batches, 0, 0, 0.
+ * stats (nullable, int64[16], host): passes, improve_node calls, moves, skipped visits, batches, 0, 0, 0,
+ * then SM-cycle counters of the phases (diagnostics).
  * At most 65535 nodes. */
 int mcb_host_optimize_partitions(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
                                  const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,

@@ -40,6 +40,14 @@ constexpr int OPT_THREADS = 512;                 // 16 warps: the speculation de
 constexpr int OPT_MAX_WARPS = OPT_THREADS / 32;
 constexpr unsigned FULL = 0xffffffffu;
 
+// One merged neighbour of a node: the other node, the weight of node -> other (0 if absent) and of other -> node.
+struct alignas(16) Neighbour {
+    int32_t node;
+    float outgoing;
+    float incoming;
+    int32_t unused;
+};
+
 struct alignas(32) Entry {
     double outgoing;
     double incoming;
@@ -123,8 +131,7 @@ __global__ void partition_range_kernel(const int32_t* __restrict__ partition_of_
 __global__ void build_union_kernel(const float* __restrict__ out_w, const int32_t* __restrict__ out_idx,
                                    const int32_t* __restrict__ out_ptr, const float* __restrict__ in_w,
                                    const int32_t* __restrict__ in_idx, const int32_t* __restrict__ in_ptr, int nodes,
-                                   int32_t* __restrict__ union_idx, float* __restrict__ union_out,
-                                   float* __restrict__ union_in, int32_t* __restrict__ union_count) {
+                                   Neighbour* __restrict__ neighbours, int32_t* __restrict__ union_count) {
     const int node = blockIdx.x * blockDim.x + threadIdx.x;
     if (node >= nodes) return;
     int o = out_ptr[node], i = in_ptr[node];
@@ -136,9 +143,7 @@ __global__ void build_union_kernel(const float* __restrict__ out_w, const int32_
         const int i_node = i < i_end ? in_idx[i] : nodes;
         const int other = min(o_node, i_node);
         const bool is_out = o_node == other, is_in = i_node == other;
-        union_idx[at] = other;
-        union_out[at] = is_out ? out_w[o] : 0.0f;
-        union_in[at] = is_in ? in_w[i] : 0.0f;
+        neighbours[at] = Neighbour{other, is_out ? out_w[o] : 0.0f, is_in ? in_w[i] : 0.0f, 0};
         ++at;
         o += is_out;
         i += is_in;
@@ -276,9 +281,7 @@ __global__ void score_kernel(int nodes, int partitions, const double* incoming_l
 // ---------------------------------------------------------------------------------------------------------
 
 struct OptParams {
-    const int32_t* union_idx;
-    const float* union_out;
-    const float* union_in;
+    const Neighbour* neighbours;
     const int32_t* union_count;
     const int32_t* out_ptr;
     const int32_t* in_ptr;
@@ -301,6 +304,8 @@ struct OptParams {
     uint32_t seed;
     double* result;
     long long* stats;  // [0] passes [1] improve_node calls [2] moves [3] skipped visits [4] batches [5] error
+                       // [8..13] SM cycles of thread 0: pass set-up, evaluation (to the barrier), choice, move, and of
+                       // warp 0 inside evaluate_node: the partition scan + neighbours, the candidate scan
 };
 
 struct Control {
@@ -311,6 +316,7 @@ struct Control {
     int did_improve, did_skip;
     int mover_node, mover_from, mover_to;
     int error;
+    long long cycles_neighbours, cycles_candidates;
     int flags[OPT_MAX_WARPS];
     int counts[OPT_MAX_WARPS];
     int scan[34];
@@ -333,7 +339,10 @@ struct WarpBuffers {
     double* total;   // tmp_partition_hot_diffs until the candidate scan, then tmp_partition_total_diffs
     int32_t* linked; // connectivity diff + 65536 * disconnected diff (both small integers in the reference's doubles)
     uint16_t* list;  // the (aliased) candidate list, in partition order
+    double* staging; // one chunk of neighbour diffs, 32 doubles
+    long long* cycles;  // warp 0 only: {scan + neighbours, candidates}
 };
+constexpr int EVAL_UNROLL = 4;
 
 __device__ __forceinline__ uint32_t rng_next(uint32_t& state) {
     state = uint32_t((uint64_t(state) * 48271u) % 2147483647u);
@@ -411,11 +420,13 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
     const int partitions = P.partitions;
     const int current = P.partition_of_nodes[node];
     if (S.sizes[current] < 2) return 0;  // :575
+    const long long entered = clock64();
     const Entry* row = P.table + int64_t(node) * partitions;
     const Entry current_entry = row[current];
     const int current_connectivity = connectivity(current_entry.outgoing, current_entry.incoming);
 
     // :647-662 and :699-723
+#pragma unroll 4
     for (int p = lane; p < partitions; p += 32) {
         const Entry entry = row[p];
         if (p == current) {
@@ -435,50 +446,70 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
     __syncwarp();
 
     // :725-802: every neighbour (merged list, ascending) re-scored as if the node had left `current` / joined the
-    // neighbour's partition; the cold diffs of one partition are added in neighbour order.
+    // neighbour's partition; the cold diffs of one partition are added in neighbour order.  EVAL_UNROLL chunks of 32
+    // neighbours are loaded and re-scored together (the two dependent gathers and the log are latency, not work).
     const int64_t base = int64_t(P.out_ptr[node]) + P.in_ptr[node];
     const int count = P.union_count[node];
-    for (int start = 0; start < count; start += 32) {
-        const int e = start + lane;
-        int q = -1 - lane;  // lanes past the end: a private group each
-        double diff = 0.0;
-        int linked = 0;
-        if (e < count) {
-            const int other = P.union_idx[base + e];
-            const double outgoing_weight = P.union_out[base + e];  // node -> other: other's incoming total
-            const double incoming_weight = P.union_in[base + e];   // other -> node: other's outgoing total
-            const Entry score = P.self[other];
-            q = int(score.partition);
-            const double direction = q == current ? -1.0 : 1.0;
-            const int old_connectivity = connectivity(score.outgoing, score.incoming);
-            const double incoming = clamp0(dadd(score.incoming, dmul(direction, outgoing_weight)));
-            const double outgoing = clamp0(dadd(score.outgoing, dmul(direction, incoming_weight)));
-            const int new_connectivity = connectivity(outgoing, incoming);
-            diff = dsub(rescore(outgoing, incoming, t), score.score);
-            linked = new_connectivity - old_connectivity;
-            if (old_connectivity == 0 && new_connectivity > 0) linked -= 65536;
-            if (old_connectivity > 0 && new_connectivity == 0) linked += 65536;
+    Neighbour ahead[EVAL_UNROLL];
+#pragma unroll
+    for (int j = 0; j < EVAL_UNROLL; ++j) {
+        const int e = j * 32 + lane;
+        ahead[j] = P.neighbours[base + (e < count ? e : 0)];
+    }
+    for (int start = 0; start < count; start += 32 * EVAL_UNROLL) {
+        float outgoing_weight[EVAL_UNROLL], incoming_weight[EVAL_UNROLL];
+        Entry score[EVAL_UNROLL];
+#pragma unroll
+        for (int j = 0; j < EVAL_UNROLL; ++j) {
+            score[j] = P.self[ahead[j].node];
+            outgoing_weight[j] = ahead[j].outgoing;  // node -> other: other's incoming total
+            incoming_weight[j] = ahead[j].incoming;  // other -> node: other's outgoing total
         }
-        const unsigned peers = __match_any_sync(FULL, q);
-        const int linked_sum = __reduce_add_sync(peers, linked);
-        const bool leader = q >= 0 && lane == __ffs(peers) - 1;
-        double chain = leader ? B.cold[q] : 0.0;
-        unsigned rest = leader ? peers : 0u;
-        while (__any_sync(FULL, rest != 0u)) {
-            const int source = rest ? __ffs(rest) - 1 : lane;
-            const double term = __shfl_sync(FULL, diff, source);
-            if (rest) {
-                chain = dadd(chain, term);
-                rest &= rest - 1;
+        if (start + 32 * EVAL_UNROLL < count) {  // the next group's neighbours, in flight during this group's work
+#pragma unroll
+            for (int j = 0; j < EVAL_UNROLL; ++j) {
+                const int e = start + 32 * EVAL_UNROLL + j * 32 + lane;
+                ahead[j] = P.neighbours[base + (e < count ? e : 0)];
             }
         }
-        if (leader) {
-            B.cold[q] = chain;
-            B.linked[q] += linked_sum;
+        int q[EVAL_UNROLL], linked[EVAL_UNROLL];
+        double diff[EVAL_UNROLL];
+#pragma unroll
+        for (int j = 0; j < EVAL_UNROLL; ++j) {
+            q[j] = int(score[j].partition);
+            const double direction = q[j] == current ? -1.0 : 1.0;
+            const int old_connectivity = connectivity(score[j].outgoing, score[j].incoming);
+            const double incoming = clamp0(dadd(score[j].incoming, dmul(direction, double(outgoing_weight[j]))));
+            const double outgoing = clamp0(dadd(score[j].outgoing, dmul(direction, double(incoming_weight[j]))));
+            const int new_connectivity = connectivity(outgoing, incoming);
+            diff[j] = dsub(rescore(outgoing, incoming, t), score[j].score);
+            linked[j] = new_connectivity - old_connectivity;
+            if (old_connectivity == 0 && new_connectivity > 0) linked[j] -= 65536;
+            if (old_connectivity > 0 && new_connectivity == 0) linked[j] += 65536;
+            if (start + j * 32 + lane >= count) {  // lanes past the end: a private group each, nothing to add
+                q[j] = -1 - lane;
+                linked[j] = 0;
+            }
         }
-        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < EVAL_UNROLL; ++j) {
+            if (start + j * 32 >= count) break;
+            const unsigned peers = __match_any_sync(FULL, q[j]);
+            if (linked[j] != 0) atomicAdd(&B.linked[q[j]], linked[j]);  // integers: any order; rarely non-zero
+            B.staging[lane] = diff[j];
+            __syncwarp();
+            if (q[j] >= 0 && lane == __ffs(peers) - 1) {  // the first lane of a partition adds its terms in lane order
+                double chain = B.cold[q[j]];
+#pragma unroll 8
+                for (int source = 0; source < 32; ++source)
+                    if (peers >> source & 1u) chain = dadd(chain, B.staging[source]);
+                B.cold[q[j]] = chain;
+            }
+            __syncwarp();
+        }
     }
 
+    const long long scanned = clock64();
     // :815-876, the partition the node would leave
     const double node_mass = P.mass_of_nodes[node];
     const double current_hot_diff = B.total[current];
@@ -499,33 +530,52 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
     const double cooled = dsub(1.0, temperature);
     __syncwarp();
 
-    // :880-1002; all three push_back sites feed the one aliased list
-    int candidates = 0;
+    // :880-1002; all three push_back sites feed the one aliased list.  First the partitions that pass the two
+    // connectivity filters (:950-957; few: a node is linked to a handful of partitions), in partition order ...
+    int admissible = 0;
     for (int first = 0; first < partitions; first += 32) {
         const int p = first + lane;
-        bool candidate = false;
+        bool passes = false;
         if (p < partitions && p != current) {
             const int linked = B.linked[p];
             const int connectivity_diff = int16_t(linked & 0xffff);
             const int disconnected_diff = (linked - connectivity_diff) >> 16;
-            if (disconnected_diff + current_disconnected_diff <= 0 &&
-                connectivity_diff + current_connectivity_diff >= min_connectivity_diff) {
-                const double grown = double(S.sizes[p] + 1);
-                const double by_mass = mass_factor(dadd(S.masses[p], node_mass), P.bounds.low_mass, P.bounds.target_mass, P.bounds.high_mass, t);
-                double adjusted = dsub(dadd(S.scores[p], B.cold[p]), S.grown_log[p]);
-                adjusted = dadd(adjusted, dmul(grown, min_like_std(by_mass, S.grown_factor[p])));
-                const double adjusted_cold_diff = dsub(adjusted, S.old_adjusted[p]);
-                const double total_diff = dadd(dmul(dadd(current_hot_diff, B.total[p]), temperature),
-                                               dmul(dadd(current_adjusted_cold_diff, adjusted_cold_diff), cooled));
-                B.total[p] = total_diff;
-                candidate = total_diff >= EPSILON || min_connectivity_diff > 0;
-            }
+            passes = disconnected_diff + current_disconnected_diff <= 0 &&
+                     connectivity_diff + current_connectivity_diff >= min_connectivity_diff;
+        }
+        const unsigned mask = __ballot_sync(FULL, passes);
+        if (passes) B.list[admissible + __popc(mask & ((1u << lane) - 1u))] = uint16_t(p);
+        admissible += __popc(mask);
+    }
+    __syncwarp();
+    // ... then their total diffs (a log each), keeping those that are candidates (compacted in place, in order).
+    int candidates = 0;
+    for (int first = 0; first < admissible; first += 32) {
+        const int i = first + lane;
+        bool candidate = false;
+        int p = 0;
+        if (i < admissible) {
+            p = B.list[i];
+            const double grown = double(S.sizes[p] + 1);
+            const double by_mass = mass_factor(dadd(S.masses[p], node_mass), P.bounds.low_mass, P.bounds.target_mass, P.bounds.high_mass, t);
+            double adjusted = dsub(dadd(S.scores[p], B.cold[p]), S.grown_log[p]);
+            adjusted = dadd(adjusted, dmul(grown, min_like_std(by_mass, S.grown_factor[p])));
+            const double adjusted_cold_diff = dsub(adjusted, S.old_adjusted[p]);
+            const double total_diff = dadd(dmul(dadd(current_hot_diff, B.total[p]), temperature),
+                                           dmul(dadd(current_adjusted_cold_diff, adjusted_cold_diff), cooled));
+            B.total[p] = total_diff;
+            candidate = total_diff >= EPSILON || min_connectivity_diff > 0;
         }
         const unsigned mask = __ballot_sync(FULL, candidate);
+        __syncwarp();
         if (candidate) B.list[candidates + __popc(mask & ((1u << lane) - 1u))] = uint16_t(p);
         candidates += __popc(mask);
     }
     __syncwarp();
+    if (B.cycles && lane == 0) {
+        B.cycles[0] += scanned - entered;
+        B.cycles[1] += clock64() - scanned;
+    }
     return candidates;
 }
 
@@ -559,9 +609,10 @@ __device__ void apply_move(const OptParams& P, const PartitionState& S, const Lo
     const int64_t base = int64_t(P.out_ptr[node]) + P.in_ptr[node];
     const int count = P.union_count[node];
     for (int e = threadIdx.x; e < count; e += blockDim.x) {
-        const int other = P.union_idx[base + e];
-        const double outgoing_weight = P.union_out[base + e];
-        const double incoming_weight = P.union_in[base + e];
+        const Neighbour neighbour = P.neighbours[base + e];
+        const int other = neighbour.node;
+        const double outgoing_weight = neighbour.outgoing;
+        const double incoming_weight = neighbour.incoming;
         Entry* row = P.table + int64_t(other) * partitions;
         Entry left = row[from];
         left.incoming = clamp0(dsub(left.incoming, outgoing_weight));
@@ -604,7 +655,7 @@ __host__ __device__ inline size_t align_up(size_t value, size_t to) { return (va
 
 // Shared memory: Control | log tables | 6 per-partition vectors | max(warps x WarpBuffers, uint16 order[N]).
 __host__ __device__ inline size_t partition_state_bytes(int padded) { return size_t(padded) * (4 + 5 * 8); }
-__host__ __device__ inline size_t warp_buffer_bytes(int padded) { return size_t(padded) * (8 + 8 + 4 + 2); }
+__host__ __device__ inline size_t warp_buffer_bytes(int padded) { return size_t(padded) * (8 + 8 + 4 + 2) + 256; }
 __host__ __device__ inline size_t fixed_shared_bytes(int padded) {
     return align_up(sizeof(Control), 16) + LOG_TABLE_WORDS * 8 + align_up(partition_state_bytes(padded), 16);
 }
@@ -626,7 +677,9 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
     WarpBuffers B;
     {
         unsigned char* mine = region + size_t(warp < P.warps ? warp : 0) * warp_buffer_bytes(P.padded);
-        B.cold = reinterpret_cast<double*>(mine);
+        B.cycles = warp == 0 ? &control->cycles_neighbours : nullptr;
+        B.staging = reinterpret_cast<double*>(mine);
+        B.cold = B.staging + 32;
         B.total = B.cold + P.padded;
         B.linked = reinterpret_cast<int32_t*>(B.total + P.padded);
         B.list = reinterpret_cast<uint16_t*>(B.linked + P.padded);
@@ -647,6 +700,8 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
         control->did_improve = 1;
         control->did_skip = 0;
         control->error = 0;
+        control->cycles_neighbours = 0;
+        control->cycles_candidates = 0;
     }
     __syncthreads();
     for (int p = threadIdx.x; p < P.partitions; p += blockDim.x) refresh_partition(S, p, P.bounds, t);
@@ -655,6 +710,7 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
     const double cooldown_rate = dsub(1.0, ddiv(P.cooldown_pass, double(nodes)));  // :443
     const double node_cooling = dsub(1.0, P.cooldown_node);                        // :521
     long long passes = 0, visits = 0, moves = 0, skipped_visits = 0, batches = 0;
+    long long cycles_setup = 0, cycles_evaluate = 0, cycles_choose = 0, cycles_move = 0;
 
     while (true) {
         __syncthreads();
@@ -680,6 +736,7 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
             temperature = 0.0;
         }
         ++passes;
+        long long mark = clock64();
 
         // :480 the visiting order (one thread: the swaps form a chain), and beside it the temperature of every
         // visit (:485, a chain of products).
@@ -717,9 +774,11 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
         if (active_count < nodes) did_skip = 1;
         skipped_visits += nodes - active_count;
         __syncthreads();
+        cycles_setup += clock64() - mark;
 
         for (int done = 0; done < active_count;) {
             const int limit = min(P.warps, active_count - done);
+            mark = clock64();
             int node = -1;
             double visit = 0.0;
             if (warp < limit) {
@@ -733,6 +792,8 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
                 }
             }
             __syncthreads();
+            cycles_evaluate += clock64() - mark;
+            mark = clock64();
             int mover = limit;
             for (int w = 0; w < limit; ++w)
                 if (control->flags[w]) {
@@ -760,6 +821,8 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
                     }
                 }
                 __syncthreads();
+                cycles_choose += clock64() - mark;
+                mark = clock64();
                 if (control->mover_to >= 0)
                     apply_move(P, S, t, control->mover_node, control->mover_from, control->mover_to, control->cold_from,
                                control->cold_to);
@@ -768,6 +831,8 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
                 visits += mover + 1;
                 done += mover + 1;
                 if (control->mover_to < 0) done = active_count;
+                __syncthreads();
+                cycles_move += clock64() - mark;
             } else {
                 visits += limit;
                 done += limit;
@@ -793,6 +858,8 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
         if (P.stats) {
             P.stats[0] = passes; P.stats[1] = visits; P.stats[2] = moves; P.stats[3] = skipped_visits;
             P.stats[4] = batches; P.stats[5] = control->error;
+            P.stats[8] = cycles_setup; P.stats[9] = cycles_evaluate; P.stats[10] = cycles_choose; P.stats[11] = cycles_move;
+            P.stats[12] = control->cycles_neighbours; P.stats[13] = control->cycles_candidates;
         }
     }
 }
@@ -848,14 +915,12 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
     const int warps = int(std::min<size_t>(OPT_MAX_WARPS, (shared_limit - fixed) / warp_buffer_bytes(padded)));
     const size_t shared_bytes = fixed + std::max(size_t(warps) * warp_buffer_bytes(padded), size_t(n) * 2);
 
-    Scratch table, self, union_idx, union_out, union_in, union_count, incoming_log2, sizes, masses, scores, temperatures, frozen,
+    Scratch table, self, neighbours, union_count, incoming_log2, sizes, masses, scores, temperatures, frozen,
         order, visit_temperature, active, result, stats_device;
     const int64_t entries = int64_t(n) * partitions;
     MCB_TRY(table.alloc(size_t(entries) * sizeof(Entry), stream));
     MCB_TRY(self.alloc(size_t(n) * sizeof(Entry), stream));
-    MCB_TRY(union_idx.alloc(size_t(union_capacity) * 4, stream));
-    MCB_TRY(union_out.alloc(size_t(union_capacity) * 4, stream));
-    MCB_TRY(union_in.alloc(size_t(union_capacity) * 4, stream));
+    MCB_TRY(neighbours.alloc(size_t(union_capacity) * sizeof(Neighbour), stream));
     MCB_TRY(union_count.alloc(size_t(n) * 4, stream));
     MCB_TRY(incoming_log2.alloc(size_t(n) * 8, stream));
     MCB_TRY(sizes.alloc(size_t(padded) * 4, stream));
@@ -867,14 +932,13 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
     MCB_TRY(visit_temperature.alloc(size_t(n) * 8, stream));
     MCB_TRY(active.alloc(size_t(n) * 4, stream));
     MCB_TRY(result.alloc(8, stream));
-    MCB_TRY(stats_device.alloc(8 * sizeof(long long), stream));
-    MCB_CUDA(cudaMemsetAsync(stats_device.ptr, 0, 8 * sizeof(long long), stream));
+    MCB_TRY(stats_device.alloc(16 * sizeof(long long), stream));
+    MCB_CUDA(cudaMemsetAsync(stats_device.ptr, 0, 16 * sizeof(long long), stream));
 
     const int node_blocks = int(ceil_div(n, 128));
     const int wide_blocks = int(std::min<int64_t>(ceil_div(entries, 256), int64_t(sm_count()) * 8));
     MCB_PROFILED("build_union", stream, build_union_kernel<<<node_blocks, 128, 0, stream>>>(
-                     out_w, out_idx, out_ptr, in_w, in_idx, in_ptr, n, union_idx.as<int32_t>(), union_out.as<float>(),
-                     union_in.as<float>(), union_count.as<int32_t>()));
+                     out_w, out_idx, out_ptr, in_w, in_idx, in_ptr, n, neighbours.as<Neighbour>(), union_count.as<int32_t>()));
     MCB_LAUNCH_CHECK();
     MCB_PROFILED("clear_table", stream, clear_table_kernel<<<wide_blocks, 256, 0, stream>>>(table.as<Entry>(), entries));
     MCB_LAUNCH_CHECK();
@@ -900,9 +964,7 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
                          temperatures.as<double>(), frozen.as<uint8_t>(), order.as<int32_t>()));
         MCB_LAUNCH_CHECK();
         OptParams params;
-        params.union_idx = union_idx.as<int32_t>();
-        params.union_out = union_out.as<float>();
-        params.union_in = union_in.as<float>();
+        params.neighbours = neighbours.as<Neighbour>();
         params.union_count = union_count.as<int32_t>();
         params.out_ptr = out_ptr;
         params.in_ptr = in_ptr;
@@ -939,13 +1001,13 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
                          scores.as<double>(), bounds, with_orphans, result.as<double>()));
         MCB_LAUNCH_CHECK();
     }
-    long long stats_host[8];
+    long long stats_host[16];
     MCB_CUDA(cudaMemcpyAsync(score, result.ptr, 8, cudaMemcpyDeviceToHost, stream));
     MCB_CUDA(cudaMemcpyAsync(stats_host, stats_device.ptr, sizeof(stats_host), cudaMemcpyDeviceToHost, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     MCB_REQUIRE(stats_host[5] == 0, "failed assert: no candidate partition was chosen (partitions.cpp:1071)");
     if (stats)
-        for (int i = 0; i < 8; ++i) stats[i] = stats_host[i];
+        for (int i = 0; i < 16; ++i) stats[i] = stats_host[i];
     return MCB_OK;
 }
 

@@ -189,7 +189,7 @@ def sort_compressed_indices_float32_t_int32_t_int32_t(data, indices, indptr, ele
 # ---- partitions.cpp ---------------------------------------------------------------------------
 
 #: Filled by every ``optimize_partitions`` call: passes, improve_node calls, moves, skipped visits, batches.
-last_optimize_stats = np.zeros(8, dtype="int64")
+last_optimize_stats = np.zeros(16, dtype="int64")
 
 
 def _graph_arguments(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices, incoming_indptr):
