@@ -28,7 +28,8 @@ def _similarity(cells, seed, ties=True):
 
 
 @pytest.mark.parametrize("shape,ascending", [((1, 1), True), ((3, 2), False), ((7, 33), True), ((40, 1000), False),
-                                             ((5, 16384), False), ((3, 24000), False), ((2, 30000), True)])
+                                             ((5, 4096), True), ((4, 4097), False), ((3, 8192), False), ((3, 8193), True),
+                                             ((5, 16384), False), ((2, 16385), True), ((3, 24000), False), ((2, 30000), True)])
 def test_rank_matrix_matches_oracle(shape, ascending):
     rng = np.random.default_rng(shape[1])
     matrix = rng.normal(size=shape).astype("float32")
