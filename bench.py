@@ -173,7 +173,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "stage_seconds_per_step": {name: seconds / max(args.steps, 1) for name, seconds in timings.items()},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---- GPU arm ---------------------------------------------------------------------------------------------
@@ -363,7 +363,7 @@ def run_gpu_arm(args):
         start = time.perf_counter()
         cpu_cells = step()
         line["cpu_baseline"] = dict(info, value=cpu_cells / (time.perf_counter() - start), unit=UNIT)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -375,7 +375,25 @@ def umma_traffic(cells, features):
     return None
 
 
+_RESULT_FD = None
+
+
+def emit(line):
+    """The one JSON line of the contract, on the process's real stdout."""
+    text = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(text.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, text)
+
+
 def main():
+    global _RESULT_FD
+    # Libraries print on stdout (NCCL's version banner, for one): keep fd 1 for the JSON line only.
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
