@@ -89,6 +89,14 @@ int mcb_host_cross_correlate_dense_f64(const double* first, int64_t first_rows, 
 int mcb_dev_cross_correlate_dense_f32(const float* first, int64_t first_rows, const float* second, int64_t second_rows,
                                       int64_t columns, float* output, int64_t out_stride, void* stream);
 
+/* One block of rows of the similarity matrix of `all_rows` (tools/similarity.py:210-215 + computation.py:465-466):
+ * output[i, j] = r(rows_block[i, :], all_rows[j, :]) (|r| when absolute != 0), NaN -> 0, and 1 where
+ * j == first_row + i.  rows_block is all_rows + first_row * columns on the rank that owns the block; used by the
+ * row-block sharded similarity of an oversized pile.  Device pointers. */
+int mcb_dev_similarity_block_f32(const float* rows_block, int64_t block_rows, int64_t first_row, const float* all_rows,
+                                 int64_t all_count, int64_t columns, float* output, int64_t out_stride, int absolute,
+                                 void* stream);
+
 /* pairs_correlate_dense<F>  (correlate.cpp:496-527): output[i] = r(first[i, :], second[i, :]). */
 int mcb_host_pairs_correlate_dense_f32(const float* first, int64_t first_stride, const float* second, int64_t second_stride,
                                        int64_t rows, int64_t columns, float* output);

@@ -75,7 +75,31 @@ int upload_matrix(Scratch& device, const T* host, int64_t rows, int64_t columns,
 
 }  // namespace
 
+namespace {
+// np.fill_diagonal(similarity, 1) (computation.py:466) for a block of rows of the full matrix.
+__global__ void unit_diagonal_kernel(float* __restrict__ block, int64_t rows, int64_t stride, int64_t first_row, int64_t columns) {
+    const int64_t row = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (row < rows && first_row + row < columns) block[row * stride + first_row + row] = 1.0f;
+}
+}  // namespace
+
 extern "C" {
+
+int mcb_dev_similarity_block_f32(const float* rows_block, int64_t block_rows, int64_t first_row, const float* all_rows,
+                                 int64_t all_count, int64_t columns, float* output, int64_t out_stride, int absolute,
+                                 void* stream) {
+    MCB_REQUIRE(block_rows >= 0 && all_count >= 0 && columns >= 0 && out_stride >= all_count && first_row >= 0 &&
+                    first_row + block_rows <= all_count,
+                "similarity_block: bad shape");
+    if (block_rows == 0)
+        return MCB_OK;
+    MCB_TRY(correlate_f32_device(rows_block, block_rows, columns, all_rows, all_count, columns, columns, output, out_stride, 0,
+                                 absolute, (cudaStream_t)stream));
+    unit_diagonal_kernel<<<(unsigned)ceil_div(block_rows, 256), 256, 0, (cudaStream_t)stream>>>(output, block_rows, out_stride,
+                                                                                               first_row, all_count);
+    MCB_LAUNCH_CHECK();
+    return MCB_OK;
+}
 
 int mcb_dev_correlate_dense_f32(const float* input, int64_t rows, int64_t columns, int64_t row_stride, float* output,
                                 int64_t out_stride, int absolute, void* stream) {

@@ -18,7 +18,8 @@ import scipy.sparse as sp
 from . import utilities as ut
 from ._lib import check, host_ptr, lib
 
-__all__ = ["downsample_cells", "compute_obs_obs_similarity", "compute_obs_obs_knn_graph", "KnnGraph"]
+__all__ = ["downsample_cells", "compute_obs_obs_similarity", "compute_obs_obs_similarity_top", "row_block_of_rank",
+           "compute_obs_obs_knn_graph", "KnnGraph"]
 
 # metacells/parameters.py
 DOWNSAMPLE_MIN_SAMPLES = 750
@@ -49,6 +50,88 @@ def compute_obs_obs_similarity(data: np.ndarray, *, method: str = "abs_pearson",
     if method == "abs_pearson":
         np.absolute(similarity, out=similarity)  # similarity.py:214-215
     return similarity
+
+
+def row_block_of_rank(rows_count: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """``[first, last)`` rows of the similarity matrix that ``rank`` computes: contiguous blocks whose sizes
+    differ by at most one (the first ``rows_count % world_size`` ranks take the extra row)."""
+    assert 0 <= rank < world_size
+    base, extra = divmod(rows_count, world_size)
+    first = rank * base + min(rank, extra)
+    return first, first + base + (1 if rank < extra else 0)
+
+
+def similarity_top_block(dense_device, first_row: int, last_row: int, top: int, *, method: str = "abs_pearson", stream=None):
+    """Rows ``[first_row, last_row)`` of ``top_per(similarity, top)`` on the device: the block of the similarity
+    matrix (tensor cores), then per row the ``top`` largest values with ascending column indices
+    (top_per.cpp:5-64).  ``dense_device`` is a CUDA float32 ``torch`` tensor [cells, genes] holding ALL rows.
+    Returns CUDA tensors ``(indices int32 [rows, top], values float32 [rows, top])``."""
+    import torch
+
+    if method not in ("pearson", "abs_pearson"):
+        raise NotImplementedError("only pearson / abs_pearson are on the hot path")
+    cells, genes = dense_device.shape
+    assert dense_device.is_cuda and dense_device.dtype == torch.float32 and dense_device.is_contiguous()
+    assert 0 < top < cells, "top must be in 1..cells-1 (top_per.cpp:81-82)"
+    rows = last_row - first_row
+    handle = ctypes.c_void_p(stream.cuda_stream if stream is not None else torch.cuda.current_stream().cuda_stream)
+    block = torch.empty((rows, cells), dtype=torch.float32, device=dense_device.device)
+    indices = torch.empty((rows, top), dtype=torch.int32, device=dense_device.device)
+    values = torch.empty((rows, top), dtype=torch.float32, device=dense_device.device)
+    if rows == 0:
+        return indices, values
+    library = lib()
+    library.mcb_dev_similarity_block_f32.restype = ctypes.c_int
+    library.mcb_dev_collect_top_f32.restype = ctypes.c_int
+    check(library.mcb_dev_similarity_block_f32(
+        ctypes.c_void_p(dense_device.data_ptr() + first_row * genes * 4), ctypes.c_int64(rows), ctypes.c_int64(first_row),
+        ctypes.c_void_p(dense_device.data_ptr()), ctypes.c_int64(cells), ctypes.c_int64(genes), ctypes.c_void_p(block.data_ptr()),
+        ctypes.c_int64(cells), ctypes.c_int(int(method == "abs_pearson")), handle))
+    check(library.mcb_dev_collect_top_f32(
+        ctypes.c_int64(top), ctypes.c_void_p(block.data_ptr()), ctypes.c_int64(rows), ctypes.c_int64(cells), ctypes.c_int64(cells),
+        ctypes.c_void_p(indices.data_ptr()), ctypes.c_void_p(values.data_ptr()), ctypes.c_int(0), handle))
+    return indices, values
+
+
+def compute_obs_obs_similarity_top(data: np.ndarray, top: int, *, method: str = "abs_pearson", rank: Optional[int] = None,
+                                   world_size: Optional[int] = None) -> sp.csr_matrix:
+    """``compute_obs_obs_similarity(..., top=top)`` (tools/similarity.py:222-238 -> ``ut.top_per``,
+    computation.py:1299-1352) for a pile too large for one GPU's N x N matrices, sharded by row blocks over the
+    ranks of the default ``torch.distributed`` group: every rank holds the whole [cells, genes]
+    operand, computes its block of rows of the similarity on the tensor cores, keeps the ``top`` largest values of
+    each row, and only those (cells x top indices and values) cross NVLink in one NCCL all-gather.  Every rank
+    returns the full CSR matrix (float32 data, sorted int32 indices, ``top`` entries per row)."""
+    import torch
+    import torch.distributed as dist
+
+    if world_size is None:
+        world_size = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+    if rank is None:
+        rank = dist.get_rank() if world_size > 1 else 0
+    dense = np.ascontiguousarray(data, dtype="float32")
+    cells = dense.shape[0]
+    device = torch.device("cuda", torch.cuda.current_device())
+    dense_device = torch.from_numpy(dense).to(device)
+    first_row, last_row = row_block_of_rank(cells, rank, world_size)
+    indices, values = similarity_top_block(dense_device, first_row, last_row, top, method=method)
+    if world_size > 1:
+        widest = row_block_of_rank(cells, 0, world_size)[1]  # rank 0 owns the (or a) widest block
+        padded_indices = torch.zeros((widest, top), dtype=torch.int32, device=device)
+        padded_values = torch.zeros((widest, top), dtype=torch.float32, device=device)
+        padded_indices[: last_row - first_row] = indices
+        padded_values[: last_row - first_row] = values
+        all_indices = torch.empty((world_size, widest, top), dtype=torch.int32, device=device)
+        all_values = torch.empty((world_size, widest, top), dtype=torch.float32, device=device)
+        dist.all_gather_into_tensor(all_indices, padded_indices)
+        dist.all_gather_into_tensor(all_values, padded_values)
+        sizes = [row_block_of_rank(cells, other, world_size) for other in range(world_size)]
+        indices = torch.cat([all_indices[other, : end - start] for other, (start, end) in enumerate(sizes)])
+        values = torch.cat([all_values[other, : end - start] for other, (start, end) in enumerate(sizes)])
+    indptr = np.arange(cells + 1, dtype="int64") * top  # computation.py:1324
+    matrix = sp.csr_matrix((values.cpu().numpy().reshape(-1), indices.cpu().numpy().reshape(-1), indptr), shape=(cells, cells))
+    matrix.has_sorted_indices = True
+    matrix.has_canonical_format = True
+    return matrix
 
 
 class KnnGraph:

@@ -86,3 +86,14 @@ def test_map_piles_world_size_two_gloo():
     alone = map_piles(pile_of_cells, lambda pile, cells: int(cells.size))
     assert [entry["cells"] for entry in first_results] == alone
     assert [entry["rank"] for entry in first_results] == [0 if pile in first_processed else 1 for pile in range(piles_count)]
+
+
+@pytest.mark.parametrize("rows,world", [(10, 3), (2, 4), (16_000, 8), (100_001, 8), (5, 1)])
+def test_row_blocks_cover_the_matrix(rows, world):
+    from metacells_b200.tools import row_block_of_rank
+
+    blocks = [row_block_of_rank(rows, rank, world) for rank in range(world)]
+    assert blocks[0][0] == 0 and blocks[-1][1] == rows
+    assert all(blocks[rank][1] == blocks[rank + 1][0] for rank in range(world - 1))
+    widths = [last - first for first, last in blocks]
+    assert max(widths) - min(widths) <= 1 and widths[0] == max(widths)
