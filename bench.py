@@ -242,17 +242,16 @@ def run_gpu_arm(args):
     result = {"weights": torch.empty(capacity, dtype=torch.float32).pin_memory(),
               "indices": torch.empty(capacity, dtype=torch.int32).pin_memory(),
               "indptr": torch.empty(cells + 1, dtype=torch.int32).pin_memory()}
-    gene_totals = np.empty(genes, dtype="float32")
     stream = torch.cuda.current_stream(device)
 
     def hot_path(pile):
         """The path on an existing pile handle; returns the graph handle."""
         library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
-        library.call("mcb_pile_gene_totals", pile, p(gene_totals.ctypes.data))
-        feature_genes = np.sort(np.argsort(-gene_totals, kind="stable")[:args.features]).astype("int32")
+        # feature genes: the largest downsampled totals (stand-in for pipeline/select.py), selected on the device
+        library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)
         graph = ctypes.c_void_p()
         outside = ctypes.c_int(0)
-        library.call("mcb_pile_knn_graph", pile, p(feature_genes.ctypes.data), ctypes.c_int64(len(feature_genes)),
+        library.call("mcb_pile_knn_graph", pile, None, ctypes.c_int64(args.features),
                      p(table.ctypes.data), ctypes.c_int64(len(table)), ctypes.c_float(np.float32(1 / 7)), ctypes.c_int(1),
                      ctypes.c_int64(k), ctypes.c_double(brf), ctypes.c_double(idf), ctypes.c_double(odf), ctypes.c_int64(mod),
                      ctypes.byref(outside), ctypes.byref(graph))

@@ -188,8 +188,14 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed);
 int mcb_pile_read_downsampled(mcb_pile* pile, float* data); /* nnz values, same structure as the input */
 /* Per-gene totals of the (downsampled, if done) matrix to a host array of `genes` floats. */
 int mcb_pile_gene_totals(mcb_pile* pile, float* totals);
-/* direct.py:242-249 + tools/similarity.py:178-246: dense slice of `feature_genes` (host, ascending
- * gene indices), log2(x + regularization) through `log_table` (host; log_table[c] = np.log2(c +
+/* The `count` genes with the largest (downsampled) totals, equal totals by lower gene index, ascending gene
+ * indices: == np.sort(np.argsort(-totals, kind="stable")[:count]).  The list stays on the device for
+ * mcb_pile_similarity / mcb_pile_knn_graph (pass feature_genes = NULL there); genes_host (nullable) receives a
+ * copy.  A stand-in for pipeline/select.py on synthetic data, computed without leaving the GPU. */
+int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host);
+
+/* direct.py:242-249 + tools/similarity.py:178-246: dense slice of `feature_genes` (host, distinct
+ * gene indices; NULL = the list of mcb_pile_top_genes), log2(x + regularization) through `log_table` (host; log_table[c] = np.log2(c +
  * regularization) for c = 0 .. table_size-1), Pearson (absolute != 0: |r|) into similarity_dev
  * [cells, cells] (device).  *outside_table (host, may be NULL) reports values the table missed. */
 int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,

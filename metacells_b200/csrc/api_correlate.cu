@@ -13,7 +13,7 @@ int pairs_rows_f32(const float* first, const float* second, int64_t rows, int64_
 int pairs_rows_f64(const double* first, const double* second, int64_t rows, int64_t columns, float* output, cudaStream_t stream);
 int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, const float* b_hi, const float* b_lo,
                           int64_t rows_b, int64_t padded, float* output, int64_t out_stride, int symmetric, int absolute,
-                          cudaStream_t stream);
+                          unsigned int* min_key, cudaStream_t stream);
 }  // namespace mcb
 
 using namespace mcb;
@@ -25,7 +25,7 @@ int64_t padded_width(int64_t columns) { return ceil_div(columns > 0 ? columns : 
 // float32 rows -> tcgen05 3xTF32 contraction.
 int correlate_f32_device(const float* first, int64_t first_rows, int64_t first_stride, const float* second,
                          int64_t second_rows, int64_t second_stride, int64_t columns, float* output, int64_t out_stride,
-                         int symmetric, int absolute, cudaStream_t stream) {
+                         int symmetric, int absolute, cudaStream_t stream, unsigned int* min_key = nullptr) {
     const int64_t padded = padded_width(columns);
     Scratch a_hi, a_lo, b_hi, b_lo;
     MCB_TRY(a_hi.alloc((size_t)first_rows * padded * sizeof(float), stream));
@@ -42,7 +42,7 @@ int correlate_f32_device(const float* first, int64_t first_rows, int64_t first_s
         bl = b_lo.as<float>();
     }
     return correlate_umma_launch(a_hi.as<float>(), a_lo.as<float>(), first_rows, bh, bl, symmetric ? first_rows : second_rows,
-                                 padded, output, out_stride, symmetric, absolute, stream);
+                                 padded, output, out_stride, symmetric, absolute, min_key, stream);
 }
 
 // float64 rows -> float64 SIMT contraction (the reference's float64 instantiation is fp64 throughout).
@@ -82,6 +82,18 @@ __global__ void unit_diagonal_kernel(float* __restrict__ block, int64_t rows, in
     if (row < rows && first_row + row < columns) block[row * stride + first_row + row] = 1.0f;
 }
 }  // namespace
+
+namespace mcb {
+// The symmetric similarity of the pile path: as mcb_dev_correlate_dense_f32, and *min_key (device, preset to
+// 0xffffffff) receives the matrix minimum as a float_to_ordered key (fused np.min of knn_graph.py:290).
+int correlate_dense_with_min(const float* input, int64_t rows, int64_t columns, int64_t row_stride, float* output,
+                             int64_t out_stride, int absolute, unsigned int* min_key, cudaStream_t stream) {
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns && out_stride >= rows, "correlate_dense: bad shape");
+    if (rows == 0)
+        return MCB_OK;
+    return correlate_f32_device(input, rows, row_stride, nullptr, 0, 0, columns, output, out_stride, 1, absolute, stream, min_key);
+}
+}  // namespace mcb
 
 extern "C" {
 

@@ -19,7 +19,7 @@ int collect_compressed_launch(const float* data, const int32_t* indices, const i
                               int32_t* out_indices, int32_t* cursor, cudaStream_t stream);
 int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t* indptr, int64_t bands, int64_t widest_band,
                                    cudaStream_t stream);
-int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream);
+int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint32_t* known_min);
 
 struct BalancedRanks {
     Scratch data, indices, indptr, best_index, best_value;
@@ -63,19 +63,26 @@ int to_host(T* host, const Scratch& device, size_t count, cudaStream_t stream) {
 }
 
 // tools/knn_graph.py:251-275: rank, balance, prune; grow k until every row keeps min_outgoing_degree edges.
+// consumed != nullptr: the caller gives its similarity buffer away (ranked in place, no copy) and may pass the
+// matrix minimum it already knows.
 int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor, double incoming_degree_factor,
-                     double outgoing_degree_factor, int64_t min_outgoing_degree, cudaStream_t stream, mcb_graph* graph) {
+                     double outgoing_degree_factor, int64_t min_outgoing_degree, cudaStream_t stream, mcb_graph* graph,
+                     float* consumed = nullptr, const uint32_t* known_min = nullptr) {
     MCB_REQUIRE(n >= 2, "knn_graph: needs at least 2 elements (got %lld)", (long long)n);
     MCB_REQUIRE(k >= 1 && balanced_ranks_factor > 0 && incoming_degree_factor > 0 && outgoing_degree_factor > 0 &&
                     min_outgoing_degree >= 1,
                 "knn_graph: bad parameters");  // knn_graph.py:216-220
     trace_lap("knn: enter", stream);
-    Scratch work;
-    MCB_TRY(work.alloc((size_t)n * n * sizeof(float), stream));
-    MCB_CUDA(cudaMemcpyAsync(work.ptr, similarity, (size_t)n * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    Scratch copy;
+    float* ranks = consumed;
+    if (ranks == nullptr) {
+        MCB_TRY(copy.alloc((size_t)n * n * sizeof(float), stream));
+        MCB_CUDA(cudaMemcpyAsync(copy.ptr, similarity, (size_t)n * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+        ranks = copy.as<float>();
+    }
     // The ranks do not depend on k: computed once (the reference recomputes them every round, knn_graph.py:252).
     trace_lap("knn: copy similarity", stream);
-    MCB_TRY(rank_outgoing_launch(work.as<float>(), n, stream));
+    MCB_TRY(rank_outgoing_launch(ranks, n, stream, known_min));
     trace_lap("knn: rank_outgoing", stream);
     std::unique_ptr<PrunedRanks> pruned_holder;
     for (;;) {
@@ -86,7 +93,7 @@ int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balan
         incoming = incoming < n - 1 ? incoming : n - 1;
         outgoing = outgoing < n - 1 ? outgoing : n - 1;
         BalancedRanks balanced;
-        MCB_TRY(balance_ranks_launch(work.as<float>(), n, shift, &balanced, stream));
+        MCB_TRY(balance_ranks_launch(ranks, n, shift, &balanced, stream));
         trace_lap("knn: balance_ranks", stream);
         pruned_holder.reset(new PrunedRanks());
         PrunedRanks& pruned = *pruned_holder;
@@ -116,6 +123,20 @@ int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balan
 }
 
 }  // namespace
+
+namespace mcb {
+// The pile path: `similarity` (device, n x n) is consumed; known_min as in rank_outgoing_launch.
+int knn_graph_consuming(float* similarity, const uint32_t* known_min, int64_t n, int64_t k, double balanced_ranks_factor,
+                        double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                        cudaStream_t stream, mcb_graph** out) {
+    MCB_REQUIRE(similarity != nullptr && out != nullptr, "knn_graph: null argument");
+    std::unique_ptr<mcb_graph> graph(new mcb_graph());
+    MCB_TRY(knn_graph_device(similarity, n, k, balanced_ranks_factor, incoming_degree_factor, outgoing_degree_factor,
+                             min_outgoing_degree, stream, graph.get(), similarity, known_min));
+    *out = graph.release();
+    return MCB_OK;
+}
+}  // namespace mcb
 
 extern "C" {
 

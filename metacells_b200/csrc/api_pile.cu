@@ -14,6 +14,13 @@ int column_totals_launch(const float* data, const int32_t* indices, int64_t nnz,
 int log_fraction_dense_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t rows,
                               const int32_t* slot_of_gene, int64_t features, const float* table, int64_t table_size,
                               float regularization, float* dense, int* outside_table, cudaStream_t stream);
+int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, int64_t columns, int64_t row_stride,
+                       int32_t* out_indices, float* out_data, int ranks, cudaStream_t stream);
+int correlate_dense_with_min(const float* input, int64_t rows, int64_t columns, int64_t row_stride, float* output,
+                             int64_t out_stride, int absolute, unsigned int* min_key, cudaStream_t stream);
+int knn_graph_consuming(float* similarity, const uint32_t* known_min, int64_t n, int64_t k, double balanced_ranks_factor,
+                        double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
+                        cudaStream_t stream, mcb_graph** out);
 }  // namespace mcb
 
 using namespace mcb;
@@ -28,6 +35,8 @@ struct mcb_pile {
     const int32_t* indptr = nullptr;
     Scratch downsampled;  // same sparsity structure as `data`
     bool has_downsampled = false;
+    Scratch top_genes;    // int32[top_genes_count] ascending, set by mcb_pile_top_genes
+    int64_t top_genes_count = 0;
 };
 
 namespace {
@@ -115,38 +124,100 @@ int mcb_pile_read_downsampled(mcb_pile* pile, float* data) {
     return MCB_OK;
 }
 
-int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
-                        int64_t table_size, float regularization, int absolute, float* similarity_dev, int* outside_table) {
-    MCB_REQUIRE(pile != nullptr && feature_genes && log_table && similarity_dev, "pile: null argument");
+}  // extern "C" (reopened below)
+
+namespace {
+
+__global__ void gene_slots_kernel(const int32_t* __restrict__ feature_genes, int64_t features, int64_t genes,
+                                  int32_t* __restrict__ slot_of_gene, int* __restrict__ bad) {
+    const int64_t f = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (f >= features) return;
+    const int32_t gene = feature_genes[f];
+    if (gene < 0 || gene >= genes) {
+        atomicOr(bad, 1);
+        return;
+    }
+    if (atomicCAS(&slot_of_gene[gene], -1, (int32_t)f) != -1) atomicOr(bad, 2);
+}
+
+// feature_genes: host pointer, or nullptr to use the list mcb_pile_top_genes left on the device.
+// min_key (optional, device uint32 preset to 0xffffffff) receives the minimum of the similarity.
+int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table, int64_t table_size,
+                    float regularization, int absolute, float* similarity_dev, int* outside_table, unsigned int* min_key) {
+    MCB_REQUIRE(pile != nullptr && log_table && similarity_dev, "pile: null argument");
+    if (feature_genes == nullptr) {
+        MCB_REQUIRE(pile->top_genes_count > 0, "pile: no feature genes given and mcb_pile_top_genes was not called");
+        features = pile->top_genes_count;
+    }
     MCB_REQUIRE(features >= 1 && features <= pile->genes, "pile: bad feature genes count %lld", (long long)features);
     cudaStream_t stream = pile->stream;
-    std::vector<int32_t> slot((size_t)pile->genes, -1);
-    for (int64_t f = 0; f < features; ++f) {
-        MCB_REQUIRE(feature_genes[f] >= 0 && feature_genes[f] < pile->genes, "pile: feature gene %d out of range", feature_genes[f]);
-        MCB_REQUIRE(slot[feature_genes[f]] < 0, "pile: feature gene %d listed twice", feature_genes[f]);
-        slot[feature_genes[f]] = (int32_t)f;
-    }
     trace_lap("similarity: enter", stream);
-    Scratch d_slot, d_table, d_dense, d_flag;
+    Scratch d_genes, d_slot, d_table, d_dense, d_flag;
+    const int32_t* genes_device = pile->top_genes.as<int32_t>();
+    if (feature_genes != nullptr) {
+        MCB_TRY(d_genes.alloc((size_t)features * sizeof(int32_t), stream));
+        MCB_CUDA(cudaMemcpyAsync(d_genes.ptr, feature_genes, (size_t)features * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+        genes_device = d_genes.as<int32_t>();
+    }
     MCB_TRY(d_slot.alloc((size_t)pile->genes * sizeof(int32_t), stream));
     MCB_TRY(d_table.alloc((size_t)table_size * sizeof(float), stream));
     MCB_TRY(d_dense.alloc((size_t)pile->cells * features * sizeof(float), stream));
-    MCB_TRY(d_flag.alloc(sizeof(int), stream));
-    MCB_CUDA(cudaMemcpyAsync(d_slot.ptr, slot.data(), (size_t)pile->genes * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(d_flag.alloc(2 * sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(d_slot.ptr, 0xff, (size_t)pile->genes * sizeof(int32_t), stream));
     MCB_CUDA(cudaMemcpyAsync(d_table.ptr, log_table, (size_t)table_size * sizeof(float), cudaMemcpyHostToDevice, stream));
-    MCB_CUDA(cudaMemsetAsync(d_flag.ptr, 0, sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(d_flag.ptr, 0, 2 * sizeof(int), stream));
+    gene_slots_kernel<<<(unsigned)ceil_div(features, 256), 256, 0, stream>>>(genes_device, features, pile->genes,
+                                                                             d_slot.as<int32_t>(), d_flag.as<int>() + 1);
+    MCB_LAUNCH_CHECK();
     const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     MCB_TRY(log_fraction_dense_launch(values, pile->indices, pile->indptr, pile->cells, d_slot.as<int32_t>(), features,
                                       d_table.as<float>(), table_size, regularization, d_dense.as<float>(), d_flag.as<int>(), stream));
     trace_lap("similarity: log_fraction", stream);
-    MCB_TRY(mcb_dev_correlate_dense_f32(d_dense.as<float>(), pile->cells, features, features, similarity_dev, pile->cells, absolute,
-                                        stream));
+    MCB_TRY(correlate_dense_with_min(d_dense.as<float>(), pile->cells, features, features, similarity_dev, pile->cells, absolute,
+                                     min_key, stream));
     trace_lap("similarity: correlate", stream);
-    int flag = 0;
-    MCB_CUDA(cudaMemcpyAsync(&flag, d_flag.ptr, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    int flags[2] = {0, 0};
+    MCB_CUDA(cudaMemcpyAsync(flags, d_flag.ptr, sizeof(flags), cudaMemcpyDeviceToHost, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
+    MCB_REQUIRE((flags[1] & 1) == 0, "pile: a feature gene is out of range");
+    MCB_REQUIRE((flags[1] & 2) == 0, "pile: a feature gene is listed twice");
     if (outside_table)
-        *outside_table = flag;
+        *outside_table = flags[0];
+    return MCB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
+                        int64_t table_size, float regularization, int absolute, float* similarity_dev, int* outside_table) {
+    return pile_similarity(pile, feature_genes, features, log_table, table_size, regularization, absolute, similarity_dev,
+                           outside_table, nullptr);
+}
+
+int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host) {
+    MCB_REQUIRE(pile != nullptr && count >= 1 && count < pile->genes, "pile: top genes count must be in 1..genes-1");
+    cudaStream_t stream = pile->stream;
+    const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
+    Scratch totals, unused;
+    MCB_TRY(totals.alloc((size_t)pile->genes * sizeof(float), stream));
+    MCB_TRY(unused.alloc((size_t)count * sizeof(float), stream));
+    MCB_TRY(column_totals_launch(values, pile->indices, pile->nnz, pile->genes, totals.as<float>(), stream));
+    if (pile->top_genes_count != count) {
+        Scratch fresh;
+        MCB_TRY(fresh.alloc((size_t)count * sizeof(int32_t), stream));
+        std::swap(pile->top_genes.ptr, fresh.ptr);
+        std::swap(pile->top_genes.stream, fresh.stream);
+        pile->top_genes_count = count;
+    }
+    // the `count` largest totals, equal totals by lower gene index, indices ascending: one row of collect_top
+    MCB_TRY(collect_top_launch(count, totals.as<float>(), 1, pile->genes, pile->genes, pile->top_genes.as<int32_t>(),
+                               unused.as<float>(), 0, stream));
+    if (genes_host != nullptr) {
+        MCB_CUDA(cudaMemcpyAsync(genes_host, pile->top_genes.ptr, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        MCB_CUDA(cudaStreamSynchronize(stream));
+    }
     return MCB_OK;
 }
 
@@ -155,12 +226,16 @@ int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t fea
                        double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
                        int* outside_table, mcb_graph** out) {
     MCB_REQUIRE(pile != nullptr && out != nullptr, "pile: null argument");
-    Scratch similarity;
+    // The similarity never leaves this call: its minimum comes out of the correlate epilogue and the ranks
+    // overwrite it in place (the public mcb_dev_knn_graph_f32 must copy and scan its input instead).
+    Scratch similarity, min_key;
     MCB_TRY(similarity.alloc((size_t)pile->cells * pile->cells * sizeof(float), pile->stream));
-    MCB_TRY(mcb_pile_similarity(pile, feature_genes, features, log_table, table_size, regularization, absolute,
-                                similarity.as<float>(), outside_table));
-    return mcb_dev_knn_graph_f32(similarity.as<float>(), pile->cells, k, balanced_ranks_factor, incoming_degree_factor,
-                                 outgoing_degree_factor, min_outgoing_degree, pile->stream, out);
+    MCB_TRY(min_key.alloc(sizeof(unsigned int), pile->stream));
+    MCB_CUDA(cudaMemsetAsync(min_key.ptr, 0xff, sizeof(unsigned int), pile->stream));
+    MCB_TRY(pile_similarity(pile, feature_genes, features, log_table, table_size, regularization, absolute,
+                            similarity.as<float>(), outside_table, min_key.as<unsigned int>()));
+    return knn_graph_consuming(similarity.as<float>(), min_key.as<uint32_t>(), pile->cells, k, balanced_ranks_factor,
+                               incoming_degree_factor, outgoing_degree_factor, min_outgoing_degree, pile->stream, out);
 }
 
 int64_t mcb_pile_nnz(const mcb_pile* pile) { return pile ? pile->nnz : 0; }

@@ -100,6 +100,7 @@ struct UmmaParams {
     int k_blocks;
     int symmetric;  // lower-triangle tiles, mirrored store, unit diagonal
     int absolute;   // store |r|
+    unsigned int* min_key;  // optional: receives min over the stored values, as float_to_ordered keys (atomicMin)
 };
 
 __device__ __forceinline__ float finish(float r, int absolute) {
@@ -204,6 +205,7 @@ __global__ void __launch_bounds__(UMMA_THREADS, 1)
         const int quarter = warp & 3;  // TMEM lanes 32 * quarter .. + 31 are visible to this warp
         const int row_in_tile = quarter * 32 + lane;
         uint32_t chunk_index = 0;
+        float least = __uint_as_float(0x7f800000u);  // min over the values this thread stores (np.min, knn_graph.py:290)
         for (int t = blockIdx.x; t < p.tiles_count; t += gridDim.x) {
             const int2 tile = p.tiles[t];
             float acc[BN];
@@ -245,6 +247,12 @@ __global__ void __launch_bounds__(UMMA_THREADS, 1)
                 acc[c] = r;
             }
             const bool diagonal_tile = p.symmetric && tile.x == tile.y;
+            if (p.min_key != nullptr && row_ok) {
+#pragma unroll
+                for (int c = 0; c < BN; ++c)
+                    if (col0 + c < p.rows_b && (!diagonal_tile || c <= row_in_tile))
+                        least = fminf(least, acc[c]);
+            }
             if (row_ok) {
                 float* out_row = p.output + global_row * p.out_stride + col0;
                 if (diagonal_tile) {
@@ -281,6 +289,12 @@ __global__ void __launch_bounds__(UMMA_THREADS, 1)
                     mirror_at += p.out_stride;
                 }
             }
+        }
+        if (p.min_key != nullptr) {
+            uint32_t key = float_to_ordered(least);
+            for (int offset = 16; offset > 0; offset >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, offset));
+            if (lane == 0)
+                atomicMin(p.min_key, key);
         }
     }
 
@@ -347,7 +361,7 @@ static void tile_order(int64_t tiles_a, int64_t tiles_b, int symmetric, std::vec
 // same arrays for a and b.  output: [rows_a, out_stride >= rows_b].
 int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, const float* b_hi, const float* b_lo,
                           int64_t rows_b, int64_t padded, float* output, int64_t out_stride, int symmetric, int absolute,
-                          cudaStream_t stream) {
+                          unsigned int* min_key, cudaStream_t stream) {
     if (rows_a == 0 || rows_b == 0)
         return MCB_OK;
     MCB_REQUIRE(padded > 0 && padded % BK == 0, "correlate: padded width %lld is not a positive multiple of %d", (long long)padded, BK);
@@ -374,6 +388,7 @@ int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, 
     p.k_blocks = (int)(padded / BK);
     p.symmetric = symmetric;
     p.absolute = absolute;
+    p.min_key = min_key;
     const int grid = (int)std::min<int64_t>((int64_t)order.size(), sm_count());
     MCB_CUDA(cudaFuncSetAttribute(correlate_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UMMA_SMEM));
     MCB_PROFILED("correlate_umma", stream, correlate_umma_kernel<<<(unsigned)grid, UMMA_THREADS, UMMA_SMEM, stream>>>(map_a_hi, map_a_lo, map_b_hi, map_b_lo, p));

@@ -343,16 +343,21 @@ static int read_i32(const int32_t* device, int32_t* host, cudaStream_t stream) {
 }
 
 // knn_graph.py:285-297 (_rank_outgoing) on a private copy: diagonal below the minimum, descending ranks.
-int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream) {
+// known_min (optional, device): the minimum of `work` as a float_to_ordered key, when the producer of the
+// similarity already has it (the correlate epilogue of the pile path); otherwise one more pass over the matrix.
+int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint32_t* known_min) {
     if (n == 0)
         return MCB_OK;
     Scratch min_key;
-    MCB_TRY(min_key.alloc(sizeof(uint32_t), stream));
-    MCB_CUDA(cudaMemsetAsync(min_key.ptr, 0xff, sizeof(uint32_t), stream));
-    MCB_PROFILED("min_matrix", stream, min_matrix_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n * n, 1024), (int64_t)sm_count() * 8), 256, 0, stream>>>(
-        work, n, n, n, min_key.as<uint32_t>()));
-    MCB_LAUNCH_CHECK();
-    fill_diagonal_below_min_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, stream>>>(work, n, n, min_key.as<uint32_t>());
+    if (known_min == nullptr) {
+        MCB_TRY(min_key.alloc(sizeof(uint32_t), stream));
+        MCB_CUDA(cudaMemsetAsync(min_key.ptr, 0xff, sizeof(uint32_t), stream));
+        MCB_PROFILED("min_matrix", stream, min_matrix_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n * n, 1024), (int64_t)sm_count() * 8), 256, 0, stream>>>(
+            work, n, n, n, min_key.as<uint32_t>()));
+        MCB_LAUNCH_CHECK();
+        known_min = min_key.as<uint32_t>();
+    }
+    fill_diagonal_below_min_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, stream>>>(work, n, n, known_min);
     MCB_LAUNCH_CHECK();
     return rank_matrix_launch(work, n, n, n, 0, stream);
 }

@@ -107,7 +107,16 @@ class Pile:
         totals = self.gene_totals()
         return np.sort(np.argsort(-totals, kind="stable")[:features]).astype("int32")
 
-    def knn_graph(self, feature_genes: np.ndarray, *, k: int, method: str = "abs_pearson",
+    def select_top_genes(self, features: int) -> np.ndarray:
+        """As ``top_total_genes``, selected on the device (``mcb_pile_top_genes``); the list also stays there, so
+        ``knn_graph(None, ...)`` uses it without another upload."""
+        genes = np.empty(features, dtype="int32")
+        function = lib().mcb_pile_top_genes
+        function.restype = ctypes.c_int
+        check(function(self._handle, ctypes.c_int64(features), _ptr(genes)))
+        return genes
+
+    def knn_graph(self, feature_genes: Optional[np.ndarray], *, k: int, method: str = "abs_pearson",
                   regularization: float = CELLS_SIMILARITY_VALUE_REGULARIZATION,
                   balanced_ranks_factor: float = tl.KNN_BALANCED_RANKS_FACTOR,
                   incoming_degree_factor: float = tl.KNN_INCOMING_DEGREE_FACTOR,
@@ -116,7 +125,8 @@ class Pile:
         """direct.py:242-283: log-fraction of the feature genes, similarity, balanced k-NN graph."""
         if method not in ("pearson", "abs_pearson"):
             raise NotImplementedError("only pearson / abs_pearson are on the hot path")
-        feature_genes = np.ascontiguousarray(feature_genes, dtype="int32")
+        if feature_genes is not None:
+            feature_genes = np.ascontiguousarray(feature_genes, dtype="int32")
         if max_count is None:
             max_count = int(self.samples if self.samples is not None else self._data.max(initial=0))
         table = log_fraction_table(min(max_count, 1 << 20), regularization)
@@ -124,7 +134,8 @@ class Pile:
         outside = ctypes.c_int(0)
         function = lib().mcb_pile_knn_graph
         function.restype = ctypes.c_int
-        check(function(self._handle, _ptr(feature_genes), ctypes.c_int64(len(feature_genes)), _ptr(table),
+        check(function(self._handle, _ptr(feature_genes) if feature_genes is not None else None,
+                       ctypes.c_int64(len(feature_genes) if feature_genes is not None else 0), _ptr(table),
                        ctypes.c_int64(len(table)), ctypes.c_float(np.float32(regularization)),
                        ctypes.c_int(int(method == "abs_pearson")), ctypes.c_int64(int(k)), ctypes.c_double(balanced_ranks_factor),
                        ctypes.c_double(incoming_degree_factor), ctypes.c_double(outgoing_degree_factor),
@@ -146,9 +157,10 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
         k = knn_k_of_pile(umis.shape[0], cell_umis)
     with Pile(umis) as pile:
         pile.downsample(samples, random_seed)
-        if feature_genes is None:
-            feature_genes = pile.top_total_genes(features)
-        graph = pile.knn_graph(feature_genes, k=k)
+        selected_on_device = feature_genes is None
+        if selected_on_device:
+            feature_genes = pile.select_top_genes(features)
+        graph = pile.knn_graph(None if selected_on_device else feature_genes, k=k)
         try:
             weights, pruned = graph.to_scipy()
             details = {"k": graph.k, "samples": samples, "feature_genes": feature_genes, "pruned_ranks": pruned}

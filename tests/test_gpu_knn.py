@@ -215,3 +215,31 @@ def test_knn_graph_full_pile_properties():
     # every row keeps its best balanced edge, in both directions (knn_graph.py:383-388)
     best = np.asarray(pruned.argmax(axis=1)).reshape(-1)
     assert np.all(np.asarray(pruned[best, np.arange(cells)]).reshape(-1) > 0)
+
+
+def test_pile_feature_genes_selected_on_device():
+    """mcb_pile_top_genes == np.sort(np.argsort(-totals, stable)[:count]) (ties by lower gene index), and the
+    fused pile path (similarity consumed in place, minimum from the correlate epilogue) == the staged one."""
+    from synth import synth_umis
+
+    from metacells_b200 import pipeline, tools as tl
+
+    umis = synth_umis(500, 2500, seed=11)
+    with pipeline.Pile(umis) as pile:
+        pile.downsample(600, 123456)
+        for count in (1, 37, 400, 2499):
+            assert np.array_equal(pile.select_top_genes(count), pile.top_total_genes(count)), count
+        genes = pile.select_top_genes(400)
+        fused = pile.knn_graph(None, k=15)
+        weights, _ = fused.to_scipy()
+        fused.close()
+        staged = pile.knn_graph(genes, k=15)
+        staged_weights, _ = staged.to_scipy()
+        staged.close()
+        down = pile.downsampled()
+    assert np.array_equal(weights.indptr, staged_weights.indptr) and np.array_equal(weights.indices, staged_weights.indices)
+    assert np.array_equal(weights.data, staged_weights.data)
+    dense = oracle.log_fraction(down[:, genes].toarray())
+    similarity = tl.compute_obs_obs_similarity(dense)
+    separate = tl.compute_obs_obs_knn_graph(similarity, k=15)
+    assert np.array_equal(weights.indices, separate.indices) and np.array_equal(weights.data, separate.data)
