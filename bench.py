@@ -60,6 +60,7 @@ def make_pile(cells, genes, seed):
     samples = int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(cell_umis, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
                             np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
     k = pipeline.knn_k_of_pile(cells, cell_umis)
+    make_pile.max_cell_total = int(cell_umis.max())  # the pipeline has the totals (samples and k come from them)
     return umis, samples, k
 
 
@@ -230,6 +231,7 @@ def run_gpu_arm(args):
     device = torch.device("cuda", local_rank)
 
     umis, samples, k = make_pile(args.cells, args.genes, SEED + rank)  # one pile per rank
+    max_cell_total = make_pile.max_cell_total
     cells, genes = umis.shape
     table = pipeline.log_fraction_table(samples)
     brf, idf, odf, mod = tl.KNN_BALANCED_RANKS_FACTOR, tl.KNN_INCOMING_DEGREE_FACTOR, tl.KNN_OUTGOING_DEGREE_FACTOR, tl.KNN_MIN_OUTGOING_DEGREE
@@ -246,6 +248,7 @@ def run_gpu_arm(args):
 
     def hot_path(pile):
         """The path on an existing pile handle; returns the graph handle."""
+        library.call("mcb_pile_set_max_cell_total", pile, ctypes.c_uint64(max_cell_total))
         library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
         # feature genes: the largest downsampled totals (stand-in for pipeline/select.py), selected on the device
         library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)

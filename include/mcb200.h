@@ -176,10 +176,17 @@ void mcb_graph_free(mcb_graph* graph);
 
 /* A pile = the cells x genes UMI matrix (CSR float32/int32/int32) of compute_direct_metacells,
  * uploaded once (create_host) or borrowed from device memory (create_dev; the arrays must outlive
- * the pile).  All later calls run on the pile's stream and keep every intermediate in HBM. */
+ * the pile).  All later calls run on the pile's stream and keep every intermediate in HBM.
+ * create_host starts the upload in row chunks on a stream of its own and returns; with pinned host memory the
+ * buffers must stay valid until a later call on the pile has synchronised (mcb_pile_similarity, _knn_graph,
+ * _gene_totals, _read_downsampled).  mcb_pile_downsample then works chunk by chunk under the rest of the upload. */
 typedef struct mcb_pile mcb_pile;
 int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
                          mcb_pile** out);
+/* Optional: the largest total of a cell (the pipeline has the totals on the host, tools/downsample.py:84-90).
+ * Sizes the downsampling scratch without a pass over the data and a synchronisation; a cell above it is
+ * reported by the next synchronising call on the pile. */
+int mcb_pile_set_max_cell_total(mcb_pile* pile, uint64_t max_total);
 int mcb_pile_create_dev(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
                         void* stream, mcb_pile** out);
 int64_t mcb_pile_nnz(const mcb_pile* pile);

@@ -1,4 +1,6 @@
 // C-ABI of the device-resident pile (see pile.cu and mcb200.h).
+#include <algorithm>
+#include <cstdlib>
 #include <memory>
 #include <vector>
 
@@ -6,9 +8,10 @@
 #include "../../include/mcb200.h"
 
 namespace mcb {
-int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
-                      int32_t samples_all, int64_t rows, int64_t columns, int64_t max_row_size, uint64_t seed,
-                      int use_row_seed, cudaStream_t stream);
+int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
+                           int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
+                           uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
+                           cudaStream_t stream);
 int column_totals_launch(const float* data, const int32_t* indices, int64_t nnz, int64_t columns, float* totals,
                          cudaStream_t stream);
 int log_fraction_dense_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t rows,
@@ -37,9 +40,44 @@ struct mcb_pile {
     bool has_downsampled = false;
     Scratch top_genes;    // int32[top_genes_count] ascending, set by mcb_pile_top_genes
     int64_t top_genes_count = 0;
+    // A host pile is uploaded in row chunks on its own stream, so that the downsampling of the first chunks runs
+    // under the upload of the later ones: chunk c holds rows [chunk_rows[c], chunk_rows[c + 1]).
+    cudaStream_t copy_stream = nullptr;
+    std::vector<int64_t> chunk_rows;
+    std::vector<cudaEvent_t> chunk_ready;
+    unsigned long long max_row_total = 0;  // mcb_pile_set_max_cell_total: spares a kernel + synchronisation
+    Scratch status;                        // device int: deferred errors of asynchronous steps
+    ~mcb_pile() {
+        for (cudaEvent_t event : chunk_ready) cudaEventDestroy(event);
+        if (copy_stream) {
+            cudaStreamSynchronize(copy_stream);
+            cudaStreamDestroy(copy_stream);
+        }
+    }
 };
 
 namespace {
+
+// Orders the pile's stream after the upload of a host pile (a no-op for a device pile).
+int wait_for_upload(mcb_pile* pile) {
+    if (!pile->chunk_ready.empty())
+        MCB_CUDA(cudaStreamWaitEvent(pile->stream, pile->chunk_ready.back(), 0));
+    return MCB_OK;
+}
+
+// Deferred errors of the asynchronous steps, read where the caller synchronises anyway.
+int check_status(mcb_pile* pile) {
+    if (!pile->status.ptr) {
+        MCB_CUDA(cudaStreamSynchronize(pile->stream));
+        return MCB_OK;
+    }
+    int status = 0;
+    MCB_CUDA(cudaMemcpyAsync(&status, pile->status.ptr, sizeof(int), cudaMemcpyDeviceToHost, pile->stream));
+    MCB_CUDA(cudaStreamSynchronize(pile->stream));
+    MCB_REQUIRE(status != 3, "downsample: a cell totals more than the maximum given to mcb_pile_set_max_cell_total");
+    MCB_REQUIRE(status == 0, "downsample: a cell totals 2^32 UMIs or more");
+    return MCB_OK;
+}
 
 int finish_create(mcb_pile* pile, const int32_t* host_indptr) {
     int64_t widest = 0;
@@ -67,13 +105,51 @@ int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_
     MCB_TRY(pile->own_data.alloc((size_t)pile->nnz * sizeof(float), stream));
     MCB_TRY(pile->own_indices.alloc((size_t)pile->nnz * sizeof(int32_t), stream));
     MCB_TRY(pile->own_indptr.alloc((size_t)(cells + 1) * sizeof(int32_t), stream));
-    MCB_CUDA(cudaMemcpyAsync(pile->own_data.ptr, data, (size_t)pile->nnz * sizeof(float), cudaMemcpyHostToDevice, stream));
-    MCB_CUDA(cudaMemcpyAsync(pile->own_indices.ptr, indices, (size_t)pile->nnz * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
-    MCB_CUDA(cudaMemcpyAsync(pile->own_indptr.ptr, indptr, (size_t)(cells + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(pile->status.alloc(sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(pile->status.ptr, 0, sizeof(int), stream));
+    // Upload on a stream of its own, in row chunks of about equal bytes, each followed by an event.
+    MCB_CUDA(cudaStreamCreateWithFlags(&pile->copy_stream, cudaStreamNonBlocking));
+    cudaEvent_t allocated;
+    MCB_CUDA(cudaEventCreateWithFlags(&allocated, cudaEventDisableTiming));
+    MCB_CUDA(cudaEventRecord(allocated, stream));
+    MCB_CUDA(cudaStreamWaitEvent(pile->copy_stream, allocated, 0));
+    cudaEventDestroy(allocated);
+    MCB_CUDA(cudaMemcpyAsync(pile->own_indptr.ptr, indptr, (size_t)(cells + 1) * sizeof(int32_t), cudaMemcpyHostToDevice,
+                             pile->copy_stream));
+    int chunks = pile->nnz >= (8 << 20) ? 8 : 1;
+    if (const char* forced = getenv("MCB_PILE_CHUNKS"))  // developer aid
+        chunks = std::max(1, atoi(forced));
+    pile->chunk_rows.push_back(0);
+    for (int c = 1; c <= chunks; ++c) {
+        int64_t row = cells;
+        if (c < chunks) {  // the first row at or past this share of the non-zeros
+            const int64_t want = pile->nnz / chunks * c;
+            row = std::lower_bound(indptr, indptr + cells + 1, (int32_t)want) - indptr;
+            row = std::min<int64_t>(std::max<int64_t>(row, pile->chunk_rows.back()), cells);
+        }
+        const int64_t begin = indptr[pile->chunk_rows.back()], end = indptr[row];
+        if (end > begin) {
+            MCB_CUDA(cudaMemcpyAsync(pile->own_data.as<float>() + begin, data + begin, (size_t)(end - begin) * sizeof(float),
+                                     cudaMemcpyHostToDevice, pile->copy_stream));
+            MCB_CUDA(cudaMemcpyAsync(pile->own_indices.as<int32_t>() + begin, indices + begin, (size_t)(end - begin) * sizeof(int32_t),
+                                     cudaMemcpyHostToDevice, pile->copy_stream));
+        }
+        cudaEvent_t ready;
+        MCB_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+        MCB_CUDA(cudaEventRecord(ready, pile->copy_stream));
+        pile->chunk_ready.push_back(ready);
+        pile->chunk_rows.push_back(row);
+    }
     pile->data = pile->own_data.as<float>();
     pile->indices = pile->own_indices.as<int32_t>();
     pile->indptr = pile->own_indptr.as<int32_t>();
     *out = pile.release();
+    return MCB_OK;
+}
+
+int mcb_pile_set_max_cell_total(mcb_pile* pile, uint64_t max_total) {
+    MCB_REQUIRE(pile != nullptr, "pile: null handle");
+    pile->max_row_total = max_total;
     return MCB_OK;
 }
 
@@ -100,14 +176,26 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
     MCB_REQUIRE(samples >= 0, "pile: negative samples");
     if (!pile->downsampled.ptr)
         MCB_TRY(pile->downsampled.alloc((size_t)pile->nnz * sizeof(float), pile->stream));
-    MCB_TRY(downsample_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples, pile->cells, 0,
-                              pile->widest, random_seed, 1, pile->stream));
+    if (pile->chunk_ready.empty()) {
+        MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples, 0, pile->cells, 0,
+                                       pile->widest, random_seed, 1, pile->max_row_total, nullptr, pile->stream));
+    } else {
+        // Every chunk as soon as it has arrived; with the largest cell total known nothing here waits on the device.
+        for (size_t c = 0; c < pile->chunk_ready.size(); ++c) {
+            MCB_CUDA(cudaStreamWaitEvent(pile->stream, pile->chunk_ready[c], 0));
+            MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples,
+                                           pile->chunk_rows[c], pile->chunk_rows[c + 1], 0, pile->widest, random_seed, 1,
+                                           pile->max_row_total, pile->max_row_total ? pile->status.as<int>() : nullptr,
+                                           pile->stream));
+        }
+    }
     pile->has_downsampled = true;
     return MCB_OK;
 }
 
 int mcb_pile_gene_totals(mcb_pile* pile, float* totals) {
     MCB_REQUIRE(pile != nullptr && totals != nullptr, "pile: null argument");
+    MCB_TRY(wait_for_upload(pile));
     const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     Scratch device;
     MCB_TRY(device.alloc((size_t)pile->genes * sizeof(float), pile->stream));
@@ -119,6 +207,7 @@ int mcb_pile_gene_totals(mcb_pile* pile, float* totals) {
 
 int mcb_pile_read_downsampled(mcb_pile* pile, float* data) {
     MCB_REQUIRE(pile != nullptr && pile->has_downsampled, "pile: not downsampled yet");
+    MCB_TRY(check_status(pile));
     MCB_CUDA(cudaMemcpyAsync(data, pile->downsampled.ptr, (size_t)pile->nnz * sizeof(float), cudaMemcpyDeviceToHost, pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     return MCB_OK;
@@ -151,6 +240,7 @@ int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t featur
     }
     MCB_REQUIRE(features >= 1 && features <= pile->genes, "pile: bad feature genes count %lld", (long long)features);
     cudaStream_t stream = pile->stream;
+    MCB_TRY(wait_for_upload(pile));
     trace_lap("similarity: enter", stream);
     Scratch d_genes, d_slot, d_table, d_dense, d_flag;
     const int32_t* genes_device = pile->top_genes.as<int32_t>();
@@ -178,7 +268,7 @@ int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t featur
     trace_lap("similarity: correlate", stream);
     int flags[2] = {0, 0};
     MCB_CUDA(cudaMemcpyAsync(flags, d_flag.ptr, sizeof(flags), cudaMemcpyDeviceToHost, stream));
-    MCB_CUDA(cudaStreamSynchronize(stream));
+    MCB_TRY(check_status(pile));  // synchronises the stream
     MCB_REQUIRE((flags[1] & 1) == 0, "pile: a feature gene is out of range");
     MCB_REQUIRE((flags[1] & 2) == 0, "pile: a feature gene is listed twice");
     if (outside_table)
@@ -199,6 +289,7 @@ int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t fe
 int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host) {
     MCB_REQUIRE(pile != nullptr && count >= 1 && count < pile->genes, "pile: top genes count must be in 1..genes-1");
     cudaStream_t stream = pile->stream;
+    MCB_TRY(wait_for_upload(pile));
     const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     Scratch totals, unused;
     MCB_TRY(totals.alloc((size_t)pile->genes * sizeof(float), stream));

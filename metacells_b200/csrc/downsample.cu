@@ -40,7 +40,8 @@ struct DownsampleParams {
     const int32_t* samples;  // per row; nullptr: use `samples_all`
     int32_t samples_all;
     int64_t columns;
-    int64_t rows;
+    int64_t rows;            // one past the last row
+    int64_t first_row;       // rows [first_row, rows) are processed
     uint64_t seed;
     int use_row_seed;        // 1: seed + 997 * row (matrix forms); 0: seed as given (array form)
     uint32_t* workspace;     // 2 * capacity uint32 per CTA when rows do not fit shared memory
@@ -70,7 +71,7 @@ __global__ void __launch_bounds__(DS_THREADS) downsample_kernel(DownsampleParams
     __syncthreads();
     const uint32_t pow_batch = pow_a[DS_THREADS - 1];  // a^BATCH
 
-    for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
+    for (int64_t row = p.first_row + blockIdx.x; row < p.rows; row += gridDim.x) {
         const int64_t lo = p.indptr ? (int64_t)p.indptr[row] : row * p.columns;
         const int64_t hi = p.indptr ? (int64_t)p.indptr[row + 1] : lo + p.columns;
         const int n = (int)(hi - lo);
@@ -200,7 +201,7 @@ constexpr int DW_WARPS = 8;
 // Largest row total of the rows that will actually be sampled (sizes the per-warp bitmap).
 __global__ void __launch_bounds__(256) max_row_total_kernel(DownsampleParams p, unsigned long long* __restrict__ result) {
     const int lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t row = p.first_row + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= p.rows)
         return;
     const int64_t lo = p.indptr ? (int64_t)p.indptr[row] : row * p.columns;
@@ -265,7 +266,7 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
         unsigned long long claimed = 0;
         if (lane == 0)
             claimed = atomicAdd(wp.next_row, 1ull);
-        const int64_t row = (int64_t)__shfl_sync(0xffffffffu, claimed, 0);
+        const int64_t row = p.first_row + (int64_t)__shfl_sync(0xffffffffu, claimed, 0);
         if (row >= p.rows)
             break;
         const int64_t lo = p.indptr ? (int64_t)p.indptr[row] : row * p.columns;
@@ -380,10 +381,26 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
 
 }  // namespace
 
+// Rows [first_row, last_row).  known_max_total > 0: the caller knows the largest row total (the pipeline has the cells'
+// totals on the host, tools/downsample.py:84-90), which spares a kernel and a stream synchronisation.
+int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
+                           int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
+                           uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
+                           cudaStream_t stream);
+
 int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                       int32_t samples_all, int64_t rows, int64_t columns, int64_t max_row_size, uint64_t seed,
                       int use_row_seed, cudaStream_t stream) {
-    if (rows == 0)
+    return downsample_rows_launch(input, output, indptr, samples, samples_all, 0, rows, columns, max_row_size, seed, use_row_seed,
+                                  0, nullptr, stream);
+}
+
+int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
+                           int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
+                           uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
+                           cudaStream_t stream) {
+    const int64_t rows = last_row - first_row;
+    if (rows <= 0)
         return MCB_OK;
     DownsampleParams p{};
     p.input = input;
@@ -392,24 +409,28 @@ int downsample_launch(const float* input, float* output, const int32_t* indptr, 
     p.samples = samples;
     p.samples_all = samples_all;
     p.columns = columns;
-    p.rows = rows;
+    p.rows = last_row;
+    p.first_row = first_row;
     p.seed = seed;
     p.use_row_seed = use_row_seed;
 
     Scratch workspace, flag, counters;
     MCB_TRY(flag.alloc(sizeof(int), stream));
     MCB_CUDA(cudaMemsetAsync(flag.ptr, 0, sizeof(int), stream));
-    p.error_flag = flag.as<int>();
+    // deferred_flag (device, sticky): the caller reads it at its next synchronisation instead of this call waiting
+    p.error_flag = deferred_flag ? deferred_flag : flag.as<int>();
 
     // Preferred: one warp per row over a bitmap of the row's UMIs, when the largest row fits shared memory.
     MCB_TRY(counters.alloc(2 * sizeof(unsigned long long), stream));
     MCB_CUDA(cudaMemsetAsync(counters.ptr, 0, 2 * sizeof(unsigned long long), stream));
-    MCB_PROFILED("downsample_totals", stream,
-                 max_row_total_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(p, counters.as<unsigned long long>()));
-    MCB_LAUNCH_CHECK();
-    unsigned long long max_total = 0;
-    MCB_CUDA(cudaMemcpyAsync(&max_total, counters.ptr, sizeof(max_total), cudaMemcpyDeviceToHost, stream));
-    MCB_CUDA(cudaStreamSynchronize(stream));
+    unsigned long long max_total = known_max_total;
+    if (max_total == 0) {
+        MCB_PROFILED("downsample_totals", stream,
+                     max_row_total_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(p, counters.as<unsigned long long>()));
+        MCB_LAUNCH_CHECK();
+        MCB_CUDA(cudaMemcpyAsync(&max_total, counters.ptr, sizeof(max_total), cudaMemcpyDeviceToHost, stream));
+        MCB_CUDA(cudaStreamSynchronize(stream));
+    }
     if (max_total == 0) {
         // nothing to sample: every row is copied (or left untouched); the warp kernel does that too
         max_total = 1;

@@ -54,7 +54,10 @@ def _ptr(array: np.ndarray) -> ctypes.c_void_p:
 class Pile:
     """A device-resident pile (cells x genes UMI CSR matrix)."""
 
-    def __init__(self, umis: sp.csr_matrix):
+    def __init__(self, umis: sp.csr_matrix, *, max_cell_total: Optional[float] = None):
+        """``max_cell_total``: the largest total of a cell when the caller has the totals anyway
+        (tools/downsample.py:84-90 needs them for the samples count); lets the downsampling start chunk by chunk
+        under the upload without a pass over the data."""
         umis = sp.csr_matrix(umis)
         self._data = np.ascontiguousarray(umis.data, dtype="float32")
         self._indices = np.ascontiguousarray(umis.indices, dtype="int32")
@@ -66,6 +69,10 @@ class Pile:
         check(function(_ptr(self._data), _ptr(self._indices), _ptr(self._indptr), ctypes.c_int64(umis.shape[0]),
                        ctypes.c_int64(umis.shape[1]), ctypes.byref(self._handle)))
         self.samples: Optional[int] = None
+        if max_cell_total is not None:
+            function = lib().mcb_pile_set_max_cell_total
+            function.restype = ctypes.c_int
+            check(function(self._handle, ctypes.c_uint64(int(max_cell_total))))
 
     def close(self) -> None:
         if getattr(self, "_handle", None):
@@ -155,7 +162,7 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
                             np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
     if k is None:
         k = knn_k_of_pile(umis.shape[0], cell_umis)
-    with Pile(umis) as pile:
+    with Pile(umis, max_cell_total=float(cell_umis.max())) as pile:
         pile.downsample(samples, random_seed)
         selected_on_device = feature_genes is None
         if selected_on_device:

@@ -111,3 +111,37 @@ def test_wide_row_goes_through_global_workspace():
     out = np.zeros_like(dense)
     _xt().downsample_dense_float32_t_float32_t(dense, out, samples, 99)
     assert np.array_equal(out, expected)
+
+
+def test_host_pile_is_downsampled_in_chunks_under_the_upload():
+    """A pile of more than 8M non-zeros is uploaded in eight row chunks, each downsampled as it arrives
+    (mcb_pile_create_host + mcb_pile_set_max_cell_total + mcb_pile_downsample): same bytes as the oracle."""
+    from synth import synth_umis
+
+    from metacells_b200 import pipeline
+    from oracle import oracle
+
+    umis = synth_umis(2600, 27000, seed=5)
+    assert umis.nnz >= (8 << 20)
+    totals = np.asarray(umis.sum(axis=1)).reshape(-1)
+    samples = int(np.quantile(totals, 0.3))
+    expected = oracle.downsample_compressed(umis.data, umis.indptr, np.full(umis.shape[0], samples, dtype="int32"), 123456)
+    for hint in (float(totals.max()), None):
+        with pipeline.Pile(umis, max_cell_total=hint) as pile:
+            pile.downsample(samples, 123456)
+            assert np.array_equal(pile.downsampled().data, expected)
+
+
+def test_too_small_cell_total_is_reported():
+    from synth import synth_umis
+
+    from metacells_b200 import pipeline
+    from metacells_b200._lib import McbError
+
+    umis = synth_umis(200, 27000, seed=6)
+    totals = np.asarray(umis.sum(axis=1)).reshape(-1)
+    assert totals.max() > 4096  # the smallest bitmap holds 2 048 UMIs
+    with pipeline.Pile(umis, max_cell_total=1.0) as pile:
+        pile.downsample(int(np.quantile(totals, 0.3)), 1)
+        with pytest.raises(McbError, match="more than the maximum"):
+            pile.downsampled()
