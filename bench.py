@@ -34,8 +34,8 @@ SEED = 123456
 def parse_args():
     parser = argparse.ArgumentParser()
     parser.add_argument("--gpus", type=int, default=1)
-    parser.add_argument("--steps", type=int, default=5)
-    parser.add_argument("--warmup", type=int, default=3)
+    parser.add_argument("--steps", type=int, default=10)
+    parser.add_argument("--warmup", type=int, default=5)
     parser.add_argument("--impl", default="b200", choices=["b200", "reference"])
     parser.add_argument("--cells", type=int, default=16000)
     parser.add_argument("--genes", type=int, default=27000)

@@ -23,6 +23,8 @@ namespace mcb {
 int exclusive_scan_i32(const int32_t* input, int32_t* output, int64_t count, int32_t* total_out, cudaStream_t stream);
 int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t* indptr, int64_t bands, int64_t widest_band,
                                    cudaStream_t stream);
+int sort_distinct_indices_launch(float* data, int32_t* indices, const int32_t* indptr, int64_t bands, int64_t widest_band,
+                                 int64_t index_range, cudaStream_t stream);
 
 namespace {
 
@@ -483,8 +485,9 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     m.out_indices = out->indices.as<int32_t>();
     MCB_PROFILED("merge_fill", stream, merge_preserved_kernel<true><<<warp_blocks, 256, 0, stream>>>(m));
     MCB_LAUNCH_CHECK();
-    return sort_compressed_indices_launch(out->data.as<float>(), out->indices.as<int32_t>(), out->indptr.as<int32_t>(), n,
-                                          -1, stream);
+    // a row's own columns and the appended preserved edges are distinct
+    return sort_distinct_indices_launch(out->data.as<float>(), out->indices.as<int32_t>(), out->indptr.as<int32_t>(), n, -1, n,
+                                        stream);
 }
 
 // knn_graph.py:395-407 (_weigh_edges); also reports the smallest row size (knn_graph.py:262-263).

@@ -288,6 +288,88 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
     return MCB_OK;
 }
 
+namespace {
+
+// Bands whose indices are DISTINCT (every transpose or merge of a proper compressed matrix): a counting sort
+// through a bitmap of the band's indices -- position = number of smaller indices present = popcount prefix.
+// Linear in band size + index_range / 32, against the log^2 stages of the bitonic sort above.
+__global__ void __launch_bounds__(SP_THREADS) sort_distinct_bands_kernel(float* __restrict__ data, int32_t* __restrict__ indices,
+                                                                        const int32_t* __restrict__ indptr, int64_t bands,
+                                                                        int index_range) {
+    extern __shared__ __align__(16) uint8_t sd_smem[];
+    __shared__ int scan_scratch[34];
+    const int words = (index_range + 31) >> 5;
+    uint32_t* bitmap = reinterpret_cast<uint32_t*>(sd_smem);
+    uint32_t* before = bitmap + words;
+    unsigned long long* staged = reinterpret_cast<unsigned long long*>(sd_smem + (((size_t)words * 8 + 15) & ~(size_t)15));
+    const int tid = threadIdx.x;
+    for (int64_t band = blockIdx.x; band < bands; band += gridDim.x) {
+        const int lo = indptr[band], count = indptr[band + 1] - lo;
+        if (count <= 1)
+            continue;
+        for (int w = tid; w < words; w += SP_THREADS) bitmap[w] = 0;
+        __syncthreads();
+        for (int e = tid; e < count; e += SP_THREADS) {
+            const uint32_t index = (uint32_t)indices[lo + e];
+            staged[e] = ((unsigned long long)index << 32) | __float_as_uint(data[lo + e]);
+            atomicOr(&bitmap[index >> 5], 1u << (index & 31));
+        }
+        __syncthreads();
+        int running = 0;
+        for (int base = 0; base < words; base += SP_THREADS) {
+            const int w = base + tid;
+            const int present = w < words ? __popc(bitmap[w]) : 0;
+            int total;
+            const int exclusive = block_exclusive_scan(present, scan_scratch, &total);
+            if (w < words)
+                before[w] = (uint32_t)(running + exclusive);
+            running += total;
+        }
+        __syncthreads();
+        for (int e = tid; e < count; e += SP_THREADS) {
+            const unsigned long long entry = staged[e];
+            const uint32_t index = (uint32_t)(entry >> 32);
+            const int at = lo + (int)before[index >> 5] + __popc(bitmap[index >> 5] & ((1u << (index & 31)) - 1u));
+            indices[at] = (int32_t)index;
+            data[at] = __uint_as_float((uint32_t)entry);
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+// As sort_compressed_indices_launch for bands of distinct indices below index_range (see the kernel); falls back to
+// the general sort when a band or the index range is too large for the shared-memory plan.
+int sort_distinct_indices_launch(float* data, int32_t* indices, const int32_t* indptr, int64_t bands, int64_t widest_band,
+                                 int64_t index_range, cudaStream_t stream) {
+    if (bands == 0)
+        return MCB_OK;
+    if (index_range > (1 << 17))
+        return sort_compressed_indices_launch(data, indices, indptr, bands, widest_band, stream);
+    if (widest_band < 0 || widest_band > 2048) {  // a loose bound would waste shared memory: measure
+        Scratch widest;
+        MCB_TRY(widest.alloc(sizeof(int32_t), stream));
+        MCB_CUDA(cudaMemsetAsync(widest.ptr, 0, sizeof(int32_t), stream));
+        max_band_kernel<<<(unsigned)std::min<int64_t>(ceil_div(bands, 256), 1024), 256, 0, stream>>>(indptr, bands, widest.as<int32_t>());
+        MCB_LAUNCH_CHECK();
+        int32_t host = 0;
+        MCB_CUDA(cudaMemcpyAsync(&host, widest.ptr, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        MCB_CUDA(cudaStreamSynchronize(stream));
+        widest_band = host;
+    }
+    if (widest_band > 8192)
+        return sort_compressed_indices_launch(data, indices, indptr, bands, widest_band, stream);
+    const size_t words = (size_t)((index_range + 31) >> 5);
+    const size_t smem_bytes = ((words * 8 + 15) & ~(size_t)15) + (size_t)widest_band * 8;
+    MCB_CUDA(cudaFuncSetAttribute(sort_distinct_bands_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    const int64_t grid = std::min<int64_t>(bands, (int64_t)sm_count() * 8);
+    MCB_PROFILED("sort_bands", stream, sort_distinct_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(
+                     data, indices, indptr, bands, (int)index_range));
+    MCB_LAUNCH_CHECK();
+    return MCB_OK;
+}
+
 // Full transpose: counts -> out_indptr[bands_out + 1], scatter, sort.  The relayout of
 // computation.py:251-303 (bincount + cumsum + collect_compressed + sort_compressed_indices).
 int relayout_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t bands_in, int64_t bands_out,
@@ -304,7 +386,7 @@ int relayout_launch(const float* data, const int32_t* indices, const int32_t* in
     MCB_TRY(exclusive_scan_i32(counts.as<int32_t>(), out_indptr, bands_out, nullptr, stream));
     MCB_CUDA(cudaMemcpyAsync(cursor.ptr, out_indptr, (size_t)(bands_out ? bands_out : 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
     MCB_TRY(collect_compressed_launch(data, indices, indptr, bands_in, out_data, out_indices, cursor.as<int32_t>(), stream));
-    return sort_compressed_indices_launch(out_data, out_indices, out_indptr, bands_out, bands_in, stream);
+    return sort_distinct_indices_launch(out_data, out_indices, out_indptr, bands_out, bands_in, bands_in, stream);
 }
 
 }  // namespace mcb
