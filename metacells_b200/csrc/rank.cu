@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(RM_THREADS, 1) rank_matrix_kernel(RankMatrixPa
     }
 }
 
-// ---- rows of up to 16 384 elements: a merge sort of (key, position) pairs ---------------------------------
+// ---- rows of up to 24 576 elements (every default pile): a merge sort of (key, position) pairs ---------------------------------
 //
 // The pair (32-bit sort key << 16 | 16-bit position) is unique per element, so any correct sort gives the
 // position-ordered tie rule.  Every thread takes ITEMS elements of the row (strided: coalesced loads), sorts
@@ -145,24 +145,36 @@ constexpr int MS_THREADS = 1024;
 
 __device__ __forceinline__ int ms_slot(int element) { return element + (element >> 4); }  // bank-conflict padding
 
+// Batcher's odd-even merge sort as a compare-exchange network over registers.  The iterative construction is
+// valid for any ITEMS (63 exchanges for 16, 132 for 24); the list of exchanges is built at compile time so that
+// every register index is a constant after unrolling.
+template <int ITEMS>
+struct SortNetwork {
+    int count = 0;
+    int low[ITEMS * ITEMS] = {};
+    int high[ITEMS * ITEMS] = {};
+    constexpr SortNetwork() {
+        for (int p = 1; p < ITEMS; p <<= 1)
+            for (int k = p; k >= 1; k >>= 1)
+                for (int j = k % p; j + k < ITEMS; j += 2 * k)
+                    for (int i = 0; i < k; ++i)
+                        if (i + j + k < ITEMS && (i + j) / (2 * p) == (i + j + k) / (2 * p)) {
+                            low[count] = i + j;
+                            high[count] = i + j + k;
+                            ++count;
+                        }
+    }
+};
+
 template <int ITEMS>
 __device__ __forceinline__ void ms_sort_registers(unsigned long long (&a)[ITEMS]) {
+    constexpr SortNetwork<ITEMS> network{};
 #pragma unroll
-    for (int k = 2; k <= ITEMS; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i) {
-                const int l = i ^ j;
-                if (l > i) {
-                    const bool ascending = (i & k) == 0;
-                    const unsigned long long x = a[i], y = a[l];
-                    const bool swap = ascending ? (x > y) : (x < y);
-                    a[i] = swap ? y : x;
-                    a[l] = swap ? x : y;
-                }
-            }
-        }
+    for (int c = 0; c < network.count; ++c) {
+        const unsigned long long x = a[network.low[c]], y = a[network.high[c]];
+        const bool swap = x > y;
+        a[network.low[c]] = swap ? y : x;
+        a[network.high[c]] = swap ? x : y;
     }
 }
 
@@ -246,6 +258,7 @@ int rank_matrix_launch(float* matrix, int64_t rows, int64_t columns, int64_t row
     if (columns <= MS_THREADS * 4) return rank_matrix_merge_launch<4>(matrix, rows, columns, row_stride, ascending, stream);
     if (columns <= MS_THREADS * 8) return rank_matrix_merge_launch<8>(matrix, rows, columns, row_stride, ascending, stream);
     if (columns <= MS_THREADS * 16) return rank_matrix_merge_launch<16>(matrix, rows, columns, row_stride, ascending, stream);
+    if (columns <= MS_THREADS * 24) return rank_matrix_merge_launch<24>(matrix, rows, columns, row_stride, ascending, stream);
     RankMatrixParams p{};
     p.matrix = matrix;
     p.rows = rows;
@@ -379,6 +392,219 @@ __global__ void __launch_bounds__(SEL_THREADS) collect_top_kernel(CollectTopPara
     }
 }
 
+// top_per.cpp:5-64 for rows whose keys fit shared memory (columns <= CT_MAX_CACHED).  Three sweeps over the cached
+// keys and a handful of block barriers per row:
+//   1. load + histogram of the top 12 key bits (shared-memory atomics);
+//   2. the bin holding the degree-th key; its members (few: 2^20 values share a bin) become candidates, and an
+//      8/8/4-bit radix select over the candidates alone yields the threshold key and how many of its ties to keep;
+//   3. every warp owns a contiguous segment: count kept elements per segment, scan the 16 counts, write.  An
+//      element's slot = (# smaller keys before it) + min(# ties before it, ties kept): indices come out ascending
+//      and ties are kept lowest position first, without a scan per 512 elements.
+constexpr int CT_MAX_CACHED = 32768;
+constexpr int CT_BINS = 4096;
+
+struct CollectTopState {
+    int bin, rank_in_bin, candidates;
+    uint32_t prefix;
+    int rank;
+    int kept_before[SEL_THREADS / 32 + 1], ties_before[SEL_THREADS / 32 + 1];
+    int scan[34];
+};
+
+__global__ void __launch_bounds__(SEL_THREADS) collect_top_cached_kernel(CollectTopParams p) {
+    extern __shared__ __align__(16) uint8_t sel_smem[];
+    __shared__ CollectTopState state;
+    const int n = (int)p.columns, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int WARPS = SEL_THREADS / 32;
+    uint32_t* keys = reinterpret_cast<uint32_t*>(sel_smem);          // [n]
+    uint32_t* candidates = keys + p.cache_capacity;                   // [n]
+    int* hist = reinterpret_cast<int*>(candidates + p.cache_capacity);  // [CT_BINS]
+    uint32_t* kept_keys = reinterpret_cast<uint32_t*>(hist + CT_BINS);  // [degree] (ranks mode)
+    const uint32_t lower_lanes = lanemask_lt();
+    const int segment = ((n + WARPS - 1) / WARPS + 31) / 32 * 32;  // elements per warp in sweep 3
+    for (int64_t row = blockIdx.x; row < p.rows; row += gridDim.x) {
+        const float* values = p.similarity + row * p.row_stride;
+        int32_t* row_indices = p.out_indices + row * p.degree;
+        float* row_data = p.out_data + row * p.degree;
+        for (int i = tid; i < CT_BINS; i += SEL_THREADS) hist[i] = 0;
+        if (tid == 0) state.candidates = 0;
+        __syncthreads();
+        // sweep 1: the row into shared memory (several loads in flight per thread), then the histogram
+        for (int base = 0; base < n; base += 4 * SEL_THREADS) {
+            float loaded[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = base + u * SEL_THREADS + tid;
+                loaded[u] = i < n ? values[i] : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = base + u * SEL_THREADS + tid;
+                if (i < n) keys[i] = sort_key(loaded[u], false);
+            }
+        }
+        __syncthreads();
+        for (int base = 0; base < n; base += SEL_THREADS) {
+            const int i = base + tid;
+            const uint32_t key = i < n ? keys[i] : 0;
+            // one shared-memory atomic per element: lanes with equal digits serialise in the memory pipe, which is
+            // cheaper than building their mask with a dozen ballots (ncu: ballots were 40 % of the instructions)
+            if (i < n) atomicAdd(&hist[key >> 20], 1);
+        }
+        __syncthreads();
+        {   // the bin of the (degree - 1)-th key in ascending key order: thread t owns bins 8t .. 8t+7
+            int counts[CT_BINS / SEL_THREADS], sum = 0;
+#pragma unroll
+            for (int b = 0; b < CT_BINS / SEL_THREADS; ++b) {
+                counts[b] = hist[tid * (CT_BINS / SEL_THREADS) + b];
+                sum += counts[b];
+            }
+            int total;
+            int before = block_exclusive_scan(sum, state.scan, &total);
+            const int wanted = p.degree - 1;
+            if (wanted >= before && wanted < before + sum) {
+#pragma unroll
+                for (int b = 0; b < CT_BINS / SEL_THREADS; ++b) {
+                    if (wanted >= before && wanted < before + counts[b]) {
+                        state.bin = tid * (CT_BINS / SEL_THREADS) + b;
+                        state.rank_in_bin = wanted - before;
+                    }
+                    before += counts[b];
+                }
+            }
+        }
+        __syncthreads();
+        // sweep 2: the members of that bin
+        const uint32_t bin = (uint32_t)state.bin;
+        for (int base = 0; base < n; base += SEL_THREADS) {
+            const int i = base + tid;
+            const uint32_t key = i < n ? keys[i] : 0;
+            const bool member = i < n && (key >> 20) == bin;
+            const uint32_t mask = __ballot_sync(0xffffffffu, member);
+            if (mask != 0) {
+                int start = 0;
+                if (lane == 0) start = atomicAdd(&state.candidates, __popc(mask));
+                start = __shfl_sync(0xffffffffu, start, 0);
+                if (member) candidates[start + __popc(mask & lower_lanes)] = key;
+            }
+        }
+        __syncthreads();
+        // radix select of the low 20 bits among the candidates: digits of 8, 8 and 4 bits
+        const int members = state.candidates;
+        if (tid == 0) {
+            state.prefix = bin << 20;
+            state.rank = state.rank_in_bin;
+        }
+        uint32_t known_mask = 0xfff00000u;
+#pragma unroll 1
+        for (int round = 0; round < 3; ++round) {
+            const int shift = round == 0 ? 12 : (round == 1 ? 4 : 0);
+            const uint32_t digit_mask = round == 2 ? 15u : 255u;
+            for (int i = tid; i < 256; i += SEL_THREADS) hist[i] = 0;
+            __syncthreads();
+            const uint32_t prefix = state.prefix;
+            for (int base = 0; base < members; base += SEL_THREADS) {
+                const int i = base + tid;
+                uint32_t digit = 0;
+                bool valid = false;
+                if (i < members) {
+                    const uint32_t key = candidates[i];
+                    valid = (key & known_mask) == prefix;
+                    digit = (key >> shift) & digit_mask;
+                }
+                if (valid) atomicAdd(&hist[digit], 1);
+            }
+            __syncthreads();
+            if (tid < 32) {
+                int counts[8], sum = 0;
+#pragma unroll
+                for (int b = 0; b < 8; ++b) {
+                    counts[b] = hist[lane * 8 + b];
+                    sum += counts[b];
+                }
+                const int inclusive = warp_inclusive_scan(sum, lane);
+                int before = inclusive - sum;
+                const int wanted = state.rank;
+                __syncwarp();
+                if (wanted >= before && wanted < inclusive) {
+#pragma unroll
+                    for (int b = 0; b < 8; ++b) {
+                        if (wanted >= before && wanted < before + counts[b]) {
+                            state.prefix = prefix | ((uint32_t)(lane * 8 + b) << shift);
+                            state.rank = wanted - before;
+                        }
+                        before += counts[b];
+                    }
+                }
+            }
+            known_mask |= digit_mask << shift;
+            __syncthreads();
+        }
+        const uint32_t threshold = state.prefix;
+        const int ties_wanted = state.rank + 1;  // equal-to-threshold elements to keep, lowest positions first
+        // sweep 3a: smaller keys and ties per warp segment
+        const int seg_begin = min(warp * segment, n), seg_end = min(seg_begin + segment, n);
+        int smaller = 0, ties = 0;
+        for (int base = seg_begin; base < seg_end; base += 32) {
+            const int i = base + lane;
+            const uint32_t key = i < seg_end ? keys[i] : 0xffffffffu;
+            smaller += __popc(__ballot_sync(0xffffffffu, i < seg_end && key < threshold));
+            ties += __popc(__ballot_sync(0xffffffffu, i < seg_end && key == threshold));
+        }
+        if (lane == 0) {
+            state.kept_before[warp] = smaller;
+            state.ties_before[warp] = ties;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int running_smaller = 0, running_ties = 0;
+            for (int w = 0; w < WARPS; ++w) {
+                const int s_count = state.kept_before[w], t_count = state.ties_before[w];
+                state.kept_before[w] = running_smaller;
+                state.ties_before[w] = running_ties;
+                running_smaller += s_count;
+                running_ties += t_count;
+            }
+        }
+        __syncthreads();
+        // sweep 3b: write, ascending positions
+        smaller = state.kept_before[warp];
+        ties = state.ties_before[warp];
+        for (int base = seg_begin; base < seg_end; base += 32) {
+            const int i = base + lane;
+            const uint32_t key = i < seg_end ? keys[i] : 0xffffffffu;
+            const bool is_smaller = i < seg_end && key < threshold, is_tie = i < seg_end && key == threshold;
+            const uint32_t smaller_mask = __ballot_sync(0xffffffffu, is_smaller), tie_mask = __ballot_sync(0xffffffffu, is_tie);
+            const int smaller_before = smaller + __popc(smaller_mask & lower_lanes);
+            const int ties_before = ties + __popc(tie_mask & lower_lanes);
+            if (is_smaller || (is_tie && ties_before < ties_wanted)) {
+                const int slot = smaller_before + min(ties_before, ties_wanted);
+                row_indices[slot] = i;
+                if (p.ranks)
+                    kept_keys[slot] = key;
+                else
+                    row_data[slot] = values[i];
+            }
+            smaller += __popc(smaller_mask);
+            ties += __popc(tie_mask);
+        }
+        if (p.ranks) {
+            __syncthreads();
+            // top_per.cpp:44-63: 1-based rank in ASCENDING value order among the kept values; equal values by position.
+            for (int e = tid; e < p.degree; e += SEL_THREADS) {
+                const uint32_t mine = kept_keys[e];
+                int before = 0;
+                for (int f = 0; f < p.degree; ++f) {
+                    const uint32_t other = kept_keys[f];
+                    before += (other > mine || (other == mine && f < e)) ? 1 : 0;
+                }
+                row_data[e] = (float)(before + 1);
+            }
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace
 
 int rank_rows_launch(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank,
@@ -415,6 +641,15 @@ int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, in
     p.ranks = ranks;
     const size_t kept_bytes = ranks ? (size_t)degree * 4 : 0;
     MCB_REQUIRE(kept_bytes <= 96 * 1024, "collect_top: degree %lld is too large for the ranks mode", (long long)degree);
+    if (columns <= CT_MAX_CACHED && (size_t)columns * 8 + CT_BINS * 4 + kept_bytes <= 220 * 1024) {
+        p.cache_capacity = (int)columns;
+        const size_t cached_bytes = (size_t)columns * 8 + CT_BINS * 4 + kept_bytes;
+        MCB_CUDA(cudaFuncSetAttribute(collect_top_cached_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cached_bytes));
+        const int64_t cached_grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
+        MCB_PROFILED("collect_top", stream, collect_top_cached_kernel<<<(unsigned)cached_grid, SEL_THREADS, cached_bytes, stream>>>(p));
+        MCB_LAUNCH_CHECK();
+        return MCB_OK;
+    }
     p.cache_capacity = ((size_t)columns * 4 + kept_bytes <= 200 * 1024) ? (int)columns : 0;
     const size_t smem_bytes = (size_t)p.cache_capacity * 4 + kept_bytes;
     MCB_CUDA(cudaFuncSetAttribute(collect_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
