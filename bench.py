@@ -42,6 +42,8 @@ def parse_args():
     parser.add_argument("--features", type=int, default=2000)
     parser.add_argument("--cpu-cells", type=int, default=8000, help="cells of the bounded CPU-baseline sample")
     parser.add_argument("--no-cpu-baseline", action="store_true")
+    parser.add_argument("--atlas-cells", type=int, default=1000000,
+                        help="cells of the divide-and-conquer atlas whose piles are timed after the per-pile steps (0: skip)")
     return parser.parse_args()
 
 
@@ -246,7 +248,7 @@ def run_gpu_arm(args):
               "indptr": torch.empty(cells + 1, dtype=torch.int32).pin_memory()}
     stream = torch.cuda.current_stream(device)
 
-    def hot_path(pile):
+    def hot_path(pile, k=k):
         """The path on an existing pile handle; returns the graph handle."""
         library.call("mcb_pile_set_max_cell_total", pile, ctypes.c_uint64(max_cell_total))
         library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
@@ -322,6 +324,10 @@ def run_gpu_arm(args):
     library.call("mcb_profile_reset")
     e2e_ms, _ = timed(step_e2e, args.steps)
 
+    atlas = None
+    if args.atlas_cells > 0:
+        atlas = time_atlas(args, library, pinned, result, capacity, hot_path, barrier, stream, device, rank, world, cells, genes)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -338,9 +344,44 @@ def run_gpu_arm(args):
     if bf16 is None:
         bf16, peak_source = 1400.0, "fallback 1.4 PFLOP/s sustained bf16 (B200_PROFILING.md) / 2 / 3"
     peak = bf16 / 6.0
-    umma_ms, umma_count = kernel_ms.get("correlate_umma", (0.0, 0))
+    hbm = peaks.get("hbm_gbs")
+    hbm_source = "MEASURED_PEAKS.json hbm_gbs"
+    if hbm is None:
+        hbm, hbm_source = 6500.0, "fallback 6.5 TB/s measured copy bandwidth (B200_PROFILING.md)"
+
+    def per_launch_ms(*names):
+        """Average duration of one pass of the named kernels (they run once per pile each)."""
+        total = 0.0
+        for name in names:
+            milliseconds, count = kernel_ms.get(name, (0.0, 0))
+            if not count:
+                return None
+            total += milliseconds / count
+        return total
+
+    def hbm_line(kernel, names, algorithmic_bytes, traffic, traffic_source):
+        ms = per_launch_ms(*names)
+        achieved_gbs = algorithmic_bytes / (ms * 1e-3) / 1e9 if ms else None
+        return {"bound": "hbm", "kernel": kernel, "achieved": achieved_gbs, "peak": hbm, "unit": "GB/s",
+                "frac": achieved_gbs / hbm if achieved_gbs else None, "traffic": traffic, "traffic_source": traffic_source,
+                "peak_source": hbm_source, "algorithmic_bytes_per_launch": algorithmic_bytes, "ms_per_launch": ms}
+
+    umma_ms = per_launch_ms("correlate_umma")
     flops = float(cells) * cells * args.features  # algorithmic: 2 * g * N (N - 1) / 2 ~= N^2 g (SURVEY 8d)
-    achieved = flops / (umma_ms / umma_count * 1e-3) / 1e12 if umma_count else None
+    achieved = flops / (umma_ms * 1e-3) / 1e12 if umma_ms else None
+    correlate_line = {"bound": "tensor", "kernel": "correlate_umma_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                      "frac": achieved / peak if achieved else None, "traffic": ncu_traffic("correlate_umma", cells, args.features),
+                      "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_correlate_umma.txt",
+                      "peak_source": peak_source, "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms}
+    # SURVEY 8d's algorithmic bytes: ranks read and write the whole square matrix; the downsample reads and writes the
+    # pile's values and reads the row pointers; balance reads every rank once (count and fill passes are one stage).
+    rank_line = hbm_line("rank_matrix_merge_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, args.features),
+                         "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_rank_matrix_merge.txt")
+    downsample_line = hbm_line("downsample_rows_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, None, None)
+    balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells, None, None)
+    # the dominant kernel is the one with the largest share of the step
+    candidates = [line for line in (rank_line, correlate_line, downsample_line, balance_line) if line["ms_per_launch"]]
+    dominant = max(candidates, key=lambda line: line["ms_per_launch"]) if candidates else correlate_line
     line = {
         "metric": METRIC, "value": world * cells * args.steps / (resident_ms * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": resident_ms / args.steps, "higher_is_better": True,
@@ -353,13 +394,12 @@ def run_gpu_arm(args):
                 "h2d_bytes_per_step": int(umis.data.nbytes + umis.indices.nbytes + umis.indptr.nbytes + table.nbytes + 4 * args.features),
                 "d2h_bytes_per_step": int(nnz * 8 + (cells + 1) * 4 + genes * 4)},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "correlate_umma_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak if achieved else None, "traffic": umma_traffic(cells, args.features),
-                     "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_correlate_umma.txt",
-                     "peak_source": peak_source,
-                     "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms / umma_count if umma_count else None},
+        "roofline": dominant,
+        "roofline_kernels": [line for line in candidates if line is not dominant],
         "kernel_ms_per_step": {name: total / args.steps for name, (total, _) in sorted(kernel_ms.items())},
     }
+    if atlas is not None:
+        line["atlas"] = atlas
     if world == 1 and not args.no_cpu_baseline:
         step, info, _ = cpu_step_factory(args)
         start = time.perf_counter()
@@ -370,11 +410,73 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
-def umma_traffic(cells, features):
-    """DRAM bytes per correlate_umma launch from the committed ncu capture; null for any other workload."""
-    if (cells, features) == (16000, 2000):
-        return 3.302457e9 + 1.005782e9
-    return None
+def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, stream, device, rank, world, cells, genes):
+    """BASELINE.json's second metric: the wall time of the k-NN graphs of every pile of one divide-and-conquer
+    phase over an atlas of `--atlas-cells` cells (strong scaling: the atlas is fixed, its piles are dealt to the
+    ranks largest first, no collective on the data path).  Every pile goes through the host-buffer path: its CSR is
+    uploaded from pinned memory and its graph is read back.  Generating a million distinct synthetic cells would take
+    longer than the run, so each pile is a row prefix of the rank's synthetic pile; the work of the path depends on
+    the sizes (cells, non-zeros, k), not on the values."""
+    import torch
+    import torch.distributed as dist
+
+    from metacells_b200 import piles as pl, pipeline
+
+    piles_count = -(-args.atlas_cells // cells)  # piles no larger than the synthetic pile
+    pile_of_cells = pl.random_piles(args.atlas_cells, args.atlas_cells / piles_count, random_seed=SEED)
+    sizes = np.bincount(pile_of_cells, minlength=int(pile_of_cells.max()) + 1)
+    assert sizes.max() <= cells, (sizes.max(), cells)
+    indptr = pinned["indptr"].numpy()
+    cell_umis = np.add.reduceat(pinned["data"].numpy(), indptr[:-1]).astype("float32")
+    mine = pl.piles_of_rank(sizes, rank, world)
+    ks = {size: pipeline.knn_k_of_pile(int(size), cell_umis[:size]) for size in set(int(sizes[pile]) for pile in mine)}
+
+    def one_pile(size):
+        pile = ctypes.c_void_p()
+        library.call("mcb_pile_create_host", p(pinned["data"].data_ptr()), p(pinned["indices"].data_ptr()),
+                     p(pinned["indptr"].data_ptr()), ctypes.c_int64(size), ctypes.c_int64(genes), ctypes.byref(pile))
+        graph = hot_path(pile, ks[size])
+        nnz = library.lib.mcb_graph_nnz(graph)
+        if nnz > capacity:
+            raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
+        library.call("mcb_graph_read", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
+                     p(result["indptr"].data_ptr()))
+        library.lib.mcb_graph_free(graph)
+        library.lib.mcb_pile_free(pile)
+        return nnz
+
+    if mine:
+        one_pile(int(sizes[mine[0]]))  # warm the pools for this pile size
+    begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    start = time.perf_counter()
+    begin.record(stream)
+    edges = 0
+    for pile in mine:
+        edges += one_pile(int(sizes[pile]))
+    end.record(stream)
+    barrier()
+    wall = time.perf_counter() - start
+    numbers = torch.tensor([begin.elapsed_time(end) * 1e-3, wall, float(edges)], dtype=torch.float64, device=device)
+    if world > 1:
+        both = numbers.clone()
+        dist.all_reduce(numbers, op=dist.ReduceOp.MAX)
+        dist.all_reduce(both, op=dist.ReduceOp.SUM)
+        edges = int(both[2].item())
+    device_s, wall_s = float(numbers[0].item()), float(numbers[1].item())
+    return {"metric": "divide_and_conquer_knn_graphs_wall_time", "cells": int(args.atlas_cells), "piles": int(len(sizes)),
+            "pile_cells": [int(sizes.min()), int(sizes.max())], "phases": 1, "n_gpus": world, "scaling": "strong",
+            "wall_s": wall_s, "device_s": device_s, "cells_per_s": args.atlas_cells / wall_s, "graph_nnz": int(edges),
+            "data": "synthetic; every pile is a row prefix of the rank's synthetic pile, uploaded from pinned host memory and "
+                    "its graph read back (max over ranks, barrier on both sides)"}
+
+
+def ncu_traffic(kernel, cells, features):
+    """DRAM bytes per launch of a kernel from the committed `ncu --set full` captures (profiles/); null for a
+    workload that was not captured."""
+    if (cells, features) != (16000, 2000):
+        return None
+    return {"correlate_umma": 3.302457e9 + 1.005782e9, "rank_matrix": 1.024111e9 + 0.964185e9}.get(kernel)
 
 
 _RESULT_FD = None
