@@ -261,6 +261,23 @@ int mcb_dev_score_partitions(const float* outgoing_weights, const int32_t* outgo
  * can pin it against libm. */
 int mcb_host_glibc_log_f64(const double* values, double* logs, int64_t count);
 
+/* ---- projection front-end (BASELINE.json config 5) ----------------------------------------
+ * Replaces, for tools/project.py:249-270 + :309-331, the pair `ut.cross_corrcoef_rows(query, atlas)`
+ * (computation.py:478-524 -> cross_correlate_dense, correlate.cpp:433-494) and the per-row
+ * `np.argsort(-correlations)` of which the candidates loop consumes a prefix: for every query row the `k` atlas rows
+ * of the largest Pearson correlation, in descending order of the correlation, equal correlations by ascending atlas
+ * index (a stable argsort of the negated row).  The [query, atlas] matrix is never materialised beyond one block of
+ * query rows in HBM (MCB_PROJECT_BLOCK_BYTES, default 4 GiB).  out_indices / out_correlations: [query_rows, k].
+ * The inputs must not hold NaNs (log fractions never do). */
+int mcb_host_project_top_f32(const float* query, int64_t query_rows, int64_t query_stride, const float* atlas, int64_t atlas_rows,
+                             int64_t atlas_stride, int64_t columns, int64_t k, int32_t* out_indices, float* out_correlations);
+int mcb_dev_project_top_f32(const float* query, int64_t query_rows, const float* atlas, int64_t atlas_rows, int64_t columns,
+                            int64_t k, int32_t* out_indices, float* out_correlations, void* stream);
+/* The selection stage alone on a device matrix [rows, row_stride >= columns]: per row the `k` largest values in
+ * descending order (ties by ascending column), 1 <= k <= min(columns, 4096). */
+int mcb_dev_ordered_top_f32(const float* values, int64_t rows, int64_t columns, int64_t row_stride, int64_t k,
+                            int32_t* out_indices, float* out_values, void* stream);
+
 /* @@APPEND@@ */
 
 #ifdef __cplusplus

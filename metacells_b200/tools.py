@@ -4,6 +4,7 @@
 * ``downsample_cells``            tools/downsample.py:25-118
 * ``compute_obs_obs_similarity``  tools/similarity.py:29-117, 178-246 (``abs_pearson`` / ``pearson``)
 * ``compute_obs_obs_knn_graph``   tools/knn_graph.py:31-121, 203-283
+* ``compute_query_atlas_candidates``  the correlation + ordering front-end of tools/project.py:249-270, 309-331
 
 Defaults are the reference's (metacells/parameters.py).
 """
@@ -16,10 +17,10 @@ import numpy as np
 import scipy.sparse as sp
 
 from . import utilities as ut
-from ._lib import check, host_ptr, lib
+from ._lib import call, check, host_ptr, lib, row_stride
 
 __all__ = ["downsample_cells", "compute_obs_obs_similarity", "compute_obs_obs_similarity_top", "row_block_of_rank",
-           "compute_obs_obs_knn_graph", "KnnGraph"]
+           "compute_obs_obs_knn_graph", "KnnGraph", "compute_query_atlas_candidates", "PROJECT_CANDIDATES_COUNT"]
 
 # metacells/parameters.py
 DOWNSAMPLE_MIN_SAMPLES = 750
@@ -29,6 +30,7 @@ KNN_BALANCED_RANKS_FACTOR = float(np.sqrt(10))
 KNN_INCOMING_DEGREE_FACTOR = 3.0
 KNN_OUTGOING_DEGREE_FACTOR = 1.0
 KNN_MIN_OUTGOING_DEGREE = 2
+PROJECT_CANDIDATES_COUNT = 50
 
 
 def downsample_cells(umis, *, downsample_min_cell_quantile: float = DOWNSAMPLE_MIN_CELL_QUANTILE,
@@ -225,3 +227,36 @@ def compute_obs_obs_knn_graph(similarity: np.ndarray, *, k: int,
     if return_details:
         return outgoing_weights, pruned_ranks, used_k
     return outgoing_weights
+
+
+def compute_query_atlas_candidates(query_data: np.ndarray, atlas_data: np.ndarray, *,
+                                   candidates_count: int = PROJECT_CANDIDATES_COUNT) -> Tuple[np.ndarray, np.ndarray]:
+    """The front-end of ``project_query_onto_atlas`` (tools/project.py): the reference computes
+    ``query_atlas_corr = ut.cross_corrcoef_rows(query_log_fractions, atlas_log_fractions)`` (:270), a dense
+    [query, atlas] matrix in host memory, and then for every query row ``np.argsort(-correlations)`` (:310), of which
+    the candidates loop (:317-331) walks a prefix.  Here both steps run on the GPU without the full matrix: for every
+    query row the ``candidates_count`` most correlated atlas rows, most correlated first (equal correlations by atlas
+    index, as a stable argsort orders them), and their correlations.  Returns ``(indices int32 [query, count],
+    correlations float32 [query, count])``; ``indices[:, 0]`` is the reference's ``atlas_anchor_index``.
+
+    The candidates loop skips atlas rows without significant genes (:325-330), so a caller that needs exactly
+    ``candidates_count`` accepted candidates asks for a longer prefix."""
+    if query_data.ndim != 2 or atlas_data.ndim != 2:
+        raise ValueError("query and atlas data must be matrices")
+    if query_data.shape[1] != atlas_data.shape[1]:
+        raise ValueError("query and atlas data must have the same genes")
+    query = np.asarray(query_data, dtype="float32")
+    atlas = np.asarray(atlas_data, dtype="float32")
+    if query.strides[1] != 4:
+        query = np.ascontiguousarray(query)
+    if atlas.strides[1] != 4:
+        atlas = np.ascontiguousarray(atlas)
+    count = min(int(candidates_count), atlas.shape[0])
+    if count <= 0:
+        raise ValueError("candidates_count must be positive and the atlas must not be empty")
+    indices = np.empty((query.shape[0], count), dtype="int32")
+    correlations = np.empty((query.shape[0], count), dtype="float32")
+    call("mcb_host_project_top_f32", host_ptr(query, "float32", "query"), ("i64", query.shape[0]), ("i64", row_stride(query)),
+         host_ptr(atlas, "float32", "atlas"), ("i64", atlas.shape[0]), ("i64", row_stride(atlas)), ("i64", query.shape[1]),
+         ("i64", count), host_ptr(indices, "int32", "indices", True), host_ptr(correlations, "float32", "correlations", True))
+    return indices, correlations

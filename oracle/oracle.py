@@ -97,6 +97,14 @@ def cross_correlate_dense(first: np.ndarray, second: np.ndarray) -> np.ndarray:
     return out
 
 
+def query_atlas_candidates(query: np.ndarray, atlas: np.ndarray, count: int) -> Tuple[np.ndarray, np.ndarray]:
+    """tools/project.py:270 + :310: the cross correlation and, per query row, the head of ``np.argsort(-row)`` (made
+    stable: numpy's default quicksort leaves the order of equal correlations unspecified)."""
+    correlations = cross_correlate_dense(query, atlas)
+    order = np.argsort(-correlations, axis=1, kind="stable")[:, :count]
+    return order.astype("int32"), np.take_along_axis(correlations, order, axis=1)
+
+
 def pairs_correlate_dense(first: np.ndarray, second: np.ndarray) -> np.ndarray:
     """correlate.cpp:496-527."""
     out = np.empty(first.shape[0], dtype="float32")
