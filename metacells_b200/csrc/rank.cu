@@ -16,8 +16,11 @@
 //   collect_top   one CTA per row; radix select of the degree-th largest value, then an ordered
 //                 compaction (indices come out ascending, as top_per.cpp:35 sorts them).
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
+#include <cstdlib>
+
 #include "select.cuh"
 
 namespace mcb {
@@ -180,13 +183,17 @@ __device__ __forceinline__ void ms_sort_registers(unsigned long long (&a)[ITEMS]
 
 template <int ITEMS>
 __global__ void __launch_bounds__(MS_THREADS, 1) rank_matrix_merge_kernel(float* __restrict__ matrix, int64_t rows, int columns,
-                                                                          int64_t row_stride, int ascending) {
+                                                                          int64_t row_stride, int ascending,
+                                                                          const int* __restrict__ row_list,
+                                                                          const int* __restrict__ row_count) {
     extern __shared__ __align__(16) uint8_t rm_smem[];
     unsigned long long* runs = reinterpret_cast<unsigned long long*>(rm_smem);  // ms_slot(MS_THREADS * ITEMS) entries
     uint16_t* rank_of = reinterpret_cast<uint16_t*>(rm_smem);                   // reuses the buffer at the end
     constexpr int CAPACITY = MS_THREADS * ITEMS;
     const int tid = threadIdx.x;
-    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    if (row_list != nullptr) rows = *row_count;  // only the listed rows (the ones the bucket kernel passed on)
+    for (int64_t entry = blockIdx.x; entry < rows; entry += gridDim.x) {
+        const int64_t row = row_list != nullptr ? row_list[entry] : entry;
         float* values = matrix + row * row_stride;
         unsigned long long a[ITEMS];
 #pragma unroll
@@ -238,14 +245,284 @@ __global__ void __launch_bounds__(MS_THREADS, 1) rank_matrix_merge_kernel(float*
     }
 }
 
+// row_list / row_count (device): when given, only those rows are ranked (their count is not known on the host, so
+// the grid covers the SMs a few times over and CTAs without a row return at once).
 template <int ITEMS>
-int rank_matrix_merge_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream) {
+int rank_matrix_merge_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream,
+                             const int* row_list = nullptr, const int* row_count = nullptr) {
     const size_t smem_bytes = (size_t)(MS_THREADS * ITEMS + MS_THREADS * ITEMS / 16 + 1) * 8;
     MCB_CUDA(cudaFuncSetAttribute(rank_matrix_merge_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    MCB_PROFILED("rank_matrix", stream, rank_matrix_merge_kernel<ITEMS><<<(unsigned)std::min<int64_t>(rows, 1 << 20), MS_THREADS, smem_bytes, stream>>>(
-                     matrix, rows, (int)columns, row_stride, ascending));
+    const int64_t grid = row_list != nullptr ? std::min<int64_t>(rows, (int64_t)sm_count() * 4) : std::min<int64_t>(rows, 1 << 20);
+    MCB_PROFILED(row_list != nullptr ? "rank_matrix_ties" : "rank_matrix", stream,
+                 rank_matrix_merge_kernel<ITEMS><<<(unsigned)grid, MS_THREADS, smem_bytes, stream>>>(
+                     matrix, rows, (int)columns, row_stride, ascending, row_list, row_count));
     MCB_LAUNCH_CHECK();
     return MCB_OK;
+}
+
+// ---- the same rows, faster when the values of a row are spread out: a one-pass bucket sort -------------------------------------
+//
+// A monotone bin of the value with about one element per bin turns sorting into counting.  Values are not spread
+// evenly over their range (most similarities of a cell are small, a few are large), so the bin is the row's own
+// distribution function, estimated by a coarse histogram.  Per row, with the elements in registers (strided: coalesced):
+//   1. the range: largest value and second smallest (the smallest is the diagonal the caller preset to min - 1,
+//      knn_graph.py:288-292, which would otherwise double the range); a histogram of 1024 linear bins over it and its
+//      scan: (elements before the bin, elements inside) is a piecewise-linear estimate of every element's rank;
+//   2. count: the estimated rank is the fine bin; a shared-memory atomicAdd per element, whose return value is the
+//      element's slot inside its bucket;
+//   3. an exclusive scan of the counts gives every bucket its place in the sorted order;
+//   4. scatter of (key, position) to place + slot;
+//   5. every element counts the members of its bucket that sort before it (key, then position: the tie rule of
+//      the file) and writes its rank, coalesced, from the registers it was loaded into.
+// About 80 instructions per element against 200 for the merge sort.  The cost of step 5 is quadratic in the bucket
+// size, so a row with a bucket wider than BK_LIMIT (heavy ties, a constant row) is passed on to the merge sort
+// through a list in device memory.  Ranks do not depend on which kernel produced them.
+constexpr int BK_LIMIT = 32;
+constexpr int BK_COARSE = MS_THREADS;  // one coarse bin per thread
+constexpr float BK_COARSE_TOP = 1023.99993896484375f;  // the largest float below BK_COARSE
+static_assert(BK_COARSE == 1024, "BK_COARSE_TOP is the float before 1024");
+
+template <int ITEMS>
+struct BucketPlan {
+    static constexpr int CAPACITY = MS_THREADS * ITEMS;
+    static constexpr int BINS = ITEMS <= 16 ? CAPACITY : 16384;
+    static constexpr int PER_THREAD = BINS / MS_THREADS;  // bins scanned by one thread: 4, 8 or 16
+    static constexpr size_t BASE_BYTES = (size_t)(BINS + 4) * 4;
+    static constexpr size_t KEYS_BYTES = (size_t)(CAPACITY + 4) * 4;  // padded: the counting loop reads in fours
+    static constexpr size_t POSITIONS_BYTES = (size_t)CAPACITY * 2;
+    static constexpr size_t SCRATCH_BYTES = 1024;
+    static constexpr size_t COARSE_BYTES = (size_t)BK_COARSE * 8;
+    static constexpr size_t SMEM = BASE_BYTES + KEYS_BYTES + POSITIONS_BYTES + SCRATCH_BYTES + COARSE_BYTES;
+};
+
+template <int ITEMS>
+__global__ void __launch_bounds__(MS_THREADS, 1) rank_matrix_bucket_kernel(float* __restrict__ matrix, int64_t rows, int columns,
+                                                                           int64_t row_stride, int ascending,
+                                                                           int* __restrict__ passed_rows,
+                                                                           int* __restrict__ passed_count) {
+    using Plan = BucketPlan<ITEMS>;
+    extern __shared__ __align__(16) uint8_t rm_smem[];
+    int* base = reinterpret_cast<int*>(rm_smem);                                                       // BINS + 4
+    uint32_t* keys = reinterpret_cast<uint32_t*>(rm_smem + Plan::BASE_BYTES);                          // CAPACITY
+    uint16_t* positions = reinterpret_cast<uint16_t*>(rm_smem + Plan::BASE_BYTES + Plan::KEYS_BYTES);  // CAPACITY
+    int* scratch = reinterpret_cast<int*>(rm_smem + Plan::BASE_BYTES + Plan::KEYS_BYTES + Plan::POSITIONS_BYTES);
+    int2* coarse = reinterpret_cast<int2*>(rm_smem + Plan::BASE_BYTES + Plan::KEYS_BYTES + Plan::POSITIONS_BYTES + Plan::SCRATCH_BYTES);
+    float* extremes = reinterpret_cast<float*>(scratch + 40);  // three values per warp
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float v[ITEMS];  // the row being ranked; reloaded with the next row while the ranks of this one are counted
+    if (blockIdx.x < rows) {
+#pragma unroll
+        for (int r = 0; r < ITEMS; ++r) {
+            const int i = r * MS_THREADS + tid;
+            v[r] = i < columns ? matrix[blockIdx.x * row_stride + i] : 0.0f;
+        }
+    }
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        float* values = matrix + row * row_stride;
+        // 1. largest, smallest and second smallest value of the row
+        float largest = -INFINITY, least = INFINITY, second = INFINITY;
+#pragma unroll
+        for (int r = 0; r < ITEMS; ++r) {
+            const int i = r * MS_THREADS + tid;
+            v[r] = canonical_zero(v[r]);
+            if (i < columns) {
+                largest = fmaxf(largest, v[r]);
+                second = fminf(second, fmaxf(least, v[r]));
+                least = fminf(least, v[r]);
+            }
+        }
+#pragma unroll
+        for (int offset = 16; offset > 0; offset >>= 1) {
+            const float other_largest = __shfl_xor_sync(0xffffffffu, largest, offset);
+            const float other_least = __shfl_xor_sync(0xffffffffu, least, offset);
+            const float other_second = __shfl_xor_sync(0xffffffffu, second, offset);
+            largest = fmaxf(largest, other_largest);
+            second = fminf(fminf(second, other_second), fmaxf(least, other_least));
+            least = fminf(least, other_least);
+        }
+        __syncthreads();  // the previous row is done with the scratch and the buffers
+        if (lane == 0) {
+            extremes[warp] = largest;
+            extremes[32 + warp] = least;
+            extremes[64 + warp] = second;
+        }
+        // clear the counts
+        {
+            int4* base4 = reinterpret_cast<int4*>(base);
+            for (int i = tid; i < (Plan::BINS + 4) / 4; i += MS_THREADS) base4[i] = make_int4(0, 0, 0, 0);
+            coarse[tid] = make_int2(0, 0);
+        }
+        __syncthreads();
+        {
+            largest = extremes[lane];
+            least = extremes[32 + lane];
+            second = extremes[64 + lane];
+#pragma unroll
+            for (int offset = 16; offset > 0; offset >>= 1) {
+                const float other_largest = __shfl_xor_sync(0xffffffffu, largest, offset);
+                const float other_least = __shfl_xor_sync(0xffffffffu, least, offset);
+                const float other_second = __shfl_xor_sync(0xffffffffu, second, offset);
+                largest = fmaxf(largest, other_largest);
+                second = fminf(fminf(second, other_second), fmaxf(least, other_least));
+                least = fminf(least, other_least);
+            }
+        }
+        // Coarse bins are linear in the value and monotone in the sort order: ascending from the second smallest
+        // value up, descending from the largest value down; whatever falls outside is clamped into the first / last.
+        const float low = isfinite(second) ? second : least;
+        const float range = largest - low;
+        const float scale = (range > 0.0f && isfinite(range)) ? (float)BK_COARSE / range : 0.0f;
+        const float origin = ascending ? low : largest;
+        const float direction = ascending ? scale : -scale;
+#pragma unroll
+        for (int r = 0; r < ITEMS; ++r) {
+            const int i = r * MS_THREADS + tid;
+            if (i < columns) {
+                const float t = fminf(fmaxf((v[r] - origin) * direction, 0.0f), BK_COARSE_TOP);
+                atomicAdd(&coarse[__float2int_rz(t)].y, 1);
+            }
+        }
+        __syncthreads();
+        {
+            // coarse[c] = (elements of earlier coarse bins, elements of this one): a piecewise-linear estimate of the
+            // row's distribution function, whose value at an element is roughly its rank
+            int total;
+            const int count = coarse[tid].y;
+            const int before = block_exclusive_scan(count, scratch, &total);
+            coarse[tid].x = before;
+        }
+        __syncthreads();
+        // 2. fine bins: the estimated rank, scaled to the number of bins; monotone in the sort order as well
+        const float ratio = (float)Plan::BINS / (float)columns;
+        uint32_t placed[ITEMS];  // bin | slot inside the bucket << 16 (saturated: such a row is passed on anyway)
+#pragma unroll
+        for (int r = 0; r < ITEMS; ++r) {
+            const int i = r * MS_THREADS + tid;
+            placed[r] = 0;
+            if (i < columns) {
+                const float t = fminf(fmaxf((v[r] - origin) * direction, 0.0f), BK_COARSE_TOP);
+                const int c = __float2int_rz(t);
+                const int2 estimate = coarse[c];
+                const float rank_estimate = (float)estimate.x + (t - (float)c) * (float)estimate.y;
+                const int bin = min(__float2int_rz(rank_estimate * ratio), Plan::BINS - 1);
+                const int slot = atomicAdd(&base[bin], 1);
+                placed[r] = (uint32_t)bin | ((uint32_t)min(slot, 0xffff) << 16);
+            }
+        }
+        __syncthreads();
+        // 3. exclusive scan of the counts; the widest bucket decides whether the row stays here
+        int counts[Plan::PER_THREAD], sum = 0, widest = 0;
+        {
+            const int4* base4 = reinterpret_cast<const int4*>(base) + tid * (Plan::PER_THREAD / 4);
+#pragma unroll
+            for (int q = 0; q < Plan::PER_THREAD / 4; ++q) {
+                const int4 four = base4[q];
+                counts[4 * q] = four.x, counts[4 * q + 1] = four.y, counts[4 * q + 2] = four.z, counts[4 * q + 3] = four.w;
+            }
+#pragma unroll
+            for (int b = 0; b < Plan::PER_THREAD; ++b) {
+                sum += counts[b];
+                widest = max(widest, counts[b]);
+            }
+        }
+        int total;
+        int before = block_exclusive_scan(sum, scratch, &total);
+        const int too_wide = __syncthreads_or(widest > BK_LIMIT);
+        if (too_wide) {
+            if (tid == 0) passed_rows[atomicAdd(passed_count, 1)] = (int)row;
+            continue;
+        }
+        {
+            int4* base4 = reinterpret_cast<int4*>(base) + tid * (Plan::PER_THREAD / 4);
+#pragma unroll
+            for (int q = 0; q < Plan::PER_THREAD / 4; ++q) {
+                int4 four;
+                four.x = before, before += counts[4 * q];
+                four.y = before, before += counts[4 * q + 1];
+                four.z = before, before += counts[4 * q + 2];
+                four.w = before, before += counts[4 * q + 3];
+                base4[q] = four;
+            }
+            if (tid == 0) base[Plan::BINS] = total;
+        }
+        __syncthreads();
+        // 4. scatter
+#pragma unroll
+        for (int r = 0; r < ITEMS; ++r) {
+            const int i = r * MS_THREADS + tid;
+            if (i < columns) {
+                const int at = base[placed[r] & 0xffffu] + (int)(placed[r] >> 16);
+                keys[at] = sort_key(v[r], ascending != 0);
+                positions[at] = (uint16_t)i;
+            }
+        }
+        __syncthreads();
+        // the next row's loads fly while this row's ranks are counted
+        if (row + gridDim.x < rows) {
+            const float* next = matrix + (row + gridDim.x) * row_stride;
+#pragma unroll
+            for (int r = 0; r < ITEMS; ++r) {
+                const int i = r * MS_THREADS + tid;
+                v[r] = i < columns ? next[i] : 0.0f;
+            }
+        }
+        // 5. rank = elements of earlier buckets + members of the own bucket that sort before
+#pragma unroll
+        for (int r = 0; r < ITEMS; ++r) {
+            const int i = r * MS_THREADS + tid;
+            if (i < columns) {
+                const int bin = (int)(placed[r] & 0xffffu);
+                const int first = base[bin], last = base[bin + 1];
+                const uint32_t key = keys[first + (int)(placed[r] >> 16)];
+                // four members at a time, the ones past the end of the bucket masked (the buffer is padded): most
+                // buckets take one round, and the four loads are independent
+                int smaller = 0, not_larger = 0;
+#pragma unroll 1
+                for (int at = first; at < last; at += 4) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t other = keys[at + u];
+                        const bool inside = at + u < last;
+                        smaller += (inside && other < key) ? 1 : 0;
+                        not_larger += (inside && other <= key) ? 1 : 0;
+                    }
+                }
+                int earlier = first + smaller;
+                if (not_larger - smaller > 1) {  // equal keys besides the element itself: earlier positions first
+                    for (int at = first; at < last; ++at) earlier += (keys[at] == key && (int)positions[at] < i) ? 1 : 0;
+                }
+                values[i] = (float)(earlier + 1);  // rank.cpp:73-75
+            }
+        }
+    }
+}
+
+template <int ITEMS>
+int rank_matrix_bucket_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream) {
+    using Plan = BucketPlan<ITEMS>;
+    Scratch passed;  // [0]: count, [1..]: the rows passed on to the merge sort
+    MCB_TRY(passed.alloc((size_t)(rows + 1) * sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(passed.ptr, 0, sizeof(int), stream));
+    MCB_CUDA(cudaFuncSetAttribute(rank_matrix_bucket_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Plan::SMEM));
+    MCB_PROFILED("rank_matrix", stream, rank_matrix_bucket_kernel<ITEMS><<<(unsigned)std::min<int64_t>(rows, 1 << 20), MS_THREADS, Plan::SMEM, stream>>>(
+                     matrix, rows, (int)columns, row_stride, ascending, passed.as<int>() + 1, passed.as<int>()));
+    MCB_LAUNCH_CHECK();
+    return rank_matrix_merge_launch<ITEMS>(matrix, rows, columns, row_stride, ascending, stream, passed.as<int>() + 1, passed.as<int>());
+}
+
+// MCB_RANK_MERGE=1 in the environment keeps every row on the merge sort (for comparisons).
+bool merge_sort_only() {
+    static const bool only = [] {
+        const char* text = std::getenv("MCB_RANK_MERGE");
+        return text != nullptr && text[0] == '1';
+    }();
+    return only;
+}
+
+template <int ITEMS>
+int rank_matrix_sorted_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream) {
+    if (merge_sort_only()) return rank_matrix_merge_launch<ITEMS>(matrix, rows, columns, row_stride, ascending, stream);
+    return rank_matrix_bucket_launch<ITEMS>(matrix, rows, columns, row_stride, ascending, stream);
 }
 
 }  // namespace
@@ -255,10 +532,10 @@ int rank_matrix_launch(float* matrix, int64_t rows, int64_t columns, int64_t row
     if (rows == 0 || columns == 0)
         return MCB_OK;
     MCB_REQUIRE(columns <= 65535, "rank_matrix: rows wider than 65535 elements are not supported (got %lld)", (long long)columns);
-    if (columns <= MS_THREADS * 4) return rank_matrix_merge_launch<4>(matrix, rows, columns, row_stride, ascending, stream);
-    if (columns <= MS_THREADS * 8) return rank_matrix_merge_launch<8>(matrix, rows, columns, row_stride, ascending, stream);
-    if (columns <= MS_THREADS * 16) return rank_matrix_merge_launch<16>(matrix, rows, columns, row_stride, ascending, stream);
-    if (columns <= MS_THREADS * 24) return rank_matrix_merge_launch<24>(matrix, rows, columns, row_stride, ascending, stream);
+    if (columns <= MS_THREADS * 4) return rank_matrix_sorted_launch<4>(matrix, rows, columns, row_stride, ascending, stream);
+    if (columns <= MS_THREADS * 8) return rank_matrix_sorted_launch<8>(matrix, rows, columns, row_stride, ascending, stream);
+    if (columns <= MS_THREADS * 16) return rank_matrix_sorted_launch<16>(matrix, rows, columns, row_stride, ascending, stream);
+    if (columns <= MS_THREADS * 24) return rank_matrix_sorted_launch<24>(matrix, rows, columns, row_stride, ascending, stream);
     RankMatrixParams p{};
     p.matrix = matrix;
     p.rows = rows;

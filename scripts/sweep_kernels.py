@@ -58,7 +58,7 @@ for cells in [int(x) for x in args.cells.split(",")]:
             _lib.check(library.mcb_dev_collect_top_f32(i64(k), p(similarity), i64(cells), i64(cells), i64(cells), p(top_indices), p(top_values), ctypes.c_int(0), stream))
             _lib.check(library.mcb_dev_collect_pruned_f32_i32_i32(i64(pruned_degree), p(top_values), p(top_indices), p(indptr), i64(cells), p(pruned_values), p(pruned_indices), p(pruned_indptr), stream))
         torch.cuda.synchronize()
-        correlate, rank, top, prune = read("correlate_umma"), read("rank_matrix"), read("collect_top"), read("prune_bands")
+        correlate, rank, top, prune = read("correlate_umma"), read("rank_matrix") + read("rank_matrix_ties"), read("collect_top"), read("prune_bands")
         flops = float(cells) * cells * genes
         tf = flops / (correlate * 1e-3) / 1e12
         rank_gbs = 8.0 * cells * cells / (rank * 1e-3) / 1e9
