@@ -43,6 +43,36 @@ def test_rank_matrix_matches_oracle(shape, ascending):
     assert np.array_equal(actual, expected)
 
 
+@pytest.mark.parametrize("columns", [3000, 9000, 16001, 20000])
+@pytest.mark.parametrize("ascending", [False, True])
+def test_rank_matrix_rows_of_every_kind(columns, ascending):
+    """The bucket sort takes the rows whose values are spread out; rows with wide groups of ties, constant rows and
+    rows with infinite values are passed to the merge sort.  The ranks must not depend on which kernel made them."""
+    rng = np.random.default_rng(columns + int(ascending))
+    matrix = np.empty((12, columns), dtype="float32")
+    matrix[0] = np.abs(rng.normal(0.2, 0.03, size=columns))                    # smooth: the bucket sort
+    matrix[0, 5] = matrix[0].min() - 1                                          # the caller's diagonal (knn_graph.py:290)
+    matrix[1] = rng.normal(size=columns)
+    matrix[2] = 0.25                                                            # constant
+    matrix[3] = rng.integers(0, 5, size=columns)                                # five values
+    matrix[4] = rng.normal(size=columns)
+    matrix[4, rng.choice(columns, 200, replace=False)] = 0.5                    # one wide group inside a smooth row
+    matrix[5] = rng.normal(size=columns)
+    matrix[5, 7], matrix[5, 11] = np.inf, -np.inf
+    matrix[6] = np.where(rng.random(columns) < 0.5, 0.0, rng.normal(size=columns))  # half of the row ties at zero
+    matrix[6, 3] = -0.0
+    matrix[7] = rng.exponential(size=columns) ** 4                              # a long tail
+    matrix[8] = np.arange(columns)[::-1]
+    matrix[9] = rng.normal(size=columns) * 1e-30                                # tiny range
+    matrix[10] = np.concatenate([rng.normal(-5, 0.001, columns // 2), rng.normal(5, 0.001, columns - columns // 2)])
+    matrix[11] = np.round(rng.normal(size=columns) * 64) / 64                   # small groups of ties everywhere
+    expected = oracle.rank_matrix(matrix, ascending)
+    actual = matrix.copy()
+    _xt().rank_matrix_float32_t(actual, ascending)
+    for row in range(12):
+        assert np.array_equal(actual[row], expected[row]), row
+
+
 def test_rank_matrix_reference_on_distinct_values(ref):
     """On tie-free rows the result must equal the compiled reference's std::sort ranks."""
     if ref is None:
