@@ -243,12 +243,17 @@ __device__ __forceinline__ int nth_set_bit(uint32_t mask, int n) {
     return position;
 }
 
+// PREFIX_ARRAY: the clear bits before every word are kept in shared memory and a draw is located by a binary search
+// over the words (rows of any size).  Otherwise (rows of up to 64 words per lane) only the clear bits before every
+// LANE's words exist, in a register: a draw finds its lane with five shuffles and walks that lane's few words; half the
+// shared memory per warp, so twice the warps per SM for a kernel that waits on its own dependent chains.
+template <bool PREFIX_ARRAY>
 __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDownsampleParams wp) {
     extern __shared__ uint32_t smem[];
     const DownsampleParams& p = wp.base;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* bitmap = smem + (size_t)warp * 2 * wp.words_capacity;  // bit set = UMI drawn (or padding)
-    uint32_t* free_before = bitmap + wp.words_capacity;              // clear bits in words [0, w)
+    uint32_t* bitmap = smem + (size_t)warp * (PREFIX_ARRAY ? 2 : 1) * wp.words_capacity;  // bit set = UMI drawn (or padding)
+    uint32_t* free_before = bitmap + wp.words_capacity;  // PREFIX_ARRAY only: clear bits in words [0, w)
 
     // a^(lane+1) and a^32
     uint32_t pow_lane = 1, pow_warp = 1;
@@ -313,16 +318,19 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
             state = 1;
 
         for (int first = 0; first < samples; first += 32) {
-            // prefix sums of clear bits per word
+            // prefix sums of clear bits: per word (PREFIX_ARRAY) or per lane
+            uint32_t lane_before;
             {
                 const int begin = min(lane * per_lane, words), end = min(begin + per_lane, words);
                 int sum = 0;
                 for (int w = begin; w < end; ++w) sum += __popc(~bitmap[w]);
                 int running = warp_inclusive_scan(sum, lane) - sum;
-                for (int w = begin; w < end; ++w) {
-                    free_before[w] = (uint32_t)running;
-                    running += __popc(~bitmap[w]);
-                }
+                lane_before = (uint32_t)running;
+                if (PREFIX_ARRAY)
+                    for (int w = begin; w < end; ++w) {
+                        free_before[w] = (uint32_t)running;
+                        running += __popc(~bitmap[w]);
+                    }
             }
             __syncwarp();
             const int draw = first + lane;
@@ -338,18 +346,46 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
                 const uint32_t earlier = __shfl_sync(0xffffffffu, r, j);
                 q += (j < lane && earlier <= q) ? 1u : 0u;
             }
-            if (active) {
-                int left = 0, right = words - 1;  // last word with free_before[w] <= q
-                while (left < right) {
-                    const int middle = (left + right + 1) >> 1;
-                    if (free_before[middle] <= q)
-                        left = middle;
-                    else
-                        right = middle - 1;
+            int word = 0;
+            uint32_t mark = 0;
+            if (PREFIX_ARRAY) {
+                if (active) {
+                    int left = 0, right = words - 1;  // last word with free_before[w] <= q
+                    while (left < right) {
+                        const int middle = (left + right + 1) >> 1;
+                        if (free_before[middle] <= q)
+                            left = middle;
+                        else
+                            right = middle - 1;
+                    }
+                    word = left;
+                    mark = 1u << nth_set_bit(~bitmap[left], (int)(q - free_before[left]));
                 }
-                const int bit = nth_set_bit(~bitmap[left], (int)(q - free_before[left]));
-                atomicOr(&bitmap[left], 1u << bit);
+            } else {
+                // the last lane whose words start at or before rank q (lanes without words start at the row's total)
+                int owner = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const uint32_t before = __shfl_sync(0xffffffffu, lane_before, owner + step);
+                    if (before <= q)
+                        owner += step;
+                }
+                uint32_t inside = q - __shfl_sync(0xffffffffu, lane_before, owner);
+                if (active) {
+                    word = owner * per_lane;
+                    uint32_t clear = ~bitmap[word];
+                    int count = __popc(clear);
+                    while (inside >= (uint32_t)count) {
+                        inside -= (uint32_t)count;
+                        clear = ~bitmap[++word];
+                        count = __popc(clear);
+                    }
+                    mark = 1u << nth_set_bit(clear, (int)inside);
+                }
             }
+            __syncwarp();  // every lane has located its draw in the bitmap of the start of the batch
+            if (active)
+                atomicOr(&bitmap[word], mark);
             __syncwarp();
         }
         if (lane == 0 && (total & 31u))
@@ -437,11 +473,12 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
     }
     const unsigned long long max_words = (max_total + 31) / 32;
     if (max_words <= 28 * 1024) {
-        int capacity = 64;
-        while ((unsigned long long)capacity < max_words) capacity *= 2;
+        const bool prefix_array = max_words > 2048;  // more than 64 words per lane: search words, not lanes
+        const int capacity = (int)((std::max<unsigned long long>(max_words, 64) + 31) / 32 * 32);
+        const int arrays = prefix_array ? 2 : 1;
         int warps = DW_WARPS;
-        while (warps > 1 && (size_t)warps * 2 * capacity * sizeof(uint32_t) > 200 * 1024) warps /= 2;
-        const size_t smem_bytes = (size_t)warps * 2 * capacity * sizeof(uint32_t);
+        while (warps > 1 && (size_t)warps * arrays * capacity * sizeof(uint32_t) > 200 * 1024) warps /= 2;
+        const size_t smem_bytes = (size_t)warps * arrays * capacity * sizeof(uint32_t);
         WarpDownsampleParams wp{};
         wp.base = p;
         wp.words_capacity = capacity;
@@ -449,8 +486,13 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
         int per_sm = (int)std::min<size_t>(16, (220 * 1024) / (smem_bytes + 1024));
         per_sm = std::max(1, std::min(per_sm, 2048 / (warps * 32)));
         const int64_t grid = std::min<int64_t>(ceil_div(rows, warps), (int64_t)sm_count() * per_sm);
-        MCB_CUDA(cudaFuncSetAttribute(downsample_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-        MCB_PROFILED("downsample", stream, downsample_warp_kernel<<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
+        if (prefix_array) {
+            MCB_CUDA(cudaFuncSetAttribute(downsample_warp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            MCB_PROFILED("downsample", stream, downsample_warp_kernel<true><<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
+        } else {
+            MCB_CUDA(cudaFuncSetAttribute(downsample_warp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            MCB_PROFILED("downsample", stream, downsample_warp_kernel<false><<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
+        }
         MCB_LAUNCH_CHECK();
         return MCB_OK;
     }

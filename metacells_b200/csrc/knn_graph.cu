@@ -13,6 +13,8 @@
 //   merge_preserved      knn_graph.py:357-369, 383-388: element-wise maximum with the preserved edge of
 //                        every row and with its transpose.
 //   weigh_edges          knn_graph.py:395-407: divide every row by its float32 sum.
+#include <cmath>
+#include <cstring>
 #include <algorithm>
 
 #include "common.cuh"
@@ -65,6 +67,7 @@ struct BalanceParams {
     float* out_data;
     int32_t* out_indices;
     const int32_t* best_index;     // pass 3: the preserved column of every row
+    float keep_product;            // the largest float32 r_ij * r_ji whose balanced rank passes the threshold (0: none)
 };
 
 __device__ __forceinline__ void tile_of_block(int block, int* tile_i, int* tile_j) {
@@ -77,9 +80,16 @@ __device__ __forceinline__ void tile_of_block(int block, int* tile_i, int* tile_
 }
 
 // t = 2^21 - sqrt(r_ij * r_ji), every step rounded to float32 as numpy does (knn_graph.py:308-317).
-__device__ __forceinline__ float balanced_t(float r_ij, float r_ji) {
-    return __fadd_rn(-__fsqrt_rn(__fmul_rn(r_ij, r_ji)), OFFSET_2_21);
+__device__ __forceinline__ float balanced_t_of_product(float product) { return __fadd_rn(-__fsqrt_rn(product), OFFSET_2_21); }
+__device__ __forceinline__ float balanced_t(float r_ij, float r_ji) { return balanced_t_of_product(__fmul_rn(r_ij, r_ji)); }
+
+// t lies in [2^20, 2^21) (ranks are below 2^20), where float32 steps by 1/8: 23 bits hold it exactly, and with the
+// column inside the tile in the low 6 bits (inverted: numpy's first-maximum rule) a row's best entry of a tile is one
+// 32-bit warp maximum.
+__device__ __forceinline__ uint32_t pack_tile_best(float t, int column_in_tile) {
+    return ((uint32_t)__float2int_rz(__fmul_rn(__fadd_rn(t, -1048576.0f), 8.0f)) << 6) | (uint32_t)(BT - 1 - column_in_tile);
 }
+static_assert(BT == 64, "pack_tile_best keeps the column of a tile in 6 bits");
 
 template <bool FILL>
 __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
@@ -109,32 +119,38 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
             const int64_t row = row0 + r;
             if (row >= n)
                 break;
-            float t[2];
-            bool valid[2], kept[2];
+            // The threshold on the balanced rank (knn_graph.py:333-334) is a threshold on the float32 product: every step
+            // from the product to the comparison is monotone, and the host found the largest product that passes with the
+            // same float32 steps.  Only the entries that pass (a few percent) pay for the square root.
+            float product[2];
+            bool valid[2], passes[2], kept[2];
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
                 const int c = lane + 32 * half;
                 const int64_t column = col0 + c;
                 const float mine = side == 0 ? tile_a[r][c] : tile_b[r][c];
                 const float other = side == 0 ? tile_b[c][r] : tile_a[c][r];
-                t[half] = balanced_t(mine, other);
+                product[half] = __fmul_rn(mine, other);
                 valid[half] = column < n;
-                kept[half] = valid[half] && column != row && __fadd_rn(t[half], p.shift) > 0.0f;  // knn_graph.py:333-334
+                passes[half] = valid[half] && product[half] <= p.keep_product;
+                kept[half] = passes[half] && column != row;
             }
             if (!FILL) {
-                unsigned long long best = 0;
+                // the row's largest t can only be an entry that passes, when there is one (rows without are redone
+                // by balance_best_kernel)
+                uint32_t best = 0;
 #pragma unroll
                 for (int half = 0; half < 2; ++half)
-                    if (valid[half]) {
-                        const unsigned long long packed =
-                            ((unsigned long long)float_to_ordered(t[half]) << 32) | (uint32_t)(~(uint32_t)(col0 + lane + 32 * half));
-                        best = max(best, packed);
-                    }
-                for (int offset = 16; offset > 0; offset >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, offset));
+                    if (passes[half]) best = max(best, pack_tile_best(balanced_t_of_product(product[half]), lane + 32 * half));
+                best = __reduce_max_sync(0xffffffffu, best);
                 const int count = __popc(__ballot_sync(0xffffffffu, kept[0])) + __popc(__ballot_sync(0xffffffffu, kept[1]));
                 if (lane == 0) {
                     p.counts[row * p.tiles + column_tile] = count;
-                    atomicMax(&p.row_best[row], best);
+                    if (best != 0) {
+                        const float t = __fadd_rn(__fmul_rn((float)(best >> 6), 0.125f), 1048576.0f);
+                        const uint32_t column = (uint32_t)(col0 + (BT - 1 - (int)(best & (BT - 1))));
+                        atomicMax(&p.row_best[row], ((unsigned long long)float_to_ordered(t) << 32) | (uint32_t)~column);
+                    }
                 }
             } else {
                 const int64_t preserved = p.best_index[row];
@@ -146,7 +162,7 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                 for (int half = 0; half < 2; ++half)
                     if (kept[half]) {
                         const int64_t column = col0 + lane + 32 * half;
-                        float value = __fadd_rn(t[half], p.shift);
+                        float value = __fadd_rn(balanced_t_of_product(product[half]), p.shift);
                         if (column == preserved)
                             value = fmaxf(value, 1.0f);  // knn_graph.py:331
                         const int64_t at = base + (half ? __popc(mask0) : 0) + __popc((half ? mask1 : mask0) & lower_lanes);
@@ -155,6 +171,26 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                     }
             }
         }
+    }
+}
+
+// Rows none of whose entries pass the threshold (a k that is tiny against the pile): the largest t over the whole row.
+__global__ void __launch_bounds__(256) balance_best_kernel(BalanceParams p) {
+    __shared__ unsigned long long warp_best[8];
+    const int64_t row = blockIdx.x;
+    if (p.row_best[row] != 0)
+        return;
+    unsigned long long best = 0;
+    for (int64_t column = threadIdx.x; column < p.n; column += blockDim.x) {
+        const float t = balanced_t(p.ranks[row * p.n + column], p.ranks[column * p.n + row]);
+        best = max(best, ((unsigned long long)float_to_ordered(t) << 32) | (uint32_t)~(uint32_t)column);
+    }
+    for (int offset = 16; offset > 0; offset >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, offset));
+    if ((threadIdx.x & 31) == 0) warp_best[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) best = max(best, warp_best[w]);
+        p.row_best[row] = best;
     }
 }
 
@@ -370,6 +406,35 @@ struct BalancedRanks {
     int64_t nnz = 0;
 };
 
+// The largest float32 product whose balanced rank passes `2^21 - sqrt(product) + shift > 0`, through the same float32
+// steps as the kernels (and numpy): the steps are monotone, so a bisection over the bit patterns finds it.  Products are
+// at least 1 (ranks start at 1); 0 means that nothing passes.
+static float largest_kept_product(float shift) {
+    auto passes = [shift](uint32_t bits) {
+        float product;
+        memcpy(&product, &bits, sizeof(product));
+        volatile float root = sqrtf(product);
+        volatile float t = OFFSET_2_21 - root;
+        volatile float value = t + shift;
+        return value > 0.0f;
+    };
+    uint32_t low = 0x3f800000u, high = 0x7f000000u;  // 1.0f .. 2^127
+    if (!passes(low))
+        return 0.0f;
+    if (passes(high))
+        low = high;
+    while (low + 1 < high) {
+        const uint32_t middle = low + (high - low) / 2;
+        if (passes(middle))
+            low = middle;
+        else
+            high = middle;
+    }
+    float product;
+    memcpy(&product, &low, sizeof(product));
+    return product;
+}
+
 int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRanks* out, cudaStream_t stream) {
     const int tiles = (int)ceil_div(n, BT);
     const int64_t blocks = (int64_t)tiles * (tiles + 1) / 2;
@@ -387,9 +452,13 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     p.n = n;
     p.tiles = tiles;
     p.shift = shift;
+    p.keep_product = largest_kept_product(shift);
+    MCB_REQUIRE(n < (1 << 20), "balance_ranks: %lld rows are more than the packed row maximum holds", (long long)n);
     p.counts = counts.as<int32_t>();
     p.row_best = row_best.as<unsigned long long>();
     MCB_PROFILED("balance_count", stream, balance_kernel<false><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p));
+    MCB_LAUNCH_CHECK();
+    MCB_PROFILED("balance_best", stream, balance_best_kernel<<<(unsigned)n, 256, 0, stream>>>(p));
     MCB_LAUNCH_CHECK();
     MCB_PROFILED("balance_rows", stream, balance_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(p, row_sizes.as<int32_t>(), out->best_index.as<int32_t>(),
                                                                      out->best_value.as<float>()));

@@ -64,11 +64,12 @@ int prepare_memory_pool() {
 }
 
 void trace_lap(const char* name, cudaStream_t stream) {
-    static const bool enabled = getenv("MCB_TRACE") != nullptr;
-    if (!enabled)
+    static const char* mode = getenv("MCB_TRACE");  // "host": the host's own time between laps, no synchronisation
+    if (mode == nullptr)
         return;
     static thread_local std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
-    cudaStreamSynchronize(stream);
+    if (strcmp(mode, "host") != 0)
+        cudaStreamSynchronize(stream);
     const auto now = std::chrono::steady_clock::now();
     fprintf(stderr, "[mcb trace] %-28s %8.3f ms\n", name, std::chrono::duration<double, std::milli>(now - last).count());
     last = now;
