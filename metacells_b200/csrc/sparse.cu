@@ -66,7 +66,91 @@ struct PruneParams {
     int32_t* out_indices;
     const int32_t* out_indptr;
     int cache_capacity;
+    int warp_limit;  // bands of up to this many entries belong to prune_bands_warp_kernel, wider ones to prune_bands_kernel
 };
+
+// ---- bands that fit a warp's registers (every band of a pile's graph: about a thousand entries) ----------------------
+//
+// One warp per band, no block barriers: the keys sit in registers (entry j * 32 + lane: coalesced), the degree-th
+// smallest key is found by a binary radix select over the bits in which the band's keys differ at all (balanced ranks
+// are multiples of 1/8 below a few thousand: about 15 bits), one warp reduction per bit, and the kept entries are
+// written in their original order with two ballots per 32 entries (equal keys: the first ones, prune_per.cpp:33 modulo
+// the tie rule of the oracle).
+constexpr int PW_MAX_ROUNDS = 64;
+
+template <int ROUNDS>
+__device__ __forceinline__ void prune_band_in_warp(const PruneParams& p, int lo, int n, int out) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lower_lanes = lanemask_lt();
+    const float* values = p.data + lo;
+    const int32_t* indices = p.indices + lo;
+    uint32_t keys[ROUNDS];
+    uint32_t differ = 0;
+    const uint32_t first = sort_key(values[0], false);
+#pragma unroll
+    for (int j = 0; j < ROUNDS; ++j) {
+        const int i = j * 32 + lane;
+        keys[j] = i < n ? sort_key(values[i], false) : first;
+        differ |= keys[j] ^ first;
+    }
+    differ = __reduce_or_sync(0xffffffffu, differ);
+    uint32_t prefix = first & ~differ, known = ~differ;
+    int wanted = p.degree - 1;  // 0-based rank, ascending keys = descending values
+    for (int bit = 31 - __clz((int)(differ | 1u)); bit >= 0; --bit) {
+        if (((differ >> bit) & 1u) == 0)
+            continue;
+        int zeros = 0;
+#pragma unroll
+        for (int j = 0; j < ROUNDS; ++j)
+            zeros += (j * 32 + lane < n && (keys[j] & known) == prefix && ((keys[j] >> bit) & 1u) == 0) ? 1 : 0;
+        zeros = __reduce_add_sync(0xffffffffu, zeros);
+        if (wanted >= zeros) {
+            wanted -= zeros;
+            prefix |= 1u << bit;
+        }
+        known |= 1u << bit;
+    }
+    const uint32_t threshold = prefix;
+    const int ties_wanted = wanted + 1;
+    int kept = 0, ties_seen = 0;
+#pragma unroll
+    for (int j = 0; j < ROUNDS; ++j) {
+        if (j * 32 >= n)
+            break;
+        const int i = j * 32 + lane;
+        const bool valid = i < n;
+        const bool tie = valid && keys[j] == threshold;
+        const uint32_t tie_mask = __ballot_sync(0xffffffffu, tie);
+        const bool keep = valid && (keys[j] < threshold || (tie && ties_seen + __popc(tie_mask & lower_lanes) < ties_wanted));
+        const uint32_t keep_mask = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+            const int slot = out + kept + __popc(keep_mask & lower_lanes);
+            p.out_data[slot] = values[i];
+            p.out_indices[slot] = indices[i];
+        }
+        kept += __popc(keep_mask);
+        ties_seen += __popc(tie_mask);
+    }
+}
+
+__global__ void __launch_bounds__(256) prune_bands_warp_kernel(PruneParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t band = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; band < p.bands; band += warps) {
+        const int lo = p.indptr[band], n = p.indptr[band + 1] - lo;
+        const int out = p.out_indptr[band];
+        if (n <= p.degree) {  // prune_per.cpp:24-28
+            for (int i = lane; i < n; i += 32) {
+                p.out_data[out + i] = p.data[lo + i];
+                p.out_indices[out + i] = p.indices[lo + i];
+            }
+        } else if (n <= 32 * 32) {
+            prune_band_in_warp<32>(p, lo, n, out);
+        } else if (n <= p.warp_limit) {
+            prune_band_in_warp<PW_MAX_ROUNDS>(p, lo, n, out);
+        }
+    }
+}
 
 __global__ void __launch_bounds__(SP_THREADS) prune_bands_kernel(PruneParams p) {
     extern __shared__ __align__(16) uint8_t sp_smem[];
@@ -80,13 +164,8 @@ __global__ void __launch_bounds__(SP_THREADS) prune_bands_kernel(PruneParams p) 
         const int out = p.out_indptr[band];
         const float* values = p.data + lo;
         const int32_t* indices = p.indices + lo;
-        if (n <= p.degree) {  // prune_per.cpp:24-28
-            for (int i = tid; i < n; i += SP_THREADS) {
-                p.out_data[out + i] = values[i];
-                p.out_indices[out + i] = indices[i];
-            }
-            continue;
-        }
+        if (n <= p.degree || n <= p.warp_limit)
+            continue;  // prune_bands_warp_kernel's
         const bool cached = n <= p.cache_capacity;
         if (cached) {
             for (int i = tid; i < n; i += SP_THREADS) cache[i] = sort_key(values[i], false);
@@ -238,9 +317,13 @@ int collect_pruned_launch(int64_t degree, const float* data, const int32_t* indi
     p.out_indices = out_indices;
     p.out_indptr = out_indptr;
     p.cache_capacity = 8192;
+    p.warp_limit = PW_MAX_ROUNDS * 32;
     const size_t smem_bytes = (size_t)p.cache_capacity * 4;
+    const int64_t warp_grid = std::min<int64_t>(ceil_div(bands * 32, 256), (int64_t)sm_count() * 8);
+    MCB_PROFILED("prune_bands", stream, prune_bands_warp_kernel<<<(unsigned)warp_grid, 256, 0, stream>>>(p));
+    MCB_LAUNCH_CHECK();
     const int64_t grid = std::min<int64_t>(bands, (int64_t)sm_count() * 6);
-    MCB_PROFILED("prune_bands", stream, prune_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(p));
+    MCB_PROFILED("prune_wide_bands", stream, prune_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(p));
     MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
