@@ -187,6 +187,12 @@ int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_
  * Sizes the downsampling scratch without a pass over the data and a synchronisation; a cell above it is
  * reported by the next synchronising call on the pile. */
 int mcb_pile_set_max_cell_total(mcb_pile* pile, uint64_t max_total);
+/* Page-lock / release a host buffer (cudaHostRegister).  mcb_pile_create_host returns before the upload has finished
+ * only for page-locked buffers; a caller that walks over many piles (ut.parallel_map over piles,
+ * pipeline/divide_and_conquer.py:1264-1295) pins the arrays of the next pile and creates it before it asks for the graph
+ * of the current one, so that the upload runs under the current pile's kernels. */
+int mcb_host_pin(const void* buffer, uint64_t bytes);
+int mcb_host_unpin(const void* buffer);
 int mcb_pile_create_dev(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
                         void* stream, mcb_pile** out);
 int64_t mcb_pile_nnz(const mcb_pile* pile);

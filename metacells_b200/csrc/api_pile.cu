@@ -147,6 +147,19 @@ int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_
     return MCB_OK;
 }
 
+int mcb_host_pin(const void* buffer, uint64_t bytes) {
+    MCB_REQUIRE(buffer != nullptr || bytes == 0, "host_pin: null buffer");
+    if (bytes > 0)
+        MCB_CUDA(cudaHostRegister(const_cast<void*>(buffer), (size_t)bytes, cudaHostRegisterDefault));
+    return MCB_OK;
+}
+
+int mcb_host_unpin(const void* buffer) {
+    if (buffer != nullptr)
+        MCB_CUDA(cudaHostUnregister(const_cast<void*>(buffer)));
+    return MCB_OK;
+}
+
 int mcb_pile_set_max_cell_total(mcb_pile* pile, uint64_t max_total) {
     MCB_REQUIRE(pile != nullptr, "pile: null handle");
     pile->max_row_total = max_total;

@@ -9,7 +9,7 @@ correlated, ranked, balanced and pruned in HBM, and only the graph comes back.
 from __future__ import annotations
 
 import ctypes
-from typing import Optional, Tuple
+from typing import Iterable, Iterator, Optional, Tuple
 
 import numpy as np
 import scipy.sparse as sp
@@ -54,15 +54,22 @@ def _ptr(array: np.ndarray) -> ctypes.c_void_p:
 class Pile:
     """A device-resident pile (cells x genes UMI CSR matrix)."""
 
-    def __init__(self, umis: sp.csr_matrix, *, max_cell_total: Optional[float] = None):
+    def __init__(self, umis: sp.csr_matrix, *, max_cell_total: Optional[float] = None, pin: bool = False):
         """``max_cell_total``: the largest total of a cell when the caller has the totals anyway
         (tools/downsample.py:84-90 needs them for the samples count); lets the downsampling start chunk by chunk
-        under the upload without a pass over the data."""
+        under the upload without a pass over the data.  ``pin``: page-lock the arrays for the life of the pile, so that
+        the constructor returns while the upload is still running (see ``compute_piles_knn_graphs``)."""
         umis = sp.csr_matrix(umis)
         self._data = np.ascontiguousarray(umis.data, dtype="float32")
         self._indices = np.ascontiguousarray(umis.indices, dtype="int32")
         self._indptr = np.ascontiguousarray(umis.indptr, dtype="int32")
         self.shape = umis.shape
+        self._pinned = []
+        if pin:
+            for array in (self._data, self._indices, self._indptr):
+                if array.nbytes:
+                    check(lib().mcb_host_pin(_ptr(array), ctypes.c_uint64(array.nbytes)))
+                    self._pinned.append(array)
         self._handle = ctypes.c_void_p()
         function = lib().mcb_pile_create_host
         function.restype = ctypes.c_int
@@ -76,8 +83,11 @@ class Pile:
 
     def close(self) -> None:
         if getattr(self, "_handle", None):
-            lib().mcb_pile_free(self._handle)
+            lib().mcb_pile_free(self._handle)  # waits for the upload
             self._handle = None
+        for array in getattr(self, "_pinned", []):
+            lib().mcb_host_unpin(_ptr(array))
+        self._pinned = []
 
     def __del__(self):
         self.close()
@@ -174,3 +184,41 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
         finally:
             graph.close()
     return weights, details
+
+
+def compute_piles_knn_graphs(piles: Iterable[sp.csr_matrix], *, features: int = 2000, random_seed: int = 123456,
+                             pin: bool = True) -> Iterator[Tuple[sp.csr_matrix, dict]]:
+    """``compute_pile_knn_graph`` over the piles of one GPU, one after the other as ``ut.parallel_map`` hands them to a
+    worker (pipeline/divide_and_conquer.py:1264-1295; every pile gets the same ``random_seed``, :1274-1279), with the
+    upload of pile k + 1 started before the graph of pile k is asked for: it runs on the pile's copy stream under the
+    kernels of pile k.  Yields ``(obs_outgoing_weights, details)`` per pile, in order; results do not depend on the
+    overlap."""
+
+    def start(umis: sp.csr_matrix):
+        cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+        return Pile(umis, max_cell_total=float(cell_umis.max(initial=0)), pin=pin), cell_umis
+
+    iterator = iter(piles)
+    try:
+        pending = start(next(iterator))
+    except StopIteration:
+        return
+    while pending is not None:
+        pile, cell_umis = pending
+        try:
+            following = next(iterator, None)
+            pending = start(following) if following is not None else None
+            samples = int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(cell_umis, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
+                                    np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
+            k = knn_k_of_pile(pile.shape[0], cell_umis)
+            pile.downsample(samples, random_seed)
+            feature_genes = pile.select_top_genes(features)
+            graph = pile.knn_graph(None, k=k)
+            try:
+                weights, pruned = graph.to_scipy()
+                details = {"k": graph.k, "samples": samples, "feature_genes": feature_genes, "pruned_ranks": pruned}
+            finally:
+                graph.close()
+        finally:
+            pile.close()
+        yield weights, details

@@ -273,3 +273,23 @@ def test_pile_feature_genes_selected_on_device():
     similarity = tl.compute_obs_obs_similarity(dense)
     separate = tl.compute_obs_obs_knn_graph(similarity, k=15)
     assert np.array_equal(weights.indices, separate.indices) and np.array_equal(weights.data, separate.data)
+
+
+@pytest.mark.parametrize("pin", [True, False])
+def test_piles_one_after_the_other_match_the_single_pile_path(pin):
+    """`compute_piles_knn_graphs` starts the upload of the next pile before it asks for the graph of the current one;
+    the graphs must be the ones `compute_pile_knn_graph` builds pile by pile (and an empty list yields nothing)."""
+    from synth import synth_umis
+
+    from metacells_b200 import pipeline
+
+    piles = [synth_umis(cells, 3000, seed=20 + cells) for cells in (400, 650, 300, 512)]
+    assert list(pipeline.compute_piles_knn_graphs([], features=300)) == []
+    together = list(pipeline.compute_piles_knn_graphs(iter(piles), features=300, pin=pin))
+    assert len(together) == len(piles)
+    for umis, (weights, details) in zip(piles, together):
+        alone, alone_details = pipeline.compute_pile_knn_graph(umis, features=300)
+        assert details["k"] == alone_details["k"] and details["samples"] == alone_details["samples"]
+        assert np.array_equal(details["feature_genes"], alone_details["feature_genes"])
+        assert np.array_equal(weights.indptr, alone.indptr) and np.array_equal(weights.indices, alone.indices)
+        assert np.array_equal(weights.data, alone.data)
