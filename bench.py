@@ -250,12 +250,15 @@ def run_gpu_arm(args):
               "indptr": torch.empty(cells + 1, dtype=torch.int32).pin_memory()}
     stream = torch.cuda.current_stream(device)
 
-    def hot_path(pile, k=k):
-        """The path on an existing pile handle; returns the graph handle."""
+    def hot_path(pile, k=k, meanwhile=None):
+        """The path on an existing pile handle; returns the graph handle.  `meanwhile` runs on the host after the
+        first (asynchronous) launches: the pipelined legs start the next pile's upload there."""
         library.call("mcb_pile_set_max_cell_total", pile, ctypes.c_uint64(max_cell_total))
         library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
         # feature genes: the largest downsampled totals (stand-in for pipeline/select.py), selected on the device
         library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)
+        if meanwhile is not None:
+            meanwhile()
         graph = ctypes.c_void_p()
         outside = ctypes.c_int(0)
         library.call("mcb_pile_knn_graph", pile, None, ctypes.c_int64(args.features),
@@ -282,10 +285,10 @@ def run_gpu_arm(args):
                      p(pinned["indptr"].data_ptr()), ctypes.c_int64(cells), ctypes.c_int64(genes), ctypes.byref(pile))
         return pile
 
-    def step_e2e(pile=None):
+    def step_e2e(pile=None, meanwhile=None):
         if pile is None:
             pile = upload()
-        graph = hot_path(pile)
+        graph = hot_path(pile, meanwhile=meanwhile)
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
             raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
@@ -307,10 +310,13 @@ def run_gpu_arm(args):
         under them on the copy stream.  Every step still uploads its pile and reads its graph back inside the timed
         region; only the first upload is exposed."""
         nnz = 0
-        pending = upload()
+        pending = [upload()]
+
+        def start_next():
+            pending.append(upload())
+
         for index in range(steps):
-            pile, pending = pending, (upload() if index + 1 < steps else None)
-            nnz = step_e2e(pile)
+            nnz = step_e2e(pending.pop(0), meanwhile=start_next if index + 1 < steps else None)
         return nnz
 
     def timed(step, steps, whole_run=False):
@@ -474,10 +480,10 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
                      p(pinned["indptr"].data_ptr()), ctypes.c_int64(size), ctypes.c_int64(genes), ctypes.byref(pile))
         return pile
 
-    def one_pile(size, pile=None):
+    def one_pile(size, pile=None, meanwhile=None):
         if pile is None:
             pile = upload(size)
-        graph = hot_path(pile, ks[size])
+        graph = hot_path(pile, ks[size], meanwhile)
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
             raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
@@ -494,10 +500,11 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
     start = time.perf_counter()
     begin.record(stream)
     edges = 0
-    pending = upload(int(sizes[mine[0]])) if mine else None
+    pending = [upload(int(sizes[mine[0]]))] if mine else []
     for index, pile in enumerate(mine):  # the next pile's upload runs under this pile's kernels
-        current, pending = pending, (upload(int(sizes[mine[index + 1]])) if index + 1 < len(mine) else None)
-        edges += one_pile(int(sizes[pile]), current)
+        following = int(sizes[mine[index + 1]]) if index + 1 < len(mine) else None
+        edges += one_pile(int(sizes[pile]), pending.pop(0),
+                          (lambda size=following: pending.append(upload(size))) if following is not None else None)
     end.record(stream)
     barrier()
     wall = time.perf_counter() - start

@@ -187,12 +187,14 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
 
 
 def compute_piles_knn_graphs(piles: Iterable[sp.csr_matrix], *, features: int = 2000, random_seed: int = 123456,
-                             pin: bool = True) -> Iterator[Tuple[sp.csr_matrix, dict]]:
+                             pin: bool = False) -> Iterator[Tuple[sp.csr_matrix, dict]]:
     """``compute_pile_knn_graph`` over the piles of one GPU, one after the other as ``ut.parallel_map`` hands them to a
     worker (pipeline/divide_and_conquer.py:1264-1295; every pile gets the same ``random_seed``, :1274-1279), with the
     upload of pile k + 1 started before the graph of pile k is asked for: it runs on the pile's copy stream under the
-    kernels of pile k.  Yields ``(obs_outgoing_weights, details)`` per pile, in order; results do not depend on the
-    overlap."""
+    kernels of pile k when the pile's arrays are page-locked (``mcb_pile_create_host`` copies from pageable memory
+    synchronously).  ``pin=True`` page-locks the arrays of every pile for its lifetime; that costs more than it saves
+    unless the arrays are reused, so a caller that streams piles keeps them in page-locked buffers of its own.
+    Yields ``(obs_outgoing_weights, details)`` per pile, in order; results do not depend on the overlap."""
 
     def start(umis: sp.csr_matrix):
         cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
