@@ -22,8 +22,8 @@ _lib: Optional[ctypes.CDLL] = None
 
 
 def build(force: bool = False) -> str:
-    """Compile mc_oracle.c + mc_partitions.c with gcc (seconds).  Building the checker is not using it."""
-    sources = [os.path.join(_HERE, name) for name in ("mc_oracle.c", "mc_partitions.c")]
+    """Compile mc_oracle.c + mc_partitions.c + mc_seeds.c with gcc (seconds).  Building the checker is not using it."""
+    sources = [os.path.join(_HERE, name) for name in ("mc_oracle.c", "mc_partitions.c", "mc_seeds.c")]
     newest = max(os.path.getmtime(src) for src in sources)
     if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < newest:
         cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
@@ -341,6 +341,38 @@ def score_partitions(outgoing: sp.csr_matrix, incoming: sp.csc_matrix, mass_of_n
         raise ReferenceAssert("score_partitions: a FastAssert of the reference fails on this input")
     _check(status)
     return score.value
+
+
+def choose_seeds(outgoing: sp.csr_matrix, incoming: sp.csc_matrix, random_seed: int, max_seeds_count: int,
+                 min_seed_size_quantile: float, max_seed_size_quantile: float, seed_of_nodes: np.ndarray) -> int:
+    """choose_seeds.cpp:264-372; ``seed_of_nodes`` (int32, -1 = no seed yet) is filled in place, the number of
+    seeds is returned."""
+    count = ctypes.c_int64()
+    function = lib().mco_choose_seeds
+    function.restype = ctypes.c_int
+    status = function(*_partition_args(outgoing, incoming), _u64(random_seed), _i64(max_seeds_count),
+                      ctypes.c_float(min_seed_size_quantile), ctypes.c_float(max_seed_size_quantile),
+                      _p(seed_of_nodes, "int32"), ctypes.byref(count))
+    if status == 2:
+        raise ReferenceAssert("choose_seeds: a FastAssert of the reference fails on this input")
+    _check(status)
+    return count.value
+
+
+def std_nth_element(keys: np.ndarray, first: int, nth: int, last: int, positions: Optional[np.ndarray] = None) -> np.ndarray:
+    """``std::nth_element`` (libstdc++ 13) over positions compared by ``keys[position]``; returns the positions."""
+    keys = np.ascontiguousarray(keys, dtype="int64")
+    positions = np.arange(len(keys), dtype="int64") if positions is None else positions
+    lib().mco_nth_element_positions(_p(positions, "int64"), _p(keys, "int64"), _i64(first), _i64(nth), _i64(last))
+    return positions
+
+
+def std_sort(keys: np.ndarray) -> np.ndarray:
+    """``std::sort`` (libstdc++ 13) of ``iota(len(keys))`` compared by ``keys[position]``; returns the positions."""
+    keys = np.ascontiguousarray(keys, dtype="int64")
+    positions = np.arange(len(keys), dtype="int64")
+    lib().mco_sort_positions(_p(positions, "int64"), _p(keys, "int64"), _i64(len(keys)))
+    return positions
 
 
 def glibc_log(values: np.ndarray) -> np.ndarray:
