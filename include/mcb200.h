@@ -220,6 +220,26 @@ int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t fea
                        int* outside_table, mcb_graph** out);
 void mcb_pile_free(mcb_pile* pile);
 
+/* ---- choose_seeds.cpp --------------------------------------------------------------------------- */
+
+/* choose_seeds (choose_seeds.cpp:264-372; bound as xt.choose_seeds, tools/candidates.py:733-745).  The graph is
+ * given twice, as outgoing CSR and incoming CSC (float32 data, sorted int32 indices, int32 indptr of nodes + 1
+ * entries, the one the transpose of the other).  seed_of_nodes int32[nodes]: on entry the seeds already given
+ * (-1 = none), on return the seed of every node; *seeds_count receives the value the reference returns.
+ * Bit-identical to the reference for a given random_seed: std::minstd_rand, uniform_real_distribution and the
+ * element order libstdc++'s std::nth_element / std::sort leave behind are reproduced.  Where the reference's
+ * FastAssert would exit(1), returns MCB_ERR_ARG with the text in mcb_last_error().  At most 65535 nodes and
+ * 16384 seeds. */
+int mcb_host_choose_seeds(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
+                          const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,
+                          int64_t nodes, uint64_t random_seed, int64_t max_seeds_count, float min_seed_size_quantile,
+                          float max_seed_size_quantile, int32_t* seed_of_nodes, int64_t* seeds_count);
+/* As above on device arrays (seeds_count stays a host pointer); synchronises the stream. */
+int mcb_dev_choose_seeds(const float* outgoing_weights, const int32_t* outgoing_indices, const int32_t* outgoing_indptr,
+                         const float* incoming_weights, const int32_t* incoming_indices, const int32_t* incoming_indptr,
+                         int64_t nodes, uint64_t random_seed, int64_t max_seeds_count, float min_seed_size_quantile,
+                         float max_seed_size_quantile, int32_t* seed_of_nodes, int64_t* seeds_count, void* stream);
+
 /* ---- partitions.cpp ----------------------------------------------------------------------------- */
 
 /* optimize_partitions (partitions.cpp:1234-1302; bound as xt.optimize_partitions, tools/candidates.py:853-873).

@@ -239,6 +239,26 @@ def score_partitions(outgoing_weights, outgoing_indices, outgoing_indptr, incomi
                     ("int", int(bool(with_orphans))))
 
 
+# ---- choose_seeds.cpp -------------------------------------------------------------------------
+
+
+def choose_seeds(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices, incoming_indptr,
+                 random_seed, max_seeds_count, min_seed_size_quantile, max_seed_size_quantile, seed_of_nodes):
+    """choose_seeds.cpp:264-372 (called at tools/candidates.py:733-745): ``seed_of_nodes`` (-1 = no seed yet) is
+    filled in place, the number of seeds is returned."""
+    import ctypes
+
+    nodes, graph = _graph_arguments(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_weights, incoming_indices,
+                                    incoming_indptr)
+    if len(seed_of_nodes) != nodes:
+        raise ValueError("seed_of_nodes must have one entry per node")
+    count = ctypes.c_int64(0)
+    call("mcb_host_choose_seeds", *graph, ("u64", int(random_seed)), ("i64", int(max_seeds_count)),
+         ("f32", float(min_seed_size_quantile)), ("f32", float(max_seed_size_quantile)),
+         host_ptr(seed_of_nodes, "int32", "seed_of_nodes", True), ("ptr", ctypes.addressof(count)))
+    return count.value
+
+
 def glibc_log(values):
     """glibc's double ``log`` evaluated on the device (what the partition scores are built from)."""
     values = np.ascontiguousarray(values, dtype="float64")

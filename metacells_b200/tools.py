@@ -20,7 +20,8 @@ from . import utilities as ut
 from ._lib import call, check, host_ptr, lib, row_stride
 
 __all__ = ["downsample_cells", "compute_obs_obs_similarity", "compute_obs_obs_similarity_top", "row_block_of_rank",
-           "compute_obs_obs_knn_graph", "KnnGraph", "compute_query_atlas_candidates", "PROJECT_CANDIDATES_COUNT"]
+           "compute_obs_obs_knn_graph", "KnnGraph", "compute_query_atlas_candidates", "PROJECT_CANDIDATES_COUNT",
+           "choose_seeds", "optimize_partitions"]
 
 # metacells/parameters.py
 DOWNSAMPLE_MIN_SAMPLES = 750
@@ -31,6 +32,10 @@ KNN_INCOMING_DEGREE_FACTOR = 3.0
 KNN_OUTGOING_DEGREE_FACTOR = 1.0
 KNN_MIN_OUTGOING_DEGREE = 2
 PROJECT_CANDIDATES_COUNT = 50
+MIN_SEED_SIZE_QUANTILE = 0.85
+MAX_SEED_SIZE_QUANTILE = 0.95
+COOLDOWN_PASS = 0.02
+COOLDOWN_NODE = 0.25
 
 
 def downsample_cells(umis, *, downsample_min_cell_quantile: float = DOWNSAMPLE_MIN_CELL_QUANTILE,
@@ -260,3 +265,60 @@ def compute_query_atlas_candidates(query_data: np.ndarray, atlas_data: np.ndarra
          host_ptr(atlas, "float32", "atlas"), ("i64", atlas.shape[0]), ("i64", row_stride(atlas)), ("i64", query.shape[1]),
          ("i64", count), host_ptr(indices, "int32", "indices", True), host_ptr(correlations, "float32", "correlations", True))
     return indices, correlations
+
+
+def _both_layouts(edge_weights):
+    """The outgoing CSR and the incoming CSC of a graph (``ut.to_layout(..., "column_major")`` of candidates.py:696)."""
+    from . import extensions as xt  # noqa: F401  (fail early when the library is missing)
+
+    outgoing = sp.csr_matrix(edge_weights)
+    if outgoing.dtype != np.float32 or outgoing.indices.dtype != np.int32 or outgoing.indptr.dtype != np.int32:
+        outgoing = sp.csr_matrix((outgoing.data.astype("float32"), outgoing.indices.astype("int32"),
+                                  outgoing.indptr.astype("int32")), shape=outgoing.shape)
+    if outgoing.shape[0] != outgoing.shape[1]:
+        raise ValueError("edge_weights must be square")
+    outgoing.sort_indices()
+    incoming = ut.relayout_compressed(outgoing)  # the CSR of the transpose = the CSC of the graph, on the GPU
+    return outgoing, incoming
+
+
+def choose_seeds(*, edge_weights, seed_of_cells: Optional[np.ndarray] = None, max_seeds_count: int,
+                 min_seed_size_quantile: float = MIN_SEED_SIZE_QUANTILE, max_seed_size_quantile: float = MAX_SEED_SIZE_QUANTILE,
+                 random_seed: int) -> np.ndarray:
+    """tools/candidates.py:653-716: the initial assignment of cells to seeds.  ``seed_of_cells`` (int32, negative =
+    no seed), when given, is completed in place and returned; otherwise a new vector is."""
+    from . import extensions as xt
+
+    outgoing, incoming = _both_layouts(edge_weights)
+    size = outgoing.shape[0]
+    if seed_of_cells is None:
+        seed_of_cells = np.full(size, -1, dtype="int32")
+    elif seed_of_cells.dtype != np.int32 or len(seed_of_cells) != size:
+        raise ValueError("seed_of_cells must be int32 with one entry per cell")
+    xt.choose_seeds(outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices, incoming.indptr,
+                    random_seed, max_seeds_count, min_seed_size_quantile, max_seed_size_quantile, seed_of_cells)
+    return seed_of_cells
+
+
+def optimize_partitions(*, edge_weights, community_of_nodes: np.ndarray, node_umis: np.ndarray, low_partition_umis: int,
+                        target_partition_umis: int, high_partition_umis: int, low_partition_size: int,
+                        target_partition_size: int, high_partition_size: int, cooldown_pass: float = COOLDOWN_PASS,
+                        cooldown_node: float = COOLDOWN_NODE, random_seed: int) -> float:
+    """tools/candidates.py:752-830: ``community_of_nodes`` is optimised in place, the score is returned (every
+    community hot, ``cold_temperature = cooldown_pass`` as :823-829)."""
+    from . import extensions as xt
+
+    if not (0 < low_partition_size < target_partition_size < high_partition_size):
+        raise ValueError("partition sizes must be 0 < low < target < high")
+    if not (0 < low_partition_umis < target_partition_umis < high_partition_umis):
+        raise ValueError("partition UMIs must be 0 < low < target < high")
+    outgoing, incoming = _both_layouts(edge_weights)
+    communities_count = int(np.max(community_of_nodes)) + 1
+    if communities_count <= 0:
+        raise ValueError("community_of_nodes holds no community")
+    hot_mask = np.ones(max(communities_count, 2), dtype="int8")
+    return xt.optimize_partitions(outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices,
+                                  incoming.indptr, random_seed, np.ascontiguousarray(node_umis, dtype="float32"),
+                                  float(low_partition_umis), float(target_partition_umis), float(high_partition_umis),
+                                  float(low_partition_size), float(target_partition_size), float(high_partition_size),
+                                  cooldown_pass, cooldown_node, community_of_nodes, hot_mask, cooldown_pass)
