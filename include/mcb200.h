@@ -37,6 +37,9 @@ int mcb_device_count(void);
 /* Select the CUDA device of the calling thread; fails unless it is compute capability 10.x. */
 int mcb_set_device(int device);
 int mcb_synchronize(void* stream);
+/* Streaming multiprocessors of the calling thread's device: how many one-CTA optimisations (mcb_host_choose_seeds,
+ * mcb_host_optimize_partitions, each on its caller thread's own stream) run side by side. */
+int mcb_device_sm_count(int* count);
 /* Number of kernels this library has launched in the calling process so far. */
 long long mcb_launch_count(void);
 /* Optional per-kernel timing: when enabled every launch is bracketed by CUDA events on its own

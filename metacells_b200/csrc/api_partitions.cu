@@ -38,6 +38,7 @@ int partitions_host(const float* out_w, const int32_t* out_idx, const int32_t* o
     MCB_REQUIRE(out_ptr[0] == 0 && in_ptr[0] == 0, "optimize_partitions: indptr[0] must be 0");
     const size_t out_edges = size_t(out_ptr[nodes]), in_edges = size_t(in_ptr[nodes]);
     cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
     Scratch d_out_w, d_out_idx, d_out_ptr, d_in_w, d_in_idx, d_in_ptr, d_mass, d_partition, d_mask;
     MCB_TRY(upload(d_out_w, out_w, out_edges, stream));
     MCB_TRY(upload(d_out_idx, out_idx, out_edges, stream));

@@ -34,6 +34,7 @@ int mcb_host_choose_seeds(const float* outgoing_weights, const int32_t* outgoing
     MCB_REQUIRE(outgoing_indptr[0] == 0 && incoming_indptr[0] == 0, "choose_seeds: indptr[0] must be 0");
     const size_t out_edges = size_t(outgoing_indptr[nodes]), in_edges = size_t(incoming_indptr[nodes]);
     cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
     Scratch d_out_w, d_out_idx, d_out_ptr, d_in_w, d_in_idx, d_in_ptr, d_seeds;
     MCB_TRY(upload(d_out_w, outgoing_weights, out_edges, stream));
     MCB_TRY(upload(d_out_idx, outgoing_indices, out_edges, stream));

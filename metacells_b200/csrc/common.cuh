@@ -82,6 +82,7 @@ struct Scratch {
 };
 
 int sm_count();
+int thread_stream(cudaStream_t* stream);  // the calling host thread's own stream on the current device
 // Developer aid: with MCB_TRACE=1 in the environment, synchronises `stream` and prints the host time
 // since the previous call on stderr.
 void trace_lap(const char* name, cudaStream_t stream);

@@ -63,6 +63,19 @@ int prepare_memory_pool() {
     return MCB_OK;
 }
 
+// A stream of the calling host thread's own (per device): host entry points that may be called from several
+// threads at once (one pile each) run side by side instead of queueing on the legacy default stream.
+int thread_stream(cudaStream_t* stream) {
+    static thread_local cudaStream_t streams[64] = {};
+    int device = 0;
+    MCB_CUDA(cudaGetDevice(&device));
+    cudaStream_t& mine = streams[device & 63];
+    if (mine == nullptr)
+        MCB_CUDA(cudaStreamCreateWithFlags(&mine, cudaStreamNonBlocking));
+    *stream = mine;
+    return MCB_OK;
+}
+
 void trace_lap(const char* name, cudaStream_t stream) {
     static const char* mode = getenv("MCB_TRACE");  // "host": the host's own time between laps, no synchronisation
     if (mode == nullptr)
@@ -103,6 +116,12 @@ ProfileScope::~ProfileScope() {
 extern "C" {
 
 long long mcb_launch_count(void) { return mcb::g_launches.load(); }
+
+int mcb_device_sm_count(int* count) {
+    MCB_REQUIRE(count != nullptr, "mcb_device_sm_count: null argument");
+    *count = mcb::sm_count();
+    return *count > 0 ? MCB_OK : mcb::fail(MCB_ERR_CUDA, "mcb_device_sm_count: no device");
+}
 
 int mcb_profile_enable(int enable) {
     mcb::g_profile.store(enable ? 1 : 0);

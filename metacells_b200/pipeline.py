@@ -17,7 +17,8 @@ import scipy.sparse as sp
 from . import tools as tl
 from ._lib import check, lib
 
-__all__ = ["Pile", "compute_pile_knn_graph", "knn_k_of_pile", "log_fraction_table"]
+__all__ = ["Pile", "compute_pile_knn_graph", "knn_k_of_pile", "log_fraction_table", "compute_pile_seed_partition",
+           "compute_piles_seed_partitions", "metacell_bounds", "seeds_count_for"]
 
 # metacells/parameters.py
 CELLS_SIMILARITY_VALUE_REGULARIZATION = 1 / 7
@@ -26,6 +27,9 @@ TARGET_METACELL_UMIS = 160000
 KNN_K_SIZE_FACTOR = 2.0
 KNN_K_UMIS_QUANTILE = 0.1
 MIN_KNN_K = 30
+MIN_METACELL_SIZE = 12
+CANDIDATES_MIN_SPLIT_SIZE_FACTOR = 2.0
+CANDIDATES_MAX_MERGE_SIZE_FACTOR = 0.5
 
 
 def log_fraction_table(max_count: int, regularization: float = CELLS_SIMILARITY_VALUE_REGULARIZATION) -> np.ndarray:
@@ -224,3 +228,77 @@ def compute_piles_knn_graphs(piles: Iterable[sp.csr_matrix], *, features: int = 
         finally:
             pile.close()
         yield weights, details
+
+
+def metacell_bounds(*, target_metacell_size: int = TARGET_METACELL_SIZE, target_metacell_umis: int = TARGET_METACELL_UMIS,
+                    min_metacell_size: int = MIN_METACELL_SIZE, min_split_size_factor: float = CANDIDATES_MIN_SPLIT_SIZE_FACTOR,
+                    max_merge_size_factor: float = CANDIDATES_MAX_MERGE_SIZE_FACTOR):
+    """tools/candidates.py:151-160: ``(min_metacell_umis, target_metacell_umis, max_metacell_umis, min_metacell_size,
+    target_metacell_size, max_metacell_size)``, the bounds ``optimize_partitions`` takes."""
+    import math
+
+    min_umis = int(math.floor(target_metacell_umis * max_merge_size_factor))
+    max_umis = int(math.ceil(target_metacell_umis * min_split_size_factor)) - 1
+    min_size = max(min_metacell_size, int(math.floor(target_metacell_size * max_merge_size_factor)))
+    max_size = max(int(math.ceil(target_metacell_size * min_split_size_factor)) - 1, min_size + 1)
+    return float(min_umis), float(target_metacell_umis), float(max_umis), float(min_size), float(target_metacell_size), float(max_size)
+
+
+def seeds_count_for(total_umis: float, total_size: int, bounds) -> int:
+    """tools/candidates.py:286-322 (``_seeds_count_for``)."""
+    import math
+
+    min_umis, _, max_umis, min_size, _, max_size = bounds
+    least_by_umis, most_by_umis = int(math.ceil(total_umis / max_umis)), int(math.ceil(total_umis / min_umis))
+    least_by_size, most_by_size = int(math.ceil(total_size / max_size)), int(math.ceil(total_size / min_size))
+    if most_by_size < least_by_umis:
+        return int(round((most_by_size + least_by_umis) / 2))
+    if most_by_umis < least_by_size:
+        return int(round((most_by_umis + least_by_size) / 2))
+    return int(round((max(least_by_size, least_by_umis) + min(most_by_size, most_by_umis)) / 2))
+
+
+def compute_pile_seed_partition(edge_weights: sp.csr_matrix, cell_umis: np.ndarray, *, random_seed: int = 123456,
+                                min_seed_size_quantile: float = tl.MIN_SEED_SIZE_QUANTILE,
+                                max_seed_size_quantile: float = tl.MAX_SEED_SIZE_QUANTILE,
+                                cooldown_pass: float = tl.COOLDOWN_PASS, cooldown_node: float = tl.COOLDOWN_NODE,
+                                **bounds_arguments) -> Tuple[np.ndarray, float, int]:
+    """The opening of ``compute_candidate_metacells`` for one pile (tools/candidates.py:128-196 and the first
+    ``_optimize_partitions`` of ``_reduce_communities``, :351-368): the seeds count from the pile's UMIs, ``choose_seeds``,
+    then ``optimize_partitions`` with every community hot and ``cold_temperature = 1 - cooldown_pass``.  Both run on the
+    GPU, one CTA each, on the calling thread's own stream.  Returns ``(community_of_nodes, score, seeds_count)``.
+    The split / min-cut rounds that follow in the reference (:370-407; ``igraph``) stay with the caller."""
+    from . import extensions as xt
+
+    outgoing, incoming = tl._both_layouts(edge_weights)
+    cell_umis = np.ascontiguousarray(cell_umis, dtype="float32")
+    bounds = metacell_bounds(**bounds_arguments)
+    total_umis = float(sum(cell_umis))  # candidates.py:162: Python's left-to-right sum of float32 values
+    wanted = seeds_count_for(total_umis, outgoing.shape[0], bounds)
+    community_of_nodes = np.full(outgoing.shape[0], -1, dtype="int32")
+    graph = (outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices, incoming.indptr)
+    seeds_count = xt.choose_seeds(*graph, random_seed, wanted, min_seed_size_quantile, max_seed_size_quantile,
+                                  community_of_nodes)
+    hot_mask = np.ones(max(seeds_count, 2), dtype="int8")
+    score = xt.optimize_partitions(*graph, random_seed, cell_umis, *bounds, cooldown_pass, cooldown_node, community_of_nodes,
+                                   hot_mask, 1 - cooldown_pass)
+    return community_of_nodes, score, seeds_count
+
+
+def compute_piles_seed_partitions(piles, *, workers: Optional[int] = None, **arguments):
+    """``compute_pile_seed_partition`` for ``(edge_weights, cell_umis)`` pairs, side by side: the seed chooser and the
+    partition optimiser are one persistent CTA each, so every pile takes one SM and up to ``workers`` (default: one per
+    SM, at most one per pile) run at once, each on the stream of the host thread that drives it (the entry points
+    release the GIL).  The reference runs its piles in forked processes, one core each
+    (pipeline/divide_and_conquer.py:1291-1295).  Results are in the order of ``piles`` and do not depend on ``workers``."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    piles = list(piles)
+    if not piles:
+        return []
+    if workers is None:
+        count = ctypes.c_int(0)
+        check(lib().mcb_device_sm_count(ctypes.byref(count)))
+        workers = count.value
+    with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(piles)))) as pool:
+        return list(pool.map(lambda pile: compute_pile_seed_partition(pile[0], pile[1], **arguments), piles))

@@ -129,3 +129,28 @@ def test_tools_mirror(xt):
     expected_score = oracle.optimize_partitions(outgoing, incoming, 51, masses, *bounds, 0.02, 0.25, theirs,
                                                 np.ones(15, dtype="int8"), 0.02)
     assert np.array_equal(mine, theirs) and score == expected_score
+
+
+def test_piles_side_by_side(xt):
+    # seeds + first optimisation of several piles at once (one CTA each, one host thread and stream each):
+    # the same partitions as one at a time, and as the oracle
+    from metacells_b200 import pipeline
+
+    piles = []
+    for seed in (61, 62, 63, 64, 65):
+        outgoing, _, masses, _ = random_partition_graph(600 + 100 * (seed - 61), 14, 7, seed)
+        piles.append((outgoing, masses))
+    arguments = dict(random_seed=SEED, target_metacell_size=40)
+    together = pipeline.compute_piles_seed_partitions(piles, workers=5, **arguments)
+    alone = pipeline.compute_piles_seed_partitions(piles, workers=1, **arguments)
+    for (outgoing, masses), (communities, score, seeds_count), (communities_alone, score_alone, _) in zip(piles, together, alone):
+        assert np.array_equal(communities, communities_alone) and score == score_alone
+        incoming = sp.csc_matrix(outgoing)
+        incoming.sort_indices()
+        bounds = pipeline.metacell_bounds(target_metacell_size=40)
+        wanted = pipeline.seeds_count_for(float(sum(masses)), outgoing.shape[0], bounds)
+        expected = np.full(outgoing.shape[0], -1, dtype="int32")
+        assert oracle.choose_seeds(outgoing, incoming, SEED, wanted, 0.85, 0.95, expected) == seeds_count
+        expected_score = oracle.optimize_partitions(outgoing, incoming, SEED, masses, *bounds, 0.02, 0.25, expected,
+                                                    np.ones(max(seeds_count, 2), dtype="int8"), 0.98)
+        assert np.array_equal(communities, expected) and score == expected_score
