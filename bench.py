@@ -305,18 +305,38 @@ def run_gpu_arm(args):
             torch.cuda.synchronize(device)
 
     def steps_e2e_overlapped(steps):
-        """K end-to-end steps as a pipeline over piles would run them (divide_and_conquer.py:1264-1295 hands piles out
-        one after the other): the upload of pile k + 1 is started before the kernels of pile k are launched, so it runs
-        under them on the copy stream.  Every step still uploads its pile and reads its graph back inside the timed
-        region; only the first upload is exposed."""
+        """K end-to-end steps as a worker walks its piles (divide_and_conquer.py:1264-1295 hands piles out one after the
+        other): the upload of pile k + 1 is started after the first launches of pile k and runs under its kernels on the
+        pile's copy stream, and the graph of pile k is copied to the host (mcb_graph_read_start, a stream of the graph's
+        own) under the first kernels of pile k + 1.  Every step still uploads its pile and reads its graph back inside
+        the timed region; only the first upload and the last read are exposed."""
         nnz = 0
         pending = [upload()]
+        reading = []  # the graph whose copy to the host is in flight
 
-        def start_next():
-            pending.append(upload())
+        def finish_read():
+            while reading:
+                graph = reading.pop()
+                library.call("mcb_graph_read_finish", graph)
+                library.lib.mcb_graph_free(graph)
 
         for index in range(steps):
-            nnz = step_e2e(pending.pop(0), meanwhile=start_next if index + 1 < steps else None)
+            pile = pending.pop(0)
+
+            def meanwhile(last=index + 1 == steps):
+                if not last:
+                    pending.append(upload())
+                finish_read()  # before this pile's graph is read into the same host buffers
+
+            graph = hot_path(pile, meanwhile=meanwhile)
+            nnz = library.lib.mcb_graph_nnz(graph)
+            if nnz > capacity:
+                raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
+            library.call("mcb_graph_read_start", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
+                         p(result["indptr"].data_ptr()))
+            reading.append(graph)
+            library.lib.mcb_pile_free(pile)
+        finish_read()
         return nnz
 
     def timed(step, steps, whole_run=False):
@@ -415,9 +435,9 @@ def run_gpu_arm(args):
                       "peak_source": peak_source, "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms}
     # SURVEY 8d's algorithmic bytes: ranks read and write the whole square matrix; the downsample reads and writes the
     # pile's values and reads the row pointers; balance reads every rank once (count and fill passes are one stage).
-    rank_line = hbm_line("rank_matrix_merge_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, args.features),
+    rank_line = hbm_line("rank_matrix_bucket_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, args.features),
                          "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_rank_matrix_merge.txt")
-    downsample_line = hbm_line("downsample_rows_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, None, None)
+    downsample_line = hbm_line("downsample_warp_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, None, None)
     balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells, None, None)
     # the dominant kernel is the one with the largest share of the step
     candidates = [line for line in (rank_line, correlate_line, downsample_line, balance_line) if line["ms_per_launch"]]
@@ -433,7 +453,8 @@ def run_gpu_arm(args):
         "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                 "unpipelined_ms_per_step": e2e_sequential_ms / args.steps,
                 "note": "every step uploads its pile from pinned host memory and reads its graph back; the upload of the next "
-                        "pile runs under the kernels of the current one (unpipelined_ms_per_step: one pile at a time)",
+                        "pile and the read of the previous graph run under the kernels of the current one (unpipelined_ms_per_step: one "
+                        "pile at a time)",
                 "h2d_bytes_per_step": int(umis.data.nbytes + umis.indices.nbytes + umis.indptr.nbytes + table.nbytes + 4 * args.features),
                 "d2h_bytes_per_step": int(nnz * 8 + (cells + 1) * 4 + genes * 4)},
         "gpu_launches": int(launches),
@@ -480,21 +501,36 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
                      p(pinned["indptr"].data_ptr()), ctypes.c_int64(size), ctypes.c_int64(genes), ctypes.byref(pile))
         return pile
 
-    def one_pile(size, pile=None, meanwhile=None):
+    reading = []  # the graph whose copy to the host is in flight (under the next pile's first kernels)
+
+    def finish_read():
+        while reading:
+            graph = reading.pop()
+            library.call("mcb_graph_read_finish", graph)
+            library.lib.mcb_graph_free(graph)
+
+    def one_pile(size, pile=None, start_next=None):
         if pile is None:
             pile = upload(size)
+
+        def meanwhile():
+            if start_next is not None:
+                start_next()
+            finish_read()  # before this pile's graph is read into the same host buffers
+
         graph = hot_path(pile, ks[size], meanwhile)
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
             raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
-        library.call("mcb_graph_read", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
+        library.call("mcb_graph_read_start", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
                      p(result["indptr"].data_ptr()))
-        library.lib.mcb_graph_free(graph)
+        reading.append(graph)
         library.lib.mcb_pile_free(pile)
         return nnz
 
     if mine:
         one_pile(int(sizes[mine[0]]))  # warm the pools for this pile size
+        finish_read()
     begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     start = time.perf_counter()
@@ -505,6 +541,7 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
         following = int(sizes[mine[index + 1]]) if index + 1 < len(mine) else None
         edges += one_pile(int(sizes[pile]), pending.pop(0),
                           (lambda size=following: pending.append(upload(size))) if following is not None else None)
+    finish_read()
     end.record(stream)
     barrier()
     wall = time.perf_counter() - start
@@ -519,7 +556,8 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
             "pile_cells": [int(sizes.min()), int(sizes.max())], "phases": 1, "n_gpus": world, "scaling": "strong",
             "wall_s": wall_s, "device_s": device_s, "cells_per_s": args.atlas_cells / wall_s, "graph_nnz": int(edges),
             "data": "synthetic; every pile is a row prefix of the rank's synthetic pile, uploaded from pinned host memory (the next "
-                    "pile's upload under the current pile's kernels) and its graph read back (max over ranks, barrier on both sides)"}
+                    "pile's upload under the current pile's kernels) and its graph read back (under the next pile's first kernels; "
+                    "max over ranks, barrier on both sides)"}
 
 
 def ncu_traffic(kernel, cells, features):

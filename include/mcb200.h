@@ -40,6 +40,8 @@ int mcb_synchronize(void* stream);
 /* Streaming multiprocessors of the calling thread's device: how many one-CTA optimisations (mcb_host_choose_seeds,
  * mcb_host_optimize_partitions, each on its caller thread's own stream) run side by side. */
 int mcb_device_sm_count(int* count);
+/* Grows the device's scratch pool (stream-ordered allocator, kept between calls) to at least `bytes` free now. */
+int mcb_reserve_scratch(long long bytes);
 /* Number of kernels this library has launched in the calling process so far. */
 long long mcb_launch_count(void);
 /* Optional per-kernel timing: when enabled every launch is bracketed by CUDA events on its own
@@ -171,6 +173,12 @@ int64_t mcb_graph_nnz(const mcb_graph* graph);
 int64_t mcb_graph_k(const mcb_graph* graph); /* the k finally used */
 /* Copy to host buffers (any may be NULL): weights/ranks/indices have nnz entries, indptr size + 1. */
 int mcb_graph_read(const mcb_graph* graph, float* weights, float* ranks, int32_t* indices, int32_t* indptr);
+/* The same copies started on a stream of the graph's own, without waiting: a worker that walks its piles (one after the
+ * other, pipeline/divide_and_conquer.py:1264-1295) reads the graph of pile k while the kernels of pile k + 1 run.  The
+ * host buffers (page-locked, or the copies are not asynchronous) hold the graph after mcb_graph_read_finish returns;
+ * mcb_graph_free also waits for the copies. */
+int mcb_graph_read_start(mcb_graph* graph, float* weights, float* ranks, int32_t* indices, int32_t* indptr);
+int mcb_graph_read_finish(mcb_graph* graph);
 int mcb_graph_device_arrays(const mcb_graph* graph, const float** weights, const float** ranks, const int32_t** indices,
                             const int32_t** indptr);
 void mcb_graph_free(mcb_graph* graph);

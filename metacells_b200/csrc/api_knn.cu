@@ -44,6 +44,13 @@ struct mcb_graph {
     int64_t n = 0, nnz = 0, k = 0;
     Scratch weights, ranks, indices, indptr;
     cudaStream_t stream = nullptr;
+    cudaStream_t read_stream = nullptr;  // mcb_graph_read_start: the copies to the host run beside the next pile's kernels
+    ~mcb_graph() {
+        if (read_stream) {
+            cudaStreamSynchronize(read_stream);
+            cudaStreamDestroy(read_stream);
+        }
+    }
 };
 
 namespace {
@@ -334,6 +341,30 @@ int mcb_graph_read(const mcb_graph* graph, float* weights, float* ranks, int32_t
     if (indices) MCB_TRY(to_host(indices, graph->indices, (size_t)graph->nnz, stream));
     if (indptr) MCB_TRY(to_host(indptr, graph->indptr, (size_t)graph->n + 1, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_graph_read_start(mcb_graph* graph, float* weights, float* ranks, int32_t* indices, int32_t* indptr) {
+    MCB_REQUIRE(graph != nullptr, "graph: null handle");
+    if (graph->read_stream == nullptr)
+        MCB_CUDA(cudaStreamCreateWithFlags(&graph->read_stream, cudaStreamNonBlocking));
+    cudaEvent_t complete;
+    MCB_CUDA(cudaEventCreateWithFlags(&complete, cudaEventDisableTiming));
+    MCB_CUDA(cudaEventRecord(complete, graph->stream));
+    MCB_CUDA(cudaStreamWaitEvent(graph->read_stream, complete, 0));
+    cudaEventDestroy(complete);
+    cudaStream_t stream = graph->read_stream;
+    if (weights) MCB_TRY(to_host(weights, graph->weights, (size_t)graph->nnz, stream));
+    if (ranks) MCB_TRY(to_host(ranks, graph->ranks, (size_t)graph->nnz, stream));
+    if (indices) MCB_TRY(to_host(indices, graph->indices, (size_t)graph->nnz, stream));
+    if (indptr) MCB_TRY(to_host(indptr, graph->indptr, (size_t)graph->n + 1, stream));
+    return MCB_OK;
+}
+
+int mcb_graph_read_finish(mcb_graph* graph) {
+    MCB_REQUIRE(graph != nullptr, "graph: null handle");
+    if (graph->read_stream)
+        MCB_CUDA(cudaStreamSynchronize(graph->read_stream));
     return MCB_OK;
 }
 

@@ -11,7 +11,7 @@ namespace mcb {
 int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
-                           cudaStream_t stream);
+                           cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr);
 int column_totals_launch(const float* data, const int32_t* indices, int64_t nnz, int64_t columns, float* totals,
                          cudaStream_t stream);
 int log_fraction_dense_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t rows,
@@ -38,6 +38,7 @@ struct mcb_pile {
     const int32_t* indptr = nullptr;
     Scratch downsampled;  // same sparsity structure as `data`
     bool has_downsampled = false;
+    Scratch gene_totals;  // float32[genes]: per-gene totals of `downsampled`, added up by the downsample kernels
     Scratch top_genes;    // int32[top_genes_count] ascending, set by mcb_pile_top_genes
     int64_t top_genes_count = 0;
     // A host pile is uploaded in row chunks on its own stream, so that the downsampling of the first chunks runs
@@ -189,9 +190,14 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
     MCB_REQUIRE(samples >= 0, "pile: negative samples");
     if (!pile->downsampled.ptr)
         MCB_TRY(pile->downsampled.alloc((size_t)pile->nnz * sizeof(float), pile->stream));
+    if (!pile->gene_totals.ptr)
+        MCB_TRY(pile->gene_totals.alloc((size_t)pile->genes * sizeof(float), pile->stream));
+    MCB_CUDA(cudaMemsetAsync(pile->gene_totals.ptr, 0, (size_t)pile->genes * sizeof(float), pile->stream));
+    float* totals = pile->gene_totals.as<float>();
     if (pile->chunk_ready.empty()) {
         MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples, 0, pile->cells, 0,
-                                       pile->widest, random_seed, 1, pile->max_row_total, nullptr, pile->stream));
+                                       pile->widest, random_seed, 1, pile->max_row_total, nullptr, pile->stream, pile->indices,
+                                       totals));
     } else {
         // Every chunk as soon as it has arrived; with the largest cell total known nothing here waits on the device.
         // Chunks that have arrived already (a pile uploaded under the previous pile's kernels) go in one launch: a
@@ -204,7 +210,7 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
             MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples,
                                            pile->chunk_rows[c], pile->chunk_rows[last + 1], 0, pile->widest, random_seed, 1,
                                            pile->max_row_total, pile->max_row_total ? pile->status.as<int>() : nullptr,
-                                           pile->stream));
+                                           pile->stream, pile->indices, totals));
             c = last + 1;
         }
     }
@@ -215,11 +221,14 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
 int mcb_pile_gene_totals(mcb_pile* pile, float* totals) {
     MCB_REQUIRE(pile != nullptr && totals != nullptr, "pile: null argument");
     MCB_TRY(wait_for_upload(pile));
-    const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     Scratch device;
-    MCB_TRY(device.alloc((size_t)pile->genes * sizeof(float), pile->stream));
-    MCB_TRY(column_totals_launch(values, pile->indices, pile->nnz, pile->genes, device.as<float>(), pile->stream));
-    MCB_CUDA(cudaMemcpyAsync(totals, device.ptr, (size_t)pile->genes * sizeof(float), cudaMemcpyDeviceToHost, pile->stream));
+    const float* source = pile->gene_totals.as<float>();  // of the downsampled pile: the downsample kernels added them up
+    if (!pile->has_downsampled) {
+        MCB_TRY(device.alloc((size_t)pile->genes * sizeof(float), pile->stream));
+        MCB_TRY(column_totals_launch(pile->data, pile->indices, pile->nnz, pile->genes, device.as<float>(), pile->stream));
+        source = device.as<float>();
+    }
+    MCB_CUDA(cudaMemcpyAsync(totals, source, (size_t)pile->genes * sizeof(float), cudaMemcpyDeviceToHost, pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     return MCB_OK;
 }
@@ -309,11 +318,14 @@ int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host) {
     MCB_REQUIRE(pile != nullptr && count >= 1 && count < pile->genes, "pile: top genes count must be in 1..genes-1");
     cudaStream_t stream = pile->stream;
     MCB_TRY(wait_for_upload(pile));
-    const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
-    Scratch totals, unused;
-    MCB_TRY(totals.alloc((size_t)pile->genes * sizeof(float), stream));
+    Scratch computed, unused;
+    const float* totals = pile->gene_totals.as<float>();  // of the downsampled pile: the downsample kernels added them up
+    if (!pile->has_downsampled) {
+        MCB_TRY(computed.alloc((size_t)pile->genes * sizeof(float), stream));
+        MCB_TRY(column_totals_launch(pile->data, pile->indices, pile->nnz, pile->genes, computed.as<float>(), stream));
+        totals = computed.as<float>();
+    }
     MCB_TRY(unused.alloc((size_t)count * sizeof(float), stream));
-    MCB_TRY(column_totals_launch(values, pile->indices, pile->nnz, pile->genes, totals.as<float>(), stream));
     if (pile->top_genes_count != count) {
         Scratch fresh;
         MCB_TRY(fresh.alloc((size_t)count * sizeof(int32_t), stream));
@@ -322,7 +334,7 @@ int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host) {
         pile->top_genes_count = count;
     }
     // the `count` largest totals, equal totals by lower gene index, indices ascending: one row of collect_top
-    MCB_TRY(collect_top_launch(count, totals.as<float>(), 1, pile->genes, pile->genes, pile->top_genes.as<int32_t>(),
+    MCB_TRY(collect_top_launch(count, totals, 1, pile->genes, pile->genes, pile->top_genes.as<int32_t>(),
                                unused.as<float>(), 0, stream));
     if (genes_host != nullptr) {
         MCB_CUDA(cudaMemcpyAsync(genes_host, pile->top_genes.ptr, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));

@@ -48,6 +48,8 @@ struct DownsampleParams {
     int64_t capacity;        // elements per array in `workspace` (0: shared memory only)
     int smem_capacity;       // elements per array that fit shared memory
     int* error_flag;
+    const int32_t* indices;  // with column_totals: the column of every element of a compressed matrix
+    float* column_totals;    // nullable: += every output value (integers far below 2^24: exact in any order)
 };
 
 __global__ void __launch_bounds__(DS_THREADS) downsample_kernel(DownsampleParams p) {
@@ -282,9 +284,14 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
         float* out = p.output + lo;
         if (samples < 0 || n == 0)
             continue;  // downsample.cpp:86-88
+        const int32_t* columns_of_row = p.column_totals ? p.indices + lo : nullptr;
         if (n == 1) {  // downsample.cpp:90-93
-            if (lane == 0)
-                out[0] = (double)samples < (double)in[0] ? (float)samples : in[0];
+            if (lane == 0) {
+                const float kept = (double)samples < (double)in[0] ? (float)samples : in[0];
+                out[0] = kept;
+                if (columns_of_row && kept != 0.0f)
+                    atomicAdd(&p.column_totals[columns_of_row[0]], kept);
+            }
             continue;
         }
         unsigned long long total64 = 0;
@@ -293,6 +300,10 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
         if (total64 <= (unsigned long long)samples) {  // downsample.cpp:100-105
             if (out != in)
                 for (int i = lane; i < n; i += 32) out[i] = in[i];
+            if (columns_of_row)
+                for (int i = lane; i < n; i += 32)
+                    if (in[i] != 0.0f)
+                        atomicAdd(&p.column_totals[columns_of_row[i]], in[i]);
             continue;
         }
         const int words = (int)((total64 + 31) >> 5);
@@ -408,11 +419,25 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
                 drawn += __popc(bitmap[w] & mask);
                 begin += take;
             }
-            if (i < n)
+            if (i < n) {
                 out[i] = (float)drawn;
+                if (columns_of_row && drawn)
+                    atomicAdd(&p.column_totals[columns_of_row[i]], (float)drawn);
+            }
         }
         __syncwarp();
     }
+}
+
+// The fallback kernels do not add to the column totals themselves.
+__global__ void __launch_bounds__(256) add_column_totals_kernel(DownsampleParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = p.first_row + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= p.rows)
+        return;
+    for (int64_t e = p.indptr[row] + lane; e < p.indptr[row + 1]; e += 32)
+        if (p.output[e] != 0.0f)
+            atomicAdd(&p.column_totals[p.indices[e]], p.output[e]);
 }
 
 }  // namespace
@@ -422,7 +447,7 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
 int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
-                           cudaStream_t stream);
+                           cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr);
 
 int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                       int32_t samples_all, int64_t rows, int64_t columns, int64_t max_row_size, uint64_t seed,
@@ -434,7 +459,7 @@ int downsample_launch(const float* input, float* output, const int32_t* indptr, 
 int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const int32_t* indices, float* column_totals) {
     const int64_t rows = last_row - first_row;
     if (rows <= 0)
         return MCB_OK;
@@ -449,6 +474,11 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
     p.first_row = first_row;
     p.seed = seed;
     p.use_row_seed = use_row_seed;
+    // column totals of the output (compressed input only): added by the kernel that writes it
+    MCB_REQUIRE(column_totals == nullptr || (indices != nullptr && indptr != nullptr),
+                "downsample: column totals need a compressed matrix");
+    p.indices = indices;
+    p.column_totals = column_totals;
 
     Scratch workspace, flag, counters;
     MCB_TRY(flag.alloc(sizeof(int), stream));
@@ -516,6 +546,10 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
     MCB_CUDA(cudaFuncSetAttribute(downsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     MCB_PROFILED("downsample", stream, downsample_kernel<<<(unsigned)grid, DS_THREADS, smem_bytes, stream>>>(p));
     MCB_LAUNCH_CHECK();
+    if (column_totals) {
+        add_column_totals_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(p);
+        MCB_LAUNCH_CHECK();
+    }
     int host_flag = 0;
     MCB_CUDA(cudaMemcpyAsync(&host_flag, flag.ptr, sizeof(int), cudaMemcpyDeviceToHost, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));

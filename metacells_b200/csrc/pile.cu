@@ -42,21 +42,36 @@ __global__ void __launch_bounds__(256) log_fraction_dense_kernel(const float* __
     const float zero_value = table[0];
     for (int64_t c = lane; c < features; c += 32) out[c] = zero_value;
     __syncwarp();
-    for (int e = indptr[row] + lane; e < indptr[row + 1]; e += 32) {
-        const int slot = slot_of_gene[indices[e]];
-        if (slot < 0)
-            continue;
-        const float value = data[e];
-        const int count = (int)value;
-        float result;
-        if (value >= 0.0f && (float)count == value && count < table_size) {
-            result = table[count];
-        } else {
-            result = log2f(__fadd_rn(value, regularization));  // not covered by the numpy-made table
-            if (error_flag)
-                atomicExch(error_flag, 1);
+    // four independent chains per lane: the gene's slot and the count are loaded for all of them before any is used
+    constexpr int UNROLL = 4;
+    const int end = indptr[row + 1];
+    for (int base = indptr[row] + lane; base < end; base += 32 * UNROLL) {
+        int slot[UNROLL];
+        float value[UNROLL];
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            const int e = base + 32 * j;
+            slot[j] = e < end ? indices[e] : -1;
+            value[j] = e < end ? data[e] : 0.0f;
         }
-        out[slot] = result;
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j)
+            if (slot[j] >= 0) slot[j] = slot_of_gene[slot[j]];
+#pragma unroll
+        for (int j = 0; j < UNROLL; ++j) {
+            if (slot[j] < 0)
+                continue;
+            const int count = (int)value[j];
+            float result;
+            if (value[j] >= 0.0f && (float)count == value[j] && count < table_size) {
+                result = table[count];
+            } else {
+                result = log2f(__fadd_rn(value[j], regularization));  // not covered by the numpy-made table
+                if (error_flag)
+                    atomicExch(error_flag, 1);
+            }
+            out[slot[j]] = result;
+        }
     }
 }
 

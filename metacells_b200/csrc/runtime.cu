@@ -117,6 +117,22 @@ extern "C" {
 
 long long mcb_launch_count(void) { return mcb::g_launches.load(); }
 
+// Grows the device's stream-ordered pool to hold `bytes` of scratch now (one allocation, freed again: the pool keeps
+// it), so that calls running side by side later do not each stop to take memory from the driver while kernels run.
+int mcb_reserve_scratch(long long bytes) {
+    MCB_REQUIRE(bytes >= 0, "mcb_reserve_scratch: negative size");
+    if (bytes == 0)
+        return MCB_OK;
+    cudaStream_t stream = nullptr;
+    MCB_TRY(mcb::thread_stream(&stream));
+    {
+        mcb::Scratch block;
+        MCB_TRY(block.alloc(size_t(bytes), stream));
+    }
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
 int mcb_device_sm_count(int* count) {
     MCB_REQUIRE(count != nullptr, "mcb_device_sm_count: null argument");
     *count = mcb::sm_count();

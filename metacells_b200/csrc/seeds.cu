@@ -329,6 +329,11 @@ __device__ void cta_nth_element(E* a, uint16_t* left, uint16_t* right, int first
     __syncthreads();
 }
 
+// seed sizes, seed weights and the bitmap of touched seeds at the head of dynamic shared memory (16-byte multiple)
+__host__ __device__ inline size_t seed_tables_bytes(int seeds_padded) {
+    return (size_t(seeds_padded) * 8 + size_t(seeds_padded >> 5) * 4 + 15) & ~size_t(15);
+}
+
 struct SeedsParams {
     const float* out_w;
     const int32_t* out_idx;
@@ -501,7 +506,7 @@ __global__ void __launch_bounds__(SEED_THREADS, 1) choose_seeds_kernel(const See
     float* seed_weights = reinterpret_cast<float*>(seed_sizes + seeds_padded);
     uint32_t* touched = reinterpret_cast<uint32_t*>(seed_weights + seeds_padded);
     unsigned char* select = P.select_global ? static_cast<unsigned char*>(P.select_global)
-                                            : dynamic + size_t(seeds_padded) * 8 + size_t(seeds_padded >> 5) * 4;
+                                            : dynamic + seed_tables_bytes(seeds_padded);
     for (int i = threadIdx.x; i < seeds_padded; i += SEED_THREADS) {
         seed_sizes[i] = 0;
         seed_weights[i] = 0.0f;
@@ -710,7 +715,7 @@ int seeds_launch(const float* out_w, const int32_t* out_idx, const int32_t* out_
     params.band_capacity = (std::max(result_host[2], 1) + 7) & ~7;
     params.result = result.as<int32_t>();
     const int seeds_padded = (params.max_seeds + 31) & ~31;
-    const size_t fixed_bytes = size_t(seeds_padded) * 8 + size_t(seeds_padded >> 5) * 4;
+    const size_t fixed_bytes = seed_tables_bytes(seeds_padded);
     const size_t select_bytes = std::max(size_t(params.select_capacity) * 8, size_t(params.band_capacity) * 12);
     int device = 0, shared_limit = 0;
     MCB_CUDA(cudaGetDevice(&device));

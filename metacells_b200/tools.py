@@ -178,16 +178,29 @@ class KnnGraph:
         function.restype = ctypes.c_int64
         return int(function(self._handle))
 
-    def to_scipy(self) -> Tuple[sp.csr_matrix, sp.csr_matrix]:
-        """``(outgoing_weights, pruned_ranks)`` as CSR float32 / int32 / int32."""
+    def read_start(self):
+        """Starts the copy of the graph to freshly allocated host arrays on a stream of the graph's own
+        (``mcb_graph_read_start``) and returns them: a worker launches its next pile before ``read_finish``."""
         size, nnz = self.shape[0], self.nnz
-        weights = np.empty(nnz, dtype="float32")
-        ranks = np.empty(nnz, dtype="float32")
-        indices = np.empty(nnz, dtype="int32")
-        indptr = np.empty(size + 1, dtype="int32")
-        function = lib().mcb_graph_read
+        arrays = (np.empty(nnz, dtype="float32"), np.empty(nnz, dtype="float32"), np.empty(nnz, dtype="int32"),
+                  np.empty(size + 1, dtype="int32"))
+        function = lib().mcb_graph_read_start
         function.restype = ctypes.c_int
-        check(function(self._handle, *(ctypes.c_void_p(a.ctypes.data) for a in (weights, ranks, indices, indptr))))
+        check(function(self._handle, *(ctypes.c_void_p(a.ctypes.data) for a in arrays)))
+        return arrays
+
+    def read_finish(self) -> None:
+        function = lib().mcb_graph_read_finish
+        function.restype = ctypes.c_int
+        check(function(self._handle))
+
+    def to_scipy(self, arrays=None) -> Tuple[sp.csr_matrix, sp.csr_matrix]:
+        """``(outgoing_weights, pruned_ranks)`` as CSR float32 / int32 / int32; ``arrays``: what ``read_start`` returned."""
+        size = self.shape[0]
+        if arrays is None:
+            arrays = self.read_start()
+        self.read_finish()
+        weights, ranks, indices, indptr = arrays
         outgoing_weights = sp.csr_matrix((weights, indices, indptr), shape=(size, size))
         pruned_ranks = sp.csr_matrix((ranks, indices.copy(), indptr.copy()), shape=(size, size))
         for matrix in (outgoing_weights, pruned_ranks):
