@@ -44,6 +44,11 @@ def parse_args():
     parser.add_argument("--no-cpu-baseline", action="store_true")
     parser.add_argument("--atlas-cells", type=int, default=1000000,
                         help="cells of the divide-and-conquer atlas whose piles are timed after the per-pile steps (0: skip)")
+    parser.add_argument("--e2e-workers", type=int, default=2,
+                        help="host threads of a rank that walk its piles end to end, each on a stream of its own")
+    parser.add_argument("--candidate-piles", type=int, default=16,
+                        help="piles whose seeds and first partition optimisation run side by side after the k-NN steps "
+                             "(N = 1 only; 0: skip)")
     return parser.parse_args()
 
 
@@ -285,15 +290,16 @@ def run_gpu_arm(args):
                      p(pinned["indptr"].data_ptr()), ctypes.c_int64(cells), ctypes.c_int64(genes), ctypes.byref(pile))
         return pile
 
-    def step_e2e(pile=None, meanwhile=None):
+    def step_e2e(pile=None, meanwhile=None, buffers=None):
+        buffers = buffers or result
         if pile is None:
             pile = upload()
         graph = hot_path(pile, meanwhile=meanwhile)
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
             raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
-        library.call("mcb_graph_read", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
-                     p(result["indptr"].data_ptr()))
+        library.call("mcb_graph_read", graph, p(buffers["weights"].data_ptr()), None, p(buffers["indices"].data_ptr()),
+                     p(buffers["indptr"].data_ptr()))
         library.lib.mcb_graph_free(graph)
         library.lib.mcb_pile_free(pile)
         return nnz
@@ -313,6 +319,13 @@ def run_gpu_arm(args):
         nnz = 0
         pending = [upload()]
         reading = []  # the graph whose copy to the host is in flight
+        trace = os.environ.get("MCB_BENCH_TRACE")  # developer aid: host times of the stages of every step, on stderr
+        sync_read = os.environ.get("MCB_BENCH_SYNC_READ")  # developer aid: read every graph before the next pile starts
+        laps = []
+
+        def lap(name):
+            if trace:
+                laps.append((name, time.perf_counter()))
 
         def finish_read():
             while reading:
@@ -322,22 +335,66 @@ def run_gpu_arm(args):
 
         for index in range(steps):
             pile = pending.pop(0)
+            lap("start")
 
             def meanwhile(last=index + 1 == steps):
+                lap("launched")
                 if not last:
                     pending.append(upload())
+                lap("upload issued")
                 finish_read()  # before this pile's graph is read into the same host buffers
+                lap("previous read")
 
             graph = hot_path(pile, meanwhile=meanwhile)
+            lap("graph")
             nnz = library.lib.mcb_graph_nnz(graph)
             if nnz > capacity:
                 raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
             library.call("mcb_graph_read_start", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
                          p(result["indptr"].data_ptr()))
             reading.append(graph)
+            if sync_read:
+                finish_read()
+            lap("read issued")
             library.lib.mcb_pile_free(pile)
+            lap("pile freed")
         finish_read()
+        lap("end")
+        if trace:
+            print("[bench] e2e pipeline: " + " | ".join(f"{name} +{(now - laps[i - 1][1]) * 1e3:.2f}" if i else name
+                                                       for i, (name, now) in enumerate(laps)), file=sys.stderr)
         return nnz
+
+    workers = max(1, args.e2e_workers)
+    worker_buffers = [result] + [{name: torch.empty_like(tensor).pin_memory() for name, tensor in result.items()}
+                                 for _ in range(workers - 1)]
+
+    def steps_e2e_workers(steps):
+        """K end-to-end steps by the rank's worker threads: every thread walks its share of the piles one after the other
+        (host CSR in, graph out into its own page-locked buffers, as step_e2e) on a stream of its own, so one thread's
+        upload, read-back and host-side gaps lie under the other threads' kernels.  Nothing is prefetched and nothing is
+        shared between the threads but the GPU."""
+        import threading
+
+        shares = [steps // workers + (1 if index < steps % workers else 0) for index in range(workers)]
+        edges, failures = [0] * workers, []
+
+        def walk(index):
+            try:
+                library.call("mcb_set_device", ctypes.c_int(local_rank))  # the current device is per thread
+                for _ in range(shares[index]):
+                    edges[index] = step_e2e(buffers=worker_buffers[index])
+            except BaseException as failure:  # noqa: BLE001 (reported by the main thread)
+                failures.append(failure)
+
+        threads = [threading.Thread(target=walk, args=(index,)) for index in range(workers)]
+        for thread in threads:
+            thread.start()
+        for thread in threads:
+            thread.join()
+        if failures:
+            raise failures[0]
+        return max(edges)
 
     def timed(step, steps, whole_run=False):
         """K steps between events on the launching stream; returns (max-over-ranks ms, nnz)."""
@@ -376,11 +433,13 @@ def run_gpu_arm(args):
         step_e2e()
     e2e_sequential_ms, _ = timed(step_e2e, args.steps)
     steps_e2e_overlapped(3)  # two piles in flight: lets the memory pool grow before the timed region
-    if os.environ.get("MCB_BENCH_PROFILE_E2E"):  # diagnosis only: kernel times while the next pile's upload is in flight
+    e2e_prefetch_ms, _ = timed(steps_e2e_overlapped, args.steps, whole_run=True)
+    steps_e2e_workers(2 * workers)
+    if os.environ.get("MCB_BENCH_PROFILE_E2E"):  # diagnosis only: kernel times while other piles are in flight
         library.call("mcb_profile_enable", ctypes.c_int(1))
-    e2e_ms, _ = timed(steps_e2e_overlapped, args.steps, whole_run=True)
+    e2e_ms, _ = timed(steps_e2e_workers, args.steps, whole_run=True)
     if os.environ.get("MCB_BENCH_PROFILE_E2E"):
-        print("[bench] kernels under upload:", {name: round(library.profile(name)[0] / args.steps, 3) for name in library.profile_names()},
+        print("[bench] kernels with piles side by side:", {name: round(library.profile(name)[0] / args.steps, 3) for name in library.profile_names()},
               file=sys.stderr)
         library.call("mcb_profile_enable", ctypes.c_int(0))
 
@@ -451,10 +510,14 @@ def run_gpu_arm(args):
                    "l2": "inputs larger than L2 (CSR pile 0.45 GB, similarity and rank matrices 1 GB each per step)"},
         "clocks": clocks,
         "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
-                "unpipelined_ms_per_step": e2e_sequential_ms / args.steps,
-                "note": "every step uploads its pile from pinned host memory and reads its graph back; the upload of the next "
-                        "pile and the read of the previous graph run under the kernels of the current one (unpipelined_ms_per_step: one "
-                        "pile at a time)",
+                "workers": workers,
+                "one_thread_ms_per_step": e2e_sequential_ms / args.steps,
+                "one_thread_prefetch_ms_per_step": e2e_prefetch_ms / args.steps,
+                "note": "every step uploads its pile from pinned host memory and reads its graph back into pinned memory, both "
+                        "inside the timed region; `workers` host threads walk the piles, each on its own stream, so one pile's "
+                        "copies and host-side gaps lie under another pile's kernels (one_thread_ms_per_step: one pile at a "
+                        "time; one_thread_prefetch_ms_per_step: one thread that starts the next upload and the previous "
+                        "graph's read under the current pile's kernels)",
                 "h2d_bytes_per_step": int(umis.data.nbytes + umis.indices.nbytes + umis.indptr.nbytes + table.nbytes + 4 * args.features),
                 "d2h_bytes_per_step": int(nnz * 8 + (cells + 1) * 4 + genes * 4)},
         "gpu_launches": int(launches),
@@ -464,6 +527,8 @@ def run_gpu_arm(args):
     }
     if atlas is not None:
         line["atlas"] = atlas
+    if world == 1 and args.candidate_piles > 0:
+        line["candidates"] = time_candidates(args, umis)
     if world == 1 and not args.no_cpu_baseline:
         step, info, _ = cpu_step_factory(args)
         start = time.perf_counter()
@@ -501,47 +566,59 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
                      p(pinned["indptr"].data_ptr()), ctypes.c_int64(size), ctypes.c_int64(genes), ctypes.byref(pile))
         return pile
 
-    reading = []  # the graph whose copy to the host is in flight (under the next pile's first kernels)
+    workers = max(1, args.e2e_workers)
+    buffers_of_worker = [result] + [{name: torch.empty_like(tensor).pin_memory() for name, tensor in result.items()}
+                                    for _ in range(workers - 1)]
 
-    def finish_read():
-        while reading:
-            graph = reading.pop()
-            library.call("mcb_graph_read_finish", graph)
-            library.lib.mcb_graph_free(graph)
-
-    def one_pile(size, pile=None, start_next=None):
-        if pile is None:
-            pile = upload(size)
-
-        def meanwhile():
-            if start_next is not None:
-                start_next()
-            finish_read()  # before this pile's graph is read into the same host buffers
-
-        graph = hot_path(pile, ks[size], meanwhile)
+    def one_pile(size, buffers):
+        pile = upload(size)
+        graph = hot_path(pile, ks[size])
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
             raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
-        library.call("mcb_graph_read_start", graph, p(result["weights"].data_ptr()), None, p(result["indices"].data_ptr()),
-                     p(result["indptr"].data_ptr()))
-        reading.append(graph)
+        library.call("mcb_graph_read", graph, p(buffers["weights"].data_ptr()), None, p(buffers["indices"].data_ptr()),
+                     p(buffers["indptr"].data_ptr()))
+        library.lib.mcb_graph_free(graph)
         library.lib.mcb_pile_free(pile)
         return nnz
 
+    def walk_piles(piles_of_run):
+        """The rank's worker threads take the rank's piles off one list, largest first (a dynamic queue, as SURVEY 8e),
+        each thread on a stream of its own: one pile's upload and read-back lie under another pile's kernels."""
+        import threading
+
+        remaining = list(piles_of_run)
+        lock = threading.Lock()
+        edges, failures = [0] * workers, []
+
+        def walk(index):
+            try:
+                library.call("mcb_set_device", ctypes.c_int(device.index))  # the current device is per thread
+                while True:
+                    with lock:
+                        if not remaining:
+                            return
+                        pile = remaining.pop(0)
+                    edges[index] += one_pile(int(sizes[pile]), buffers_of_worker[index])
+            except BaseException as failure:  # noqa: BLE001 (reported by the main thread)
+                failures.append(failure)
+
+        threads = [threading.Thread(target=walk, args=(index,)) for index in range(workers)]
+        for thread in threads:
+            thread.start()
+        for thread in threads:
+            thread.join()
+        if failures:
+            raise failures[0]
+        return sum(edges)
+
     if mine:
-        one_pile(int(sizes[mine[0]]))  # warm the pools for this pile size
-        finish_read()
+        walk_piles(mine[:workers])  # warm the pools for this pile size
     begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     start = time.perf_counter()
     begin.record(stream)
-    edges = 0
-    pending = [upload(int(sizes[mine[0]]))] if mine else []
-    for index, pile in enumerate(mine):  # the next pile's upload runs under this pile's kernels
-        following = int(sizes[mine[index + 1]]) if index + 1 < len(mine) else None
-        edges += one_pile(int(sizes[pile]), pending.pop(0),
-                          (lambda size=following: pending.append(upload(size))) if following is not None else None)
-    finish_read()
+    edges = walk_piles(mine)
     end.record(stream)
     barrier()
     wall = time.perf_counter() - start
@@ -555,9 +632,36 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
     return {"metric": "divide_and_conquer_knn_graphs_wall_time", "cells": int(args.atlas_cells), "piles": int(len(sizes)),
             "pile_cells": [int(sizes.min()), int(sizes.max())], "phases": 1, "n_gpus": world, "scaling": "strong",
             "wall_s": wall_s, "device_s": device_s, "cells_per_s": args.atlas_cells / wall_s, "graph_nnz": int(edges),
-            "data": "synthetic; every pile is a row prefix of the rank's synthetic pile, uploaded from pinned host memory (the next "
-                    "pile's upload under the current pile's kernels) and its graph read back (under the next pile's first kernels; "
-                    "max over ranks, barrier on both sides)"}
+            "data": "synthetic; every pile is a row prefix of the rank's synthetic pile, uploaded from pinned host memory and its "
+                    "graph read back; the rank's worker threads (e2e_workers) take piles off one list, each on its own stream "
+                    "(max over ranks, barrier on both sides)", "workers": workers}
+
+
+def time_candidates(args, umis):
+    """What follows the k-NN graph in a pile (tools/candidates.py:128-196, 351-368): choose_seeds and the first
+    optimize_partitions, through the reference's own entry points with host arrays.  Both are one persistent CTA, so the
+    piles of a worker run side by side, one SM and one host thread each; every pile here is the bench pile's graph."""
+    from metacells_b200 import extensions as xt, pipeline
+
+    cells = umis.shape[0]
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    weights, _ = pipeline.compute_pile_knn_graph(umis, features=args.features, random_seed=SEED)
+    pipeline.compute_pile_seed_partition(weights, cell_umis, random_seed=SEED)  # warm-up: pools, attributes
+    start = time.perf_counter()
+    communities, score, seeds = pipeline.compute_pile_seed_partition(weights, cell_umis, random_seed=SEED)
+    alone_s = time.perf_counter() - start
+    piles = [(weights, cell_umis)] * args.candidate_piles
+    start = time.perf_counter()
+    results = pipeline.compute_piles_seed_partitions(piles, random_seed=SEED)
+    together_s = time.perf_counter() - start
+    identical = all(np.array_equal(communities, other[0]) and score == other[1] for other in results)
+    return {"metric": "seeds_and_first_partition_optimisation_wall_time", "cells_per_pile": int(cells), "seeds": int(seeds),
+            "one_pile_s": alone_s, "piles_side_by_side": int(args.candidate_piles), "side_by_side_s": together_s,
+            "s_per_pile_side_by_side": together_s / args.candidate_piles, "identical_results": bool(identical),
+            "optimize_partitions_stats": {name: int(value) for name, value in
+                                          zip(("passes", "visits", "moves", "skipped", "batches"), xt.last_optimize_stats[:5])},
+            "note": "host arrays in, partition out (uploads and the relayout to the incoming layout included); one CTA = one "
+                    "SM per pile, one host thread and stream per pile"}
 
 
 def ncu_traffic(kernel, cells, features):

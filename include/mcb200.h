@@ -36,6 +36,9 @@ int mcb_version(void);
 int mcb_device_count(void);
 /* Select the CUDA device of the calling thread; fails unless it is compute capability 10.x. */
 int mcb_set_device(int device);
+/* The device of the calling thread.  The current device is per host thread and a new thread starts on device 0, so
+ * worker threads of a process that drives another GPU call mcb_set_device before anything else. */
+int mcb_current_device(int* device);
 int mcb_synchronize(void* stream);
 /* Streaming multiprocessors of the calling thread's device: how many one-CTA optimisations (mcb_host_choose_seeds,
  * mcb_host_optimize_partitions, each on its caller thread's own stream) run side by side. */

@@ -142,7 +142,7 @@ int mcb_host_correlate_dense_f32(const float* input, int64_t rows, int64_t colum
     MCB_TRY(upload_matrix(d_in, input, rows, columns, row_stride, stream));
     MCB_TRY(d_out.alloc((size_t)rows * rows * sizeof(float), stream));
     MCB_TRY(correlate_f32_device(d_in.as<float>(), rows, columns, nullptr, 0, 0, columns, d_out.as<float>(), rows, 1, 0, stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, (size_t)rows * rows * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, (size_t)rows * rows * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -156,7 +156,7 @@ int mcb_host_correlate_dense_f64(const double* input, int64_t rows, int64_t colu
     MCB_TRY(upload_matrix(d_in, input, rows, columns, row_stride, stream));
     MCB_TRY(d_out.alloc((size_t)rows * rows * sizeof(float), stream));
     MCB_TRY(correlate_f64_device(d_in.as<double>(), rows, columns, nullptr, 0, 0, columns, d_out.as<float>(), rows, 1, stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, (size_t)rows * rows * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, (size_t)rows * rows * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -174,7 +174,7 @@ int mcb_host_cross_correlate_dense_f32(const float* first, int64_t first_rows, i
     MCB_TRY(d_out.alloc((size_t)first_rows * second_rows * sizeof(float), stream));
     MCB_TRY(correlate_f32_device(d_a.as<float>(), first_rows, columns, d_b.as<float>(), second_rows, columns, columns,
                                  d_out.as<float>(), second_rows, 0, 0, stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, (size_t)first_rows * second_rows * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, (size_t)first_rows * second_rows * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -192,7 +192,7 @@ int mcb_host_cross_correlate_dense_f64(const double* first, int64_t first_rows, 
     MCB_TRY(d_out.alloc((size_t)first_rows * second_rows * sizeof(float), stream));
     MCB_TRY(correlate_f64_device(d_a.as<double>(), first_rows, columns, d_b.as<double>(), second_rows, columns, columns,
                                  d_out.as<float>(), second_rows, 0, stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, (size_t)first_rows * second_rows * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, (size_t)first_rows * second_rows * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -208,7 +208,7 @@ int mcb_host_pairs_correlate_dense_f32(const float* first, int64_t first_stride,
     MCB_TRY(upload_matrix(d_b, second, rows, columns, second_stride, stream));
     MCB_TRY(d_out.alloc((size_t)rows * sizeof(float), stream));
     MCB_TRY(pairs_rows_f32(d_a.as<float>(), d_b.as<float>(), rows, columns, d_out.as<float>(), stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, (size_t)rows * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, (size_t)rows * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -224,7 +224,7 @@ int mcb_host_pairs_correlate_dense_f64(const double* first, int64_t first_stride
     MCB_TRY(upload_matrix(d_b, second, rows, columns, second_stride, stream));
     MCB_TRY(d_out.alloc((size_t)rows * sizeof(float), stream));
     MCB_TRY(pairs_rows_f64(d_a.as<double>(), d_b.as<double>(), rows, columns, d_out.as<float>(), stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, (size_t)rows * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, (size_t)rows * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }

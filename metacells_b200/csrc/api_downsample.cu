@@ -44,7 +44,7 @@ int mcb_host_downsample_compressed_f32_i32_f32(const float* data, const int32_t*
     MCB_CUDA(cudaMemcpyAsync(d_samples.ptr, samples, bands * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
     MCB_TRY(downsample_launch(d_data.as<float>(), d_out.as<float>(), d_indptr.as<int32_t>(), d_samples.as<int32_t>(), 0,
                               bands, 0, widest, random_seed, 1, stream));
-    MCB_CUDA(cudaMemcpyAsync(out, d_out.ptr, nnz * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(out, d_out.ptr, nnz * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -72,7 +72,7 @@ int mcb_host_downsample_dense_f32_f32(const float* input, float* output, const i
     MCB_CUDA(cudaMemcpyAsync(d_samples.ptr, samples, rows * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
     MCB_TRY(downsample_launch(d_in.as<float>(), d_out.as<float>(), nullptr, d_samples.as<int32_t>(), 0, rows, columns,
                               columns, random_seed, 1, stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, bytes, cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, bytes, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }
@@ -90,7 +90,7 @@ int mcb_host_downsample_array_f32_f32(const float* input, float* output, int64_t
     MCB_CUDA(cudaMemcpyAsync(d_out.ptr, output, size * sizeof(float), cudaMemcpyHostToDevice, stream));
     MCB_TRY(downsample_launch(d_in.as<float>(), d_out.as<float>(), nullptr, nullptr, samples, 1, size, size, random_seed,
                               0, stream));
-    MCB_CUDA(cudaMemcpyAsync(output, d_out.ptr, size * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(output, d_out.ptr, size * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }

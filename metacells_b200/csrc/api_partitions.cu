@@ -54,7 +54,7 @@ int partitions_host(const float* out_w, const int32_t* out_idx, const int32_t* o
                               cooldown_pass, cooldown_node, d_partition.as<int32_t>(), d_mask.as<int8_t>(), mask_count,
                               cold_temperature, optimize, with_orphans, score, stats, stream));
     if (optimize) {
-        MCB_CUDA(cudaMemcpyAsync(partition_of_nodes, d_partition.ptr, size_t(nodes) * 4, cudaMemcpyDeviceToHost, stream));
+        MCB_TRY(copy_to_host(partition_of_nodes, d_partition.ptr, size_t(nodes) * 4, stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
     }
     return MCB_OK;
@@ -125,7 +125,7 @@ int mcb_host_glibc_log_f64(const double* values, double* logs, int64_t count) {
         glibc_log_kernel<<<int(std::min<int64_t>(ceil_div(count, 256), 4096)), 256, 0, stream>>>(input.as<double>(),
                                                                                                  output.as<double>(), count);
         MCB_LAUNCH_CHECK();
-        MCB_CUDA(cudaMemcpyAsync(logs, output.ptr, size_t(count) * 8, cudaMemcpyDeviceToHost, stream));
+        MCB_TRY(copy_to_host(logs, output.ptr, size_t(count) * 8, stream));
     }
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;

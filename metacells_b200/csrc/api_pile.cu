@@ -73,7 +73,7 @@ int check_status(mcb_pile* pile) {
         return MCB_OK;
     }
     int status = 0;
-    MCB_CUDA(cudaMemcpyAsync(&status, pile->status.ptr, sizeof(int), cudaMemcpyDeviceToHost, pile->stream));
+    MCB_TRY(copy_to_host(&status, pile->status.ptr, sizeof(int), pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     MCB_REQUIRE(status != 3, "downsample: a cell totals more than the maximum given to mcb_pile_set_max_cell_total");
     MCB_REQUIRE(status == 0, "downsample: a cell totals 2^32 UMIs or more");
@@ -102,6 +102,9 @@ int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_
     pile->cells = cells;
     pile->genes = genes;
     MCB_TRY(finish_create(pile.get(), indptr));
+    // the calling thread's own stream: piles of different host threads run side by side, and one thread's pile fills
+    // the gaps the other's host-side steps leave
+    MCB_TRY(thread_stream(&pile->stream));
     cudaStream_t stream = pile->stream;
     MCB_TRY(pile->own_data.alloc((size_t)pile->nnz * sizeof(float), stream));
     MCB_TRY(pile->own_indices.alloc((size_t)pile->nnz * sizeof(int32_t), stream));
@@ -175,7 +178,7 @@ int mcb_pile_create_dev(const float* data, const int32_t* indices, const int32_t
     pile->genes = genes;
     pile->stream = (cudaStream_t)stream;
     std::vector<int32_t> host_indptr((size_t)cells + 1);
-    MCB_CUDA(cudaMemcpyAsync(host_indptr.data(), indptr, (size_t)(cells + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, pile->stream));
+    MCB_TRY(copy_to_host(host_indptr.data(), indptr, (size_t)(cells + 1) * sizeof(int32_t), pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     MCB_TRY(finish_create(pile.get(), host_indptr.data()));
     pile->data = data;
@@ -228,7 +231,7 @@ int mcb_pile_gene_totals(mcb_pile* pile, float* totals) {
         MCB_TRY(column_totals_launch(pile->data, pile->indices, pile->nnz, pile->genes, device.as<float>(), pile->stream));
         source = device.as<float>();
     }
-    MCB_CUDA(cudaMemcpyAsync(totals, source, (size_t)pile->genes * sizeof(float), cudaMemcpyDeviceToHost, pile->stream));
+    MCB_TRY(copy_to_host(totals, source, (size_t)pile->genes * sizeof(float), pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     return MCB_OK;
 }
@@ -236,7 +239,7 @@ int mcb_pile_gene_totals(mcb_pile* pile, float* totals) {
 int mcb_pile_read_downsampled(mcb_pile* pile, float* data) {
     MCB_REQUIRE(pile != nullptr && pile->has_downsampled, "pile: not downsampled yet");
     MCB_TRY(check_status(pile));
-    MCB_CUDA(cudaMemcpyAsync(data, pile->downsampled.ptr, (size_t)pile->nnz * sizeof(float), cudaMemcpyDeviceToHost, pile->stream));
+    MCB_TRY(copy_to_host(data, pile->downsampled.ptr, (size_t)pile->nnz * sizeof(float), pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     return MCB_OK;
 }
@@ -295,7 +298,7 @@ int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t featur
                                      min_key, stream));
     trace_lap("similarity: correlate", stream);
     int flags[2] = {0, 0};
-    MCB_CUDA(cudaMemcpyAsync(flags, d_flag.ptr, sizeof(flags), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(flags, d_flag.ptr, sizeof(flags), stream));
     MCB_TRY(check_status(pile));  // synchronises the stream
     MCB_REQUIRE((flags[1] & 1) == 0, "pile: a feature gene is out of range");
     MCB_REQUIRE((flags[1] & 2) == 0, "pile: a feature gene is listed twice");
@@ -337,7 +340,7 @@ int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host) {
     MCB_TRY(collect_top_launch(count, totals, 1, pile->genes, pile->genes, pile->top_genes.as<int32_t>(),
                                unused.as<float>(), 0, stream));
     if (genes_host != nullptr) {
-        MCB_CUDA(cudaMemcpyAsync(genes_host, pile->top_genes.ptr, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        MCB_TRY(copy_to_host(genes_host, pile->top_genes.ptr, (size_t)count * sizeof(int32_t), stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
     }
     return MCB_OK;

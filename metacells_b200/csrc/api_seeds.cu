@@ -46,7 +46,7 @@ int mcb_host_choose_seeds(const float* outgoing_weights, const int32_t* outgoing
     MCB_TRY(seeds_launch(d_out_w.as<float>(), d_out_idx.as<int32_t>(), d_out_ptr.as<int32_t>(), d_in_w.as<float>(),
                          d_in_idx.as<int32_t>(), d_in_ptr.as<int32_t>(), nodes, random_seed, max_seeds_count,
                          min_seed_size_quantile, max_seed_size_quantile, d_seeds.as<int32_t>(), seeds_count, stream));
-    MCB_CUDA(cudaMemcpyAsync(seed_of_nodes, d_seeds.ptr, size_t(nodes) * 4, cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(seed_of_nodes, d_seeds.ptr, size_t(nodes) * 4, stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }

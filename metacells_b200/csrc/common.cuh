@@ -81,7 +81,17 @@ struct Scratch {
     }
 };
 
+// Device -> host copy of a result the caller waits for.  Waits for the stream FIRST: a copy into pageable memory waits
+// for the stream's earlier work inside the driver call, and host threads driving other streams cannot launch meanwhile.
+static inline int copy_to_host(void* host, const void* device, size_t bytes, cudaStream_t stream) {
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    if (bytes)
+        MCB_CUDA(cudaMemcpyAsync(host, device, bytes, cudaMemcpyDeviceToHost, stream));
+    return MCB_OK;
+}
+
 int sm_count();
+int allow_dynamic_shared(const void* kernel, size_t bytes);  // opt in to `bytes` of dynamic shared memory (only ever raised)
 int thread_stream(cudaStream_t* stream);  // the calling host thread's own stream on the current device
 // Developer aid: with MCB_TRACE=1 in the environment, synchronises `stream` and prints the host time
 // since the previous call on stderr.

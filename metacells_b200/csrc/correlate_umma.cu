@@ -390,7 +390,7 @@ int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, 
     p.absolute = absolute;
     p.min_key = min_key;
     const int grid = (int)std::min<int64_t>((int64_t)order.size(), sm_count());
-    MCB_CUDA(cudaFuncSetAttribute(correlate_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UMMA_SMEM));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(correlate_umma_kernel), (size_t)UMMA_SMEM));
     MCB_PROFILED("correlate_umma", stream, correlate_umma_kernel<<<(unsigned)grid, UMMA_THREADS, UMMA_SMEM, stream>>>(map_a_hi, map_a_lo, map_b_hi, map_b_lo, p));
     MCB_LAUNCH_CHECK();
     return MCB_OK;

@@ -494,7 +494,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
         MCB_PROFILED("downsample_totals", stream,
                      max_row_total_kernel<<<(unsigned)ceil_div(rows, 8), 256, 0, stream>>>(p, counters.as<unsigned long long>()));
         MCB_LAUNCH_CHECK();
-        MCB_CUDA(cudaMemcpyAsync(&max_total, counters.ptr, sizeof(max_total), cudaMemcpyDeviceToHost, stream));
+        MCB_TRY(copy_to_host(&max_total, counters.ptr, sizeof(max_total), stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
     }
     if (max_total == 0) {
@@ -517,10 +517,10 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
         per_sm = std::max(1, std::min(per_sm, 2048 / (warps * 32)));
         const int64_t grid = std::min<int64_t>(ceil_div(rows, warps), (int64_t)sm_count() * per_sm);
         if (prefix_array) {
-            MCB_CUDA(cudaFuncSetAttribute(downsample_warp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(downsample_warp_kernel<true>), (size_t)smem_bytes));
             MCB_PROFILED("downsample", stream, downsample_warp_kernel<true><<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
         } else {
-            MCB_CUDA(cudaFuncSetAttribute(downsample_warp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(downsample_warp_kernel<false>), (size_t)smem_bytes));
             MCB_PROFILED("downsample", stream, downsample_warp_kernel<false><<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
         }
         MCB_LAUNCH_CHECK();
@@ -543,7 +543,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
         MCB_TRY(workspace.alloc((size_t)grid * 2 * (size_t)max_row_size * sizeof(uint32_t), stream));
         p.workspace = workspace.as<uint32_t>();
     }
-    MCB_CUDA(cudaFuncSetAttribute(downsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(downsample_kernel), (size_t)smem_bytes));
     MCB_PROFILED("downsample", stream, downsample_kernel<<<(unsigned)grid, DS_THREADS, smem_bytes, stream>>>(p));
     MCB_LAUNCH_CHECK();
     if (column_totals) {
@@ -551,7 +551,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
         MCB_LAUNCH_CHECK();
     }
     int host_flag = 0;
-    MCB_CUDA(cudaMemcpyAsync(&host_flag, flag.ptr, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(&host_flag, flag.ptr, sizeof(int), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     if (host_flag == 1)
         return fail(MCB_ERR_ARG, "downsample: a row is wider than the stated max_row_size");

@@ -897,9 +897,9 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
     MCB_LAUNCH_CHECK();
     int flags_host[8];
     int edges_host[2];
-    MCB_CUDA(cudaMemcpyAsync(flags_host, flags, sizeof(flags_host), cudaMemcpyDeviceToHost, stream));
-    MCB_CUDA(cudaMemcpyAsync(&edges_host[0], out_ptr + n, sizeof(int), cudaMemcpyDeviceToHost, stream));
-    MCB_CUDA(cudaMemcpyAsync(&edges_host[1], in_ptr + n, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(flags_host, flags, sizeof(flags_host), stream));
+    MCB_TRY(copy_to_host(&edges_host[0], out_ptr + n, sizeof(int), stream));
+    MCB_TRY(copy_to_host(&edges_host[1], in_ptr + n, sizeof(int), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     MCB_REQUIRE(flags_host[1] == 0, "failed assert: partition_index >= 0");  // partitions.cpp:93
     const int partitions = flags_host[0] + 1;
@@ -952,7 +952,7 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
                      partition_of_nodes, mass_of_nodes, table.as<Entry>(), n, partitions, sizes.as<int32_t>(),
                      masses.as<double>(), scores.as<double>(), flags + 2));
     MCB_LAUNCH_CHECK();
-    MCB_CUDA(cudaMemcpyAsync(flags_host, flags, sizeof(flags_host), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(flags_host, flags, sizeof(flags_host), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     MCB_REQUIRE((flags_host[2] & 1) == 0, "failed assert: the outgoing weights of every node sum to 1");  // :182-183
     MCB_REQUIRE((flags_host[2] & 2) == 0, "failed assert: total_incoming_weights > 0");                    // :123
@@ -991,7 +991,8 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
         params.seed = random_seed;
         params.result = result.as<double>();
         params.stats = stats_device.as<long long>();
-        MCB_CUDA(cudaFuncSetAttribute(optimize_partitions_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(shared_bytes)));
+        // the device's limit, once: optimisations of several host threads run side by side
+        MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(optimize_partitions_kernel), std::max<size_t>(shared_bytes, shared_limit - 4096)));
         MCB_PROFILED("optimize_partitions", stream,
                      optimize_partitions_kernel<<<1, OPT_THREADS, shared_bytes, stream>>>(params));
         MCB_LAUNCH_CHECK();
@@ -1002,8 +1003,8 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
         MCB_LAUNCH_CHECK();
     }
     long long stats_host[16];
-    MCB_CUDA(cudaMemcpyAsync(score, result.ptr, 8, cudaMemcpyDeviceToHost, stream));
-    MCB_CUDA(cudaMemcpyAsync(stats_host, stats_device.ptr, sizeof(stats_host), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(score, result.ptr, 8, stream));
+    MCB_TRY(copy_to_host(stats_host, stats_device.ptr, sizeof(stats_host), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     MCB_REQUIRE(stats_host[5] == 0, "failed assert: no candidate partition was chosen (partitions.cpp:1071)");
     if (stats)

@@ -247,7 +247,7 @@ int ordered_top_launch(const float* values, int64_t rows, int64_t columns, int64
     p.out_indices = out_indices;
     p.out_values = out_values;
     const size_t smem = ordered_top_smem();
-    MCB_CUDA(cudaFuncSetAttribute(ordered_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(ordered_top_kernel), (size_t)smem));
     const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 16);
     MCB_PROFILED("ordered_top", stream, ordered_top_kernel<<<(unsigned)grid, PT_THREADS, smem, stream>>>(p));
     MCB_LAUNCH_CHECK();
@@ -333,8 +333,8 @@ int mcb_host_project_top_f32(const float* query, int64_t query_rows, int64_t que
     MCB_TRY(d_values.alloc((size_t)query_rows * k * sizeof(float), stream));
     MCB_TRY(project_top_device(d_query.as<float>(), query_rows, columns, d_atlas.as<float>(), atlas_rows, columns, columns, k,
                                d_indices.as<int32_t>(), d_values.as<float>(), stream));
-    MCB_CUDA(cudaMemcpyAsync(out_indices, d_indices.ptr, (size_t)query_rows * k * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-    MCB_CUDA(cudaMemcpyAsync(out_correlations, d_values.ptr, (size_t)query_rows * k * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(out_indices, d_indices.ptr, (size_t)query_rows * k * sizeof(int32_t), stream));
+    MCB_TRY(copy_to_host(out_correlations, d_values.ptr, (size_t)query_rows * k * sizeof(float), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }

@@ -251,7 +251,7 @@ template <int ITEMS>
 int rank_matrix_merge_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, cudaStream_t stream,
                              const int* row_list = nullptr, const int* row_count = nullptr) {
     const size_t smem_bytes = (size_t)(MS_THREADS * ITEMS + MS_THREADS * ITEMS / 16 + 1) * 8;
-    MCB_CUDA(cudaFuncSetAttribute(rank_matrix_merge_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(rank_matrix_merge_kernel<ITEMS>), (size_t)smem_bytes));
     const int64_t grid = row_list != nullptr ? std::min<int64_t>(rows, (int64_t)sm_count() * 4) : std::min<int64_t>(rows, 1 << 20);
     MCB_PROFILED(row_list != nullptr ? "rank_matrix_ties" : "rank_matrix", stream,
                  rank_matrix_merge_kernel<ITEMS><<<(unsigned)grid, MS_THREADS, smem_bytes, stream>>>(
@@ -503,7 +503,7 @@ int rank_matrix_bucket_launch(float* matrix, int64_t rows, int64_t columns, int6
     Scratch passed;  // [0]: count, [1..]: the rows passed on to the merge sort
     MCB_TRY(passed.alloc((size_t)(rows + 1) * sizeof(int), stream));
     MCB_CUDA(cudaMemsetAsync(passed.ptr, 0, sizeof(int), stream));
-    MCB_CUDA(cudaFuncSetAttribute(rank_matrix_bucket_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Plan::SMEM));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(rank_matrix_bucket_kernel<ITEMS>), (size_t)Plan::SMEM));
     MCB_PROFILED("rank_matrix", stream, rank_matrix_bucket_kernel<ITEMS><<<(unsigned)std::min<int64_t>(rows, 1 << 20), MS_THREADS, Plan::SMEM, stream>>>(
                      matrix, rows, (int)columns, row_stride, ascending, passed.as<int>() + 1, passed.as<int>()));
     MCB_LAUNCH_CHECK();
@@ -559,7 +559,7 @@ int rank_matrix_launch(float* matrix, int64_t rows, int64_t columns, int64_t row
         MCB_TRY(workspace.alloc((size_t)grid * p.workspace_stride, stream));
         p.workspace = workspace.as<uint8_t>();
     }
-    MCB_CUDA(cudaFuncSetAttribute(rank_matrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(rank_matrix_kernel), (size_t)smem_bytes));
     MCB_PROFILED("rank_matrix", stream, rank_matrix_kernel<<<(unsigned)grid, RM_THREADS, smem_bytes, stream>>>(p));
     MCB_LAUNCH_CHECK();
     return MCB_OK;
@@ -892,7 +892,7 @@ int rank_rows_launch(const float* matrix, int64_t rows, int64_t columns, int64_t
     MCB_REQUIRE(columns < (1ll << 31), "rank_rows: too many columns");
     int cache_capacity = columns <= 16384 ? (int)columns : (columns <= 48 * 1024 ? (int)columns : 0);
     const size_t smem_bytes = (size_t)cache_capacity * 4;
-    MCB_CUDA(cudaFuncSetAttribute(rank_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(rank_rows_kernel), (size_t)smem_bytes));
     const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
     MCB_PROFILED("rank_rows", stream, rank_rows_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(matrix, rows, columns, row_stride, output, (int)rank,
                                                                         cache_capacity));
@@ -921,7 +921,7 @@ int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, in
     if (columns <= CT_MAX_CACHED && (size_t)columns * 8 + CT_BINS * 4 + kept_bytes <= 220 * 1024) {
         p.cache_capacity = (int)columns;
         const size_t cached_bytes = (size_t)columns * 8 + CT_BINS * 4 + kept_bytes;
-        MCB_CUDA(cudaFuncSetAttribute(collect_top_cached_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cached_bytes));
+        MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(collect_top_cached_kernel), (size_t)cached_bytes));
         const int64_t cached_grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
         MCB_PROFILED("collect_top", stream, collect_top_cached_kernel<<<(unsigned)cached_grid, SEL_THREADS, cached_bytes, stream>>>(p));
         MCB_LAUNCH_CHECK();
@@ -929,7 +929,7 @@ int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, in
     }
     p.cache_capacity = ((size_t)columns * 4 + kept_bytes <= 200 * 1024) ? (int)columns : 0;
     const size_t smem_bytes = (size_t)p.cache_capacity * 4 + kept_bytes;
-    MCB_CUDA(cudaFuncSetAttribute(collect_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(collect_top_kernel), (size_t)smem_bytes));
     const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 8);
     MCB_PROFILED("collect_top", stream, collect_top_kernel<<<(unsigned)grid, SEL_THREADS, smem_bytes, stream>>>(p));
     MCB_LAUNCH_CHECK();

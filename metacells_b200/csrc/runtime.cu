@@ -59,7 +59,33 @@ int prepare_memory_pool() {
     MCB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
     unsigned long long threshold = ~0ull;
     MCB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+    // Piles of different host threads run on streams of their own: never make one stream wait for another just to take
+    // over a block it freed (the pool grows a little instead).
+    int no = 0;
+    MCB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowInternalDependencies, &no));
     prepared.fetch_or(bit);
+    return MCB_OK;
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per kernel and device, and again only to raise it: setting
+// the attribute while instances of the kernel run waits for them, which queues up calls that would otherwise run side
+// by side (one CTA each, on their own streams).
+int allow_dynamic_shared(const void* kernel, size_t bytes) {
+    static std::mutex mutex;
+    static std::vector<std::pair<std::pair<int, const void*>, size_t>> allowed;
+    int device = 0;
+    MCB_CUDA(cudaGetDevice(&device));
+    std::lock_guard<std::mutex> lock(mutex);
+    for (auto& entry : allowed)
+        if (entry.first.first == device && entry.first.second == kernel) {
+            if (entry.second >= bytes)
+                return MCB_OK;
+            MCB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+            entry.second = bytes;
+            return MCB_OK;
+        }
+    MCB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+    allowed.push_back({{device, kernel}, bytes});
     return MCB_OK;
 }
 
@@ -130,6 +156,14 @@ int mcb_reserve_scratch(long long bytes) {
         MCB_TRY(block.alloc(size_t(bytes), stream));
     }
     MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+// The CUDA device of the calling thread (a new host thread starts on device 0: workers of a process that drives
+// another GPU select it with mcb_set_device first).
+int mcb_current_device(int* device) {
+    MCB_REQUIRE(device != nullptr, "mcb_current_device: null argument");
+    MCB_CUDA(cudaGetDevice(device));
     return MCB_OK;
 }
 

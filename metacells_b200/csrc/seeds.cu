@@ -694,7 +694,7 @@ int seeds_launch(const float* out_w, const int32_t* out_idx, const int32_t* out_
     MCB_PROFILED("seeds_prepare", stream, seeds_prepare_kernel<<<int(std::min<int64_t>(ceil_div(n, 8), int64_t(sm_count()) * 8)), 256, 0, stream>>>(
                      in_idx, in_ptr, seed_of_nodes, n, connected.as<int32_t>(), result.as<int32_t>()));
     MCB_LAUNCH_CHECK();
-    MCB_CUDA(cudaMemcpyAsync(result_host, result.ptr, sizeof(result_host), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(result_host, result.ptr, sizeof(result_host), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
 
     SeedsParams params;
@@ -728,10 +728,10 @@ int seeds_launch(const float* out_w, const int32_t* out_idx, const int32_t* out_
         params.select_global = select_global.ptr;
         shared_bytes = fixed_bytes;
     }
-    MCB_CUDA(cudaFuncSetAttribute(choose_seeds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(shared_bytes)));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(choose_seeds_kernel), budget));
     MCB_PROFILED("choose_seeds", stream, choose_seeds_kernel<<<1, SEED_THREADS, shared_bytes, stream>>>(params));
     MCB_LAUNCH_CHECK();
-    MCB_CUDA(cudaMemcpyAsync(result_host, result.ptr, sizeof(result_host), cudaMemcpyDeviceToHost, stream));
+    MCB_TRY(copy_to_host(result_host, result.ptr, sizeof(result_host), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     MCB_REQUIRE(result_host[0] != SEEDS_ASSERT, "choose_seeds: a FastAssert of the reference fails on this input");
     MCB_REQUIRE(result_host[0] != SEEDS_UNLUCKY_DRAW,

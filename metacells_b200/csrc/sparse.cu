@@ -351,7 +351,7 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
         max_band_kernel<<<(unsigned)std::min<int64_t>(ceil_div(bands, 256), 1024), 256, 0, stream>>>(indptr, bands, widest.as<int32_t>());
         MCB_LAUNCH_CHECK();
         int32_t host = 0;
-        MCB_CUDA(cudaMemcpyAsync(&host, widest.ptr, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        MCB_TRY(copy_to_host(&host, widest.ptr, sizeof(int32_t), stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
         widest_band = host;
     }
@@ -364,7 +364,7 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
     Scratch workspace;
     if (padded > smem_capacity)
         MCB_TRY(workspace.alloc((size_t)grid * padded * 8, stream));
-    MCB_CUDA(cudaFuncSetAttribute(sort_bands_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(sort_bands_kernel), (size_t)smem_bytes));
     MCB_PROFILED("sort_bands", stream, sort_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(data, indices, indptr, bands, smem_capacity,
                                                                           workspace.as<unsigned long long>(), padded));
     MCB_LAUNCH_CHECK();
@@ -437,7 +437,7 @@ int sort_distinct_indices_launch(float* data, int32_t* indices, const int32_t* i
         max_band_kernel<<<(unsigned)std::min<int64_t>(ceil_div(bands, 256), 1024), 256, 0, stream>>>(indptr, bands, widest.as<int32_t>());
         MCB_LAUNCH_CHECK();
         int32_t host = 0;
-        MCB_CUDA(cudaMemcpyAsync(&host, widest.ptr, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        MCB_TRY(copy_to_host(&host, widest.ptr, sizeof(int32_t), stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
         widest_band = host;
     }
@@ -445,7 +445,7 @@ int sort_distinct_indices_launch(float* data, int32_t* indices, const int32_t* i
         return sort_compressed_indices_launch(data, indices, indptr, bands, widest_band, stream);
     const size_t words = (size_t)((index_range + 31) >> 5);
     const size_t smem_bytes = ((words * 8 + 15) & ~(size_t)15) + (size_t)widest_band * 8;
-    MCB_CUDA(cudaFuncSetAttribute(sort_distinct_bands_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(sort_distinct_bands_kernel), (size_t)smem_bytes));
     const int64_t grid = std::min<int64_t>(bands, (int64_t)sm_count() * 8);
     MCB_PROFILED("sort_bands", stream, sort_distinct_bands_kernel<<<(unsigned)grid, SP_THREADS, smem_bytes, stream>>>(
                      data, indices, indptr, bands, (int)index_range));

@@ -191,14 +191,37 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
 
 
 def compute_piles_knn_graphs(piles: Iterable[sp.csr_matrix], *, features: int = 2000, random_seed: int = 123456,
-                             pin: bool = False) -> Iterator[Tuple[sp.csr_matrix, dict]]:
+                             pin: bool = False, workers: int = 1) -> Iterator[Tuple[sp.csr_matrix, dict]]:
     """``compute_pile_knn_graph`` over the piles of one GPU, one after the other as ``ut.parallel_map`` hands them to a
     worker (pipeline/divide_and_conquer.py:1264-1295; every pile gets the same ``random_seed``, :1274-1279), with the
     upload of pile k + 1 started before the graph of pile k is asked for: it runs on the pile's copy stream under the
     kernels of pile k when the pile's arrays are page-locked (``mcb_pile_create_host`` copies from pageable memory
     synchronously).  ``pin=True`` page-locks the arrays of every pile for its lifetime; that costs more than it saves
     unless the arrays are reused, so a caller that streams piles keeps them in page-locked buffers of its own.
-    Yields ``(obs_outgoing_weights, details)`` per pile, in order; results do not depend on the overlap."""
+    Yields ``(obs_outgoing_weights, details)`` per pile, in order; results do not depend on the overlap.
+
+    ``workers > 1``: that many host threads walk the piles instead (``compute_pile_knn_graph`` each, on the thread's own
+    stream), so one pile's upload, read-back and host-side steps lie under another pile's kernels; at most
+    ``workers + 1`` piles are taken from ``piles`` ahead of the one being yielded."""
+    if workers > 1:
+        from collections import deque
+        from concurrent.futures import ThreadPoolExecutor
+
+        device = ctypes.c_int(0)
+        check(lib().mcb_current_device(ctypes.byref(device)))
+
+        def on_device() -> None:  # the current device is per thread
+            check(lib().mcb_set_device(device))
+
+        with ThreadPoolExecutor(max_workers=int(workers), initializer=on_device) as pool:
+            in_flight: deque = deque()
+            for umis in piles:
+                in_flight.append(pool.submit(compute_pile_knn_graph, umis, features=features, random_seed=random_seed))
+                if len(in_flight) > workers:
+                    yield in_flight.popleft().result()
+            while in_flight:
+                yield in_flight.popleft().result()
+        return
 
     def start(umis: sp.csr_matrix):
         cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
@@ -300,5 +323,11 @@ def compute_piles_seed_partitions(piles, *, workers: Optional[int] = None, **arg
         count = ctypes.c_int(0)
         check(lib().mcb_device_sm_count(ctypes.byref(count)))
         workers = count.value
-    with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(piles)))) as pool:
+    device = ctypes.c_int(0)
+    check(lib().mcb_current_device(ctypes.byref(device)))
+
+    def on_device() -> None:  # the current device is per thread
+        check(lib().mcb_set_device(device))
+
+    with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(piles))), initializer=on_device) as pool:
         return list(pool.map(lambda pile: compute_pile_seed_partition(pile[0], pile[1], **arguments), piles))

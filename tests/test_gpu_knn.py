@@ -293,3 +293,21 @@ def test_piles_one_after_the_other_match_the_single_pile_path(pin):
         assert np.array_equal(details["feature_genes"], alone_details["feature_genes"])
         assert np.array_equal(weights.indptr, alone.indptr) and np.array_equal(weights.indices, alone.indices)
         assert np.array_equal(weights.data, alone.data)
+
+
+def test_piles_walked_by_several_threads_match_the_single_pile_path():
+    """`compute_piles_knn_graphs(workers=3)`: three host threads, each pile on its thread's own stream, the same graphs
+    in the same order as pile by pile."""
+    from synth import synth_umis
+
+    from metacells_b200 import pipeline
+
+    piles = [synth_umis(cells, 3000, seed=40 + cells) for cells in (400, 650, 300, 512, 380, 700, 450)]
+    together = list(pipeline.compute_piles_knn_graphs(iter(piles), features=300, workers=3))
+    assert len(together) == len(piles)
+    for umis, (weights, details) in zip(piles, together):
+        alone, alone_details = pipeline.compute_pile_knn_graph(umis, features=300)
+        assert details["k"] == alone_details["k"] and details["samples"] == alone_details["samples"]
+        assert np.array_equal(details["feature_genes"], alone_details["feature_genes"])
+        assert np.array_equal(weights.indptr, alone.indptr) and np.array_equal(weights.indices, alone.indices)
+        assert np.array_equal(weights.data, alone.data)
