@@ -15,6 +15,7 @@ parser.add_argument("--genes", type=int, default=8000)
 parser.add_argument("--threads", type=int, default=4)
 parser.add_argument("--profile", type=int, default=1)
 parser.add_argument("--reserve-mb", type=int, default=0)
+parser.add_argument("--device-arrays", type=int, default=0, help="1: the graph stays on the device (mcb_dev_optimize_partitions, a torch stream per thread)")
 parser.add_argument("--connections", type=int, default=0)
 args = parser.parse_args()
 SEED = 123456
@@ -32,10 +33,30 @@ _lib.call("mcb_profile_enable", ("int", args.profile))
 if args.reserve_mb:
     _lib.call("mcb_reserve_scratch", ("i64", args.reserve_mb << 20))
 origin = time.perf_counter()
+if args.device_arrays:
+    import torch
+    device_graph = [torch.from_numpy(array).cuda() for array in graph]
+    device_umis, device_mask = torch.from_numpy(cell_umis).cuda(), torch.from_numpy(mask).cuda()
+    torch.cuda.synchronize()
 def work(index, log):
     mine = seeds.copy()
     start = time.perf_counter() - origin
-    score = xt.optimize_partitions(*graph, SEED, cell_umis, *bounds, 0.02, 0.25, mine, mask, 0.98)
+    if args.device_arrays:
+        stream = torch.cuda.Stream()
+        partition = torch.from_numpy(mine).cuda()
+        torch.cuda.synchronize()
+        start = time.perf_counter() - origin
+        score = ctypes.c_double(0)
+        pointer = lambda tensor: ctypes.c_void_p(tensor.data_ptr())
+        function = _lib.lib().mcb_dev_optimize_partitions
+        function.restype = ctypes.c_int
+        _lib.check(function(*[pointer(tensor) for tensor in device_graph], ctypes.c_int64(args.cells), ctypes.c_uint32(SEED),
+                            pointer(device_umis), *[ctypes.c_double(bound) for bound in bounds], ctypes.c_double(0.02),
+                            ctypes.c_double(0.25), pointer(partition), pointer(device_mask), ctypes.c_int64(len(mask)),
+                            ctypes.c_double(0.98), None, ctypes.byref(score), ctypes.c_void_p(stream.cuda_stream)))
+        score = score.value
+    else:
+        score = xt.optimize_partitions(*graph, SEED, cell_umis, *bounds, 0.02, 0.25, mine, mask, 0.98)
     log[index] = (start, time.perf_counter() - origin, score)
 for threads in (1, args.threads):
     origin = time.perf_counter()
