@@ -495,7 +495,7 @@ def run_gpu_arm(args):
     # SURVEY 8d's algorithmic bytes: ranks read and write the whole square matrix; the downsample reads and writes the
     # pile's values and reads the row pointers; balance reads every rank once (count and fill passes are one stage).
     rank_line = hbm_line("rank_matrix_bucket_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, args.features),
-                         "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_rank_matrix_merge.txt")
+                         "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_rank_matrix_bucket_kernel.txt")
     downsample_line = hbm_line("downsample_warp_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, None, None)
     balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells, None, None)
     # the dominant kernel is the one with the largest share of the step
@@ -670,7 +670,7 @@ def ncu_traffic(kernel, cells, features):
     workload that was not captured."""
     if (cells, features) != (16000, 2000):
         return None
-    return {"correlate_umma": 3.302457e9 + 1.005782e9, "rank_matrix": 1.024111e9 + 0.964185e9}.get(kernel)
+    return {"correlate_umma": 3.302457e9 + 1.005782e9, "rank_matrix": 1.024083e9 + 0.970209e9}.get(kernel)
 
 
 _RESULT_FD = None
