@@ -91,24 +91,16 @@ __device__ __forceinline__ uint32_t pack_tile_best(float t, int column_in_tile) 
 }
 static_assert(BT == 64, "pack_tile_best keeps the column of a tile in 6 bits");
 
-// One CTA per pair of mirrored 64 x 64 rank tiles (I, J), I <= J: tile_a = ranks[rows of I][columns of J], tile_b =
-// ranks[rows of J][columns of I].  The product r_ij * r_ji is the same float32 for (i, j) and (j, i), so it is computed
-// once, for the rows of I ("side 0"), and serves the rows of J ("side 1") as the transpose: a lane owns two columns of
-// the tile, i.e. two rows of J, and walks down them while its warp walks the rows of I.
 template <bool FILL>
 __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
-    constexpr int WARPS = BAL_THREADS / 32;
-    constexpr int ROWS = BT / WARPS;  // consecutive rows of I per warp: a column's entries stay in row order
-    __shared__ float tile_a[BT][BT + 1];
-    __shared__ float tile_b[BT][BT + 1];
-    __shared__ int column_counts[WARPS][BT];
-    __shared__ uint32_t column_best[FILL ? 1 : WARPS][BT];
+    __shared__ float tile_a[BT][BT + 1];  // ranks[I rows][J columns]
+    __shared__ float tile_b[BT][BT + 1];  // ranks[J rows][I columns]
     int tile_i, tile_j;
     tile_of_block(blockIdx.x, &tile_i, &tile_j);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t n = p.n;
     const int64_t i0 = (int64_t)tile_i * BT, j0 = (int64_t)tile_j * BT;
-    for (int r = warp; r < BT; r += WARPS) {
+    for (int r = warp; r < BT; r += BAL_THREADS / 32) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             const int c = lane + 32 * half;
@@ -118,78 +110,59 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
     }
     __syncthreads();
     const uint32_t lower_lanes = lanemask_lt();
-    const bool mirrored = tile_i != tile_j;
-    // side 1, per lane: its two columns are the rows j0 + lane and j0 + lane + 32
-    int below[2] = {0, 0};          // kept entries of the column in this warp's rows
-    uint32_t best_down[2] = {0, 0}; // count pass: the column's best entry, packed with the row inside the tile
-    float product[ROWS][2];
-    uint32_t kept_down[2] = {0, 0};  // fill pass: bit k = the entry of this warp's k-th row is written for side 1
-    int64_t preserved_down[2] = {-1, -1};
-    if (FILL && mirrored) {
-#pragma unroll
-        for (int half = 0; half < 2; ++half)
-            if (j0 + lane + 32 * half < n) preserved_down[half] = p.best_index[j0 + lane + 32 * half];
-    }
-#pragma unroll
-    for (int k = 0; k < ROWS; ++k) {
-        const int r = warp * ROWS + k;
-        const int64_t row = i0 + r;
-        // The threshold on the balanced rank (knn_graph.py:333-334) is a threshold on the float32 product: every step from
-        // the product to the comparison is monotone, and the host found the largest product that passes with the same
-        // float32 steps.  Only the entries that pass (a few percent) pay for the square root.
-        bool valid[2], passes[2], kept[2];
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int c = lane + 32 * half;
-            const int64_t column = j0 + c;
-            product[k][half] = __fmul_rn(tile_a[r][c], tile_b[c][r]);
-            valid[half] = row < n && column < n;
-            passes[half] = valid[half] && product[k][half] <= p.keep_product;
-            kept[half] = passes[half] && column != row;
-        }
-        if (!FILL) {
-            // a row's largest t can only be an entry that passes, when there is one (rows without are redone by
-            // balance_best_kernel)
-            uint32_t best = 0;
-#pragma unroll
-            for (int half = 0; half < 2; ++half)
-                if (passes[half]) {
-                    const float t = balanced_t_of_product(product[k][half]);
-                    best = max(best, pack_tile_best(t, lane + 32 * half));
-                    if (mirrored) best_down[half] = max(best_down[half], pack_tile_best(t, r));
-                }
-            best = __reduce_max_sync(0xffffffffu, best);
-            const int count = __popc(__ballot_sync(0xffffffffu, kept[0])) + __popc(__ballot_sync(0xffffffffu, kept[1]));
-            if (lane == 0 && row < n) {
-                p.counts[row * p.tiles + tile_j] = count;
-                if (best != 0) {
-                    const float t = __fadd_rn(__fmul_rn((float)(best >> 6), 0.125f), 1048576.0f);
-                    const uint32_t column = (uint32_t)(j0 + (BT - 1 - (int)(best & (BT - 1))));
-                    atomicMax(&p.row_best[row], ((unsigned long long)float_to_ordered(t) << 32) | (uint32_t)~column);
-                }
-            }
-#pragma unroll
-            for (int half = 0; half < 2; ++half) below[half] += kept[half] ? 1 : 0;
-        } else {
-            const int64_t preserved = row < n ? (int64_t)p.best_index[row] : -1;
-            bool kept_here[2];
+    const int sides = tile_i == tile_j ? 1 : 2;
+    for (int side = 0; side < sides; ++side) {
+        // side 0: rows of I, columns of J; side 1: rows of J, columns of I
+        const int64_t row0 = side == 0 ? i0 : j0, col0 = side == 0 ? j0 : i0;
+        const int column_tile = side == 0 ? tile_j : tile_i;
+        for (int r = warp; r < BT; r += BAL_THREADS / 32) {
+            const int64_t row = row0 + r;
+            if (row >= n)
+                break;
+            // The threshold on the balanced rank (knn_graph.py:333-334) is a threshold on the float32 product: every step
+            // from the product to the comparison is monotone, and the host found the largest product that passes with the
+            // same float32 steps.  Only the entries that pass (a few percent) pay for the square root.
+            float product[2];
+            bool valid[2], passes[2], kept[2];
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
-                const int64_t column = j0 + lane + 32 * half;
-                kept_here[half] = kept[half] || (valid[half] && column == preserved);
-                if (mirrored && (kept[half] || (valid[half] && row == preserved_down[half]))) {
-                    kept_down[half] |= 1u << k;
-                    below[half] += 1;
-                }
+                const int c = lane + 32 * half;
+                const int64_t column = col0 + c;
+                const float mine = side == 0 ? tile_a[r][c] : tile_b[r][c];
+                const float other = side == 0 ? tile_b[c][r] : tile_a[c][r];
+                product[half] = __fmul_rn(mine, other);
+                valid[half] = column < n;
+                passes[half] = valid[half] && product[half] <= p.keep_product;
+                kept[half] = passes[half] && column != row;
             }
-            const uint32_t mask0 = __ballot_sync(0xffffffffu, kept_here[0]), mask1 = __ballot_sync(0xffffffffu, kept_here[1]);
-            if (row < n && (mask0 | mask1)) {
-                const int64_t base = (int64_t)p.indptr[row] + p.counts[row * p.tiles + tile_j];
+            if (!FILL) {
+                // the row's largest t can only be an entry that passes, when there is one (rows without are redone
+                // by balance_best_kernel)
+                uint32_t best = 0;
 #pragma unroll
                 for (int half = 0; half < 2; ++half)
-                    if (kept_here[half]) {
-                        const int64_t column = j0 + lane + 32 * half;
-                        float value = __fadd_rn(balanced_t_of_product(product[k][half]), p.shift);
+                    if (passes[half]) best = max(best, pack_tile_best(balanced_t_of_product(product[half]), lane + 32 * half));
+                best = __reduce_max_sync(0xffffffffu, best);
+                const int count = __popc(__ballot_sync(0xffffffffu, kept[0])) + __popc(__ballot_sync(0xffffffffu, kept[1]));
+                if (lane == 0) {
+                    p.counts[row * p.tiles + column_tile] = count;
+                    if (best != 0) {
+                        const float t = __fadd_rn(__fmul_rn((float)(best >> 6), 0.125f), 1048576.0f);
+                        const uint32_t column = (uint32_t)(col0 + (BT - 1 - (int)(best & (BT - 1))));
+                        atomicMax(&p.row_best[row], ((unsigned long long)float_to_ordered(t) << 32) | (uint32_t)~column);
+                    }
+                }
+            } else {
+                const int64_t preserved = p.best_index[row];
+#pragma unroll
+                for (int half = 0; half < 2; ++half) kept[half] = kept[half] || (valid[half] && col0 + lane + 32 * half == preserved);
+                const uint32_t mask0 = __ballot_sync(0xffffffffu, kept[0]), mask1 = __ballot_sync(0xffffffffu, kept[1]);
+                const int64_t base = (int64_t)p.indptr[row] + p.counts[row * p.tiles + column_tile];
+#pragma unroll
+                for (int half = 0; half < 2; ++half)
+                    if (kept[half]) {
+                        const int64_t column = col0 + lane + 32 * half;
+                        float value = __fadd_rn(balanced_t_of_product(product[half]), p.shift);
                         if (column == preserved)
                             value = fmaxf(value, 1.0f);  // knn_graph.py:331
                         const int64_t at = base + (half ? __popc(mask0) : 0) + __popc((half ? mask1 : mask0) & lower_lanes);
@@ -198,61 +171,6 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                     }
             }
         }
-    }
-    if (!mirrored)
-        return;
-    // side 1: the rows of J take the same entries, column by column
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        column_counts[warp][lane + 32 * half] = below[half];
-        if (!FILL) column_best[warp][lane + 32 * half] = best_down[half];
-    }
-    __syncthreads();
-    if (!FILL) {
-        if (warp == 0) {
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const int c = lane + 32 * half;
-                const int64_t row = j0 + c;
-                if (row >= n)
-                    continue;
-                int count = 0;
-                uint32_t best = 0;
-#pragma unroll
-                for (int w = 0; w < WARPS; ++w) {
-                    count += column_counts[w][c];
-                    best = max(best, column_best[w][c]);
-                }
-                p.counts[row * p.tiles + tile_i] = count;
-                if (best != 0) {
-                    const float t = __fadd_rn(__fmul_rn((float)(best >> 6), 0.125f), 1048576.0f);
-                    const uint32_t column = (uint32_t)(i0 + (BT - 1 - (int)(best & (BT - 1))));
-                    atomicMax(&p.row_best[row], ((unsigned long long)float_to_ordered(t) << 32) | (uint32_t)~column);
-                }
-            }
-        }
-        return;
-    }
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        if (kept_down[half] == 0)
-            continue;
-        const int c = lane + 32 * half;
-        const int64_t row = j0 + c;
-        int before = 0;
-        for (int w = 0; w < warp; ++w) before += column_counts[w][c];
-        int64_t at = (int64_t)p.indptr[row] + p.counts[row * p.tiles + tile_i] + before;
-#pragma unroll
-        for (int k = 0; k < ROWS; ++k)
-            if (kept_down[half] >> k & 1u) {
-                const int64_t column = i0 + warp * ROWS + k;
-                float value = __fadd_rn(balanced_t_of_product(product[k][half]), p.shift);
-                if (column == preserved_down[half])
-                    value = fmaxf(value, 1.0f);  // knn_graph.py:331
-                p.out_data[at] = value;
-                p.out_indices[at] = (int32_t)column;
-                ++at;
-            }
     }
 }
 
