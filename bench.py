@@ -372,18 +372,22 @@ def run_gpu_arm(args):
     def steps_e2e_workers(steps):
         """K end-to-end steps by the rank's worker threads: every thread walks its share of the piles one after the other
         (host CSR in, graph out into its own page-locked buffers, as step_e2e) on a stream of its own, so one thread's
-        upload, read-back and host-side gaps lie under the other threads' kernels.  Nothing is prefetched and nothing is
-        shared between the threads but the GPU."""
+        upload, read-back and host-side gaps lie under the other threads' kernels.  Nothing is prefetched; the threads
+        share the GPU and take turns uploading."""
         import threading
 
         shares = [steps // workers + (1 if index < steps % workers else 0) for index in range(workers)]
         edges, failures = [0] * workers, []
+        upload_turn = threading.Lock()  # one upload at a time has the whole link, under the other threads' kernels
 
         def walk(index):
             try:
                 library.call("mcb_set_device", ctypes.c_int(local_rank))  # the current device is per thread
                 for _ in range(shares[index]):
-                    edges[index] = step_e2e(buffers=worker_buffers[index])
+                    with upload_turn:
+                        pile = upload()
+                        library.call("mcb_pile_wait_upload", pile)
+                    edges[index] = step_e2e(pile, buffers=worker_buffers[index])
             except BaseException as failure:  # noqa: BLE001 (reported by the main thread)
                 failures.append(failure)
 
@@ -575,8 +579,12 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
     buffers_of_worker = [result] + [{name: torch.empty_like(tensor).pin_memory() for name, tensor in result.items()}
                                     for _ in range(workers - 1)]
 
+    upload_turn = threading.Lock()  # one upload at a time has the whole link, under the other threads' kernels
+
     def one_pile(size, buffers):
-        pile = upload(size)
+        with upload_turn:
+            pile = upload(size)
+            library.call("mcb_pile_wait_upload", pile)
         graph = hot_path(pile, ks[size])
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
@@ -590,7 +598,6 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
     def walk_piles(piles_of_run):
         """The rank's worker threads take the rank's piles off one list, largest first (a dynamic queue, as SURVEY 8e),
         each thread on a stream of its own: one pile's upload and read-back lie under another pile's kernels."""
-        import threading
 
         remaining = list(piles_of_run)
         lock = threading.Lock()

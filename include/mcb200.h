@@ -210,6 +210,9 @@ int mcb_host_unpin(const void* buffer);
 int mcb_pile_create_dev(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
                         void* stream, mcb_pile** out);
 int64_t mcb_pile_nnz(const mcb_pile* pile);
+/* Returns when the upload mcb_pile_create_host started has arrived.  Host threads that walk piles side by side take
+ * turns uploading (one upload at a time has the whole link, and falls under the other threads' kernels). */
+int mcb_pile_wait_upload(mcb_pile* pile);
 /* tools/downsample.py:99 -> downsample_compressed (downsample.cpp:171-192), every cell to `samples`. */
 int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed);
 int mcb_pile_read_downsampled(mcb_pile* pile, float* data); /* nnz values, same structure as the input */

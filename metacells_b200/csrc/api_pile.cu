@@ -365,6 +365,13 @@ int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t fea
 
 int64_t mcb_pile_nnz(const mcb_pile* pile) { return pile ? pile->nnz : 0; }
 
+int mcb_pile_wait_upload(mcb_pile* pile) {
+    MCB_REQUIRE(pile != nullptr, "pile: null handle");
+    if (pile->copy_stream)
+        MCB_CUDA(cudaStreamSynchronize(pile->copy_stream));
+    return MCB_OK;
+}
+
 void mcb_pile_free(mcb_pile* pile) { delete pile; }
 
 }  // extern "C"

@@ -85,6 +85,10 @@ class Pile:
             function.restype = ctypes.c_int
             check(function(self._handle, ctypes.c_uint64(int(max_cell_total))))
 
+    def wait_upload(self) -> None:
+        """Returns when the pile's upload has arrived (``mcb_pile_wait_upload``)."""
+        check(lib().mcb_pile_wait_upload(self._handle))
+
     def close(self) -> None:
         if getattr(self, "_handle", None):
             lib().mcb_pile_free(self._handle)  # waits for the upload
@@ -167,7 +171,7 @@ class Pile:
 
 
 def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature_genes: Optional[np.ndarray] = None,
-                           k: Optional[int] = None, random_seed: int = 123456) -> Tuple[sp.csr_matrix, dict]:
+                           k: Optional[int] = None, random_seed: int = 123456, upload_turn=None) -> Tuple[sp.csr_matrix, dict]:
     """The k-NN graph part of ``compute_direct_metacells`` for one pile: downsample (tools/downsample.py),
     feature genes, log-fraction, ``abs_pearson`` similarity, ``compute_obs_obs_knn_graph``.
     Returns ``(obs_outgoing_weights, details)``."""
@@ -176,7 +180,13 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
                             np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
     if k is None:
         k = knn_k_of_pile(umis.shape[0], cell_umis)
-    with Pile(umis, max_cell_total=float(cell_umis.max())) as pile:
+    if upload_turn is None:  # a lock shared by the threads that walk piles side by side: one upload at a time
+        pile = Pile(umis, max_cell_total=float(cell_umis.max()))
+    else:
+        with upload_turn:
+            pile = Pile(umis, max_cell_total=float(cell_umis.max()))
+            pile.wait_upload()
+    with pile:
         pile.downsample(samples, random_seed)
         selected_on_device = feature_genes is None
         if selected_on_device:
@@ -213,10 +223,14 @@ def compute_piles_knn_graphs(piles: Iterable[sp.csr_matrix], *, features: int = 
         def on_device() -> None:  # the current device is per thread
             check(lib().mcb_set_device(device))
 
+        import threading
+
+        upload_turn = threading.Lock()  # the threads take turns uploading: each upload under the others' kernels
         with ThreadPoolExecutor(max_workers=int(workers), initializer=on_device) as pool:
             in_flight: deque = deque()
             for umis in piles:
-                in_flight.append(pool.submit(compute_pile_knn_graph, umis, features=features, random_seed=random_seed))
+                in_flight.append(pool.submit(compute_pile_knn_graph, umis, features=features, random_seed=random_seed,
+                                             upload_turn=upload_turn))
                 if len(in_flight) > workers:
                     yield in_flight.popleft().result()
             while in_flight:
