@@ -372,22 +372,19 @@ def run_gpu_arm(args):
     def steps_e2e_workers(steps):
         """K end-to-end steps by the rank's worker threads: every thread walks its share of the piles one after the other
         (host CSR in, graph out into its own page-locked buffers, as step_e2e) on a stream of its own, so one thread's
-        upload, read-back and host-side gaps lie under the other threads' kernels.  Nothing is prefetched; the threads
-        share the GPU and take turns uploading."""
+        upload, read-back and host-side gaps lie under the other threads' kernels.  Nothing is prefetched and nothing is
+        shared between the threads but the GPU (taking turns at the upload was measured: no better here, worse over the
+        atlas, where it costs the overlap of a pile's own downsampling with its upload)."""
         import threading
 
         shares = [steps // workers + (1 if index < steps % workers else 0) for index in range(workers)]
         edges, failures = [0] * workers, []
-        upload_turn = threading.Lock()  # one upload at a time has the whole link, under the other threads' kernels
 
         def walk(index):
             try:
                 library.call("mcb_set_device", ctypes.c_int(local_rank))  # the current device is per thread
                 for _ in range(shares[index]):
-                    with upload_turn:
-                        pile = upload()
-                        library.call("mcb_pile_wait_upload", pile)
-                    edges[index] = step_e2e(pile, buffers=worker_buffers[index])
+                    edges[index] = step_e2e(buffers=worker_buffers[index])
             except BaseException as failure:  # noqa: BLE001 (reported by the main thread)
                 failures.append(failure)
 
@@ -579,12 +576,8 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
     buffers_of_worker = [result] + [{name: torch.empty_like(tensor).pin_memory() for name, tensor in result.items()}
                                     for _ in range(workers - 1)]
 
-    upload_turn = threading.Lock()  # one upload at a time has the whole link, under the other threads' kernels
-
     def one_pile(size, buffers):
-        with upload_turn:
-            pile = upload(size)
-            library.call("mcb_pile_wait_upload", pile)
+        pile = upload(size)
         graph = hot_path(pile, ks[size])
         nnz = library.lib.mcb_graph_nnz(graph)
         if nnz > capacity:
