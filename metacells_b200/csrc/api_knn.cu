@@ -22,8 +22,9 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
 int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint32_t* known_min);
 
 struct BalancedRanks {
-    Scratch data, indices, indptr, best_index, best_value;
+    Scratch data, indices, indptr, best_index, best_value, best_raw;  // best_raw: the preserved value before max(., 1)
     int64_t nnz = 0;
+    int64_t widest = 0;  // the longest row
 };
 struct PrunedRanks {
     Scratch data, indices, indptr;

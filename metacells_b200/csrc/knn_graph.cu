@@ -19,6 +19,7 @@
 
 #include "common.cuh"
 #include "select.cuh"
+#include "prune_mirror.cuh"
 
 namespace mcb {
 
@@ -197,7 +198,8 @@ __global__ void __launch_bounds__(256) balance_best_kernel(BalanceParams p) {
 // Pass 2: one warp per row.  Decodes the argmax, adds the preserved entry to its tile's count when the
 // threshold dropped it, turns the counts into exclusive offsets and writes the row's size.
 __global__ void __launch_bounds__(256) balance_rows_kernel(BalanceParams p, int32_t* __restrict__ row_sizes,
-                                                          int32_t* __restrict__ best_index, float* __restrict__ best_value) {
+                                                          int32_t* __restrict__ best_index, float* __restrict__ best_value,
+                                                          float* __restrict__ best_raw, int32_t* __restrict__ widest) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= p.n)
@@ -223,6 +225,8 @@ __global__ void __launch_bounds__(256) balance_rows_kernel(BalanceParams p, int3
         row_sizes[row] = running;
         best_index[row] = (int32_t)column;
         best_value[row] = fmaxf(value, 1.0f);
+        best_raw[row] = value;
+        atomicMax(widest, running);
     }
 }
 
@@ -402,8 +406,9 @@ int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint
 
 // The balanced-rank CSR of knn_graph.py:300-340 plus the preserved edge of every row.
 struct BalancedRanks {
-    Scratch data, indices, indptr, best_index, best_value;
+    Scratch data, indices, indptr, best_index, best_value, best_raw;  // best_raw: the preserved value before max(., 1)
     int64_t nnz = 0;
+    int64_t widest = 0;  // the longest row
 };
 
 // The largest float32 product whose balanced rank passes `2^21 - sqrt(product) + shift > 0`, through the same float32
@@ -446,6 +451,10 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     MCB_TRY(out->indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
     MCB_TRY(out->best_index.alloc((size_t)n * sizeof(int32_t), stream));
     MCB_TRY(out->best_value.alloc((size_t)n * sizeof(float), stream));
+    MCB_TRY(out->best_raw.alloc((size_t)n * sizeof(float), stream));
+    Scratch widest;
+    MCB_TRY(widest.alloc(sizeof(int32_t), stream));
+    MCB_CUDA(cudaMemsetAsync(widest.ptr, 0, sizeof(int32_t), stream));
     MCB_CUDA(cudaMemsetAsync(row_best.ptr, 0, (size_t)n * sizeof(unsigned long long), stream));
     BalanceParams p{};
     p.ranks = ranks;
@@ -461,12 +470,14 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     MCB_PROFILED("balance_best", stream, balance_best_kernel<<<(unsigned)n, 256, 0, stream>>>(p));
     MCB_LAUNCH_CHECK();
     MCB_PROFILED("balance_rows", stream, balance_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(p, row_sizes.as<int32_t>(), out->best_index.as<int32_t>(),
-                                                                     out->best_value.as<float>()));
+                                                                     out->best_value.as<float>(), out->best_raw.as<float>(), widest.as<int32_t>()));
     MCB_LAUNCH_CHECK();
     MCB_TRY(exclusive_scan_i32(row_sizes.as<int32_t>(), out->indptr.as<int32_t>(), n, nullptr, stream));
-    int32_t nnz = 0;
+    int32_t nnz = 0, widest_host = 0;
     MCB_TRY(read_i32(out->indptr.as<int32_t>() + n, &nnz, stream));
+    MCB_TRY(read_i32(widest.as<int32_t>(), &widest_host, stream));
     out->nnz = nnz;
+    out->widest = widest_host;
     MCB_TRY(out->data.alloc((size_t)nnz * sizeof(float), stream));
     MCB_TRY(out->indices.alloc((size_t)nnz * sizeof(int32_t), stream));
     p.indptr = out->indptr.as<int32_t>();
@@ -487,33 +498,6 @@ struct PrunedRanks {
 
 int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incoming_degree, int64_t outgoing_degree,
                        PrunedRanks* out, cudaStream_t stream) {
-    // (1) knn_graph.py:371-374: the CSR arrays reinterpreted as CSC; keep the best `incoming_degree` per column
-    Scratch in_data, in_indices, in_indptr;
-    MCB_TRY(in_data.alloc((size_t)balanced.nnz * sizeof(float), stream));
-    MCB_TRY(in_indices.alloc((size_t)balanced.nnz * sizeof(int32_t), stream));
-    MCB_TRY(in_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
-    MCB_TRY(collect_pruned_launch(incoming_degree, balanced.data.as<float>(), balanced.indices.as<int32_t>(),
-                                  balanced.indptr.as<int32_t>(), n, in_data.as<float>(), in_indices.as<int32_t>(),
-                                  in_indptr.as<int32_t>(), stream));
-    int32_t in_nnz = 0;
-    MCB_TRY(read_i32(in_indptr.as<int32_t>() + n, &in_nnz, stream));
-    // (2) knn_graph.py:377: CSC -> CSR
-    Scratch row_data, row_indices, row_indptr;
-    MCB_TRY(row_data.alloc((size_t)in_nnz * sizeof(float), stream));
-    MCB_TRY(row_indices.alloc((size_t)in_nnz * sizeof(int32_t), stream));
-    MCB_TRY(row_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
-    trace_lap("prune: incoming", stream);
-    MCB_TRY(relayout_launch(in_data.as<float>(), in_indices.as<int32_t>(), in_indptr.as<int32_t>(), n, n, in_nnz,
-                            row_data.as<float>(), row_indices.as<int32_t>(), row_indptr.as<int32_t>(), stream));
-    trace_lap("prune: relayout", stream);
-    // (3) knn_graph.py:380: keep the best `outgoing_degree` per row
-    Scratch out_data, out_indices, out_indptr;
-    MCB_TRY(out_data.alloc((size_t)in_nnz * sizeof(float), stream));
-    MCB_TRY(out_indices.alloc((size_t)in_nnz * sizeof(int32_t), stream));
-    MCB_TRY(out_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
-    MCB_TRY(collect_pruned_launch(outgoing_degree, row_data.as<float>(), row_indices.as<int32_t>(), row_indptr.as<int32_t>(), n,
-                                  out_data.as<float>(), out_indices.as<int32_t>(), out_indptr.as<int32_t>(), stream));
-    trace_lap("prune: outgoing", stream);
     // (4) knn_graph.py:383-388: maximum with the preserved edges and their transpose
     Scratch reverse_counts, reverse_ptr, reverse_cursor, reverse_list, sizes;
     MCB_TRY(reverse_counts.alloc((size_t)n * sizeof(int32_t), stream));
@@ -530,6 +514,98 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     reverse_scatter_kernel<<<row_blocks, 256, 0, stream>>>(balanced.best_index.as<int32_t>(), n, reverse_cursor.as<int32_t>(),
                                                           reverse_list.as<int32_t>());
     MCB_LAUNCH_CHECK();
+    Scratch out_data, out_indices, out_indptr;
+    // (1)-(3) without the transposition (prune_mirror.cuh) when every band fits a warp's registers
+    bool mirrored = outgoing_degree >= 1 && getenv("MCB_PRUNE_RELAYOUT") == nullptr;
+    if (mirrored) {
+        Scratch cuts, padded_data, padded_indices, kept_sizes, overflow;
+        MCB_TRY(cuts.alloc((size_t)n * sizeof(RowCut), stream));
+        MCB_TRY(padded_data.alloc((size_t)n * outgoing_degree * sizeof(float), stream));
+        MCB_TRY(padded_indices.alloc((size_t)n * outgoing_degree * sizeof(int32_t), stream));
+        MCB_TRY(kept_sizes.alloc((size_t)n * sizeof(int32_t), stream));
+        MCB_TRY(overflow.alloc(sizeof(int), stream));
+        MCB_CUDA(cudaMemsetAsync(overflow.ptr, 0, sizeof(int), stream));
+        MirrorParams mp{};
+        mp.data = balanced.data.as<float>();
+        mp.indices = balanced.indices.as<int32_t>();
+        mp.indptr = balanced.indptr.as<int32_t>();
+        mp.n = n;
+        mp.incoming_degree = (int)incoming_degree;
+        mp.outgoing_degree = (int)outgoing_degree;
+        mp.best_index = balanced.best_index.as<int32_t>();
+        mp.best_value = balanced.best_value.as<float>();
+        mp.best_raw = balanced.best_raw.as<float>();
+        mp.reverse_ptr = reverse_ptr.as<int32_t>();
+        mp.reverse_list = reverse_list.as<int32_t>();
+        mp.cuts = cuts.as<RowCut>();
+        mp.padded_data = padded_data.as<float>();
+        mp.padded_indices = padded_indices.as<int32_t>();
+        mp.sizes = kept_sizes.as<int32_t>();
+        mp.overflow = overflow.as<int>();
+        const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n * 32, 256), (int64_t)sm_count() * 8);
+        MCB_PROFILED("row_cuts", stream, row_cuts_kernel<<<grid, 256, 0, stream>>>(mp));
+        MCB_LAUNCH_CHECK();
+        const unsigned narrow_grid = (unsigned)std::min<int64_t>(ceil_div(n * 32, 128), (int64_t)sm_count() * 16);
+        MCB_PROFILED("mirror_prune", stream, mirror_prune_kernel<32><<<narrow_grid, 128, 0, stream>>>(mp));
+        MCB_LAUNCH_CHECK();
+        if (balanced.widest > 32 * 32) {
+            MCB_PROFILED("mirror_prune_wide", stream, mirror_prune_kernel<MP_MAX_ROUNDS><<<narrow_grid, 128, 0, stream>>>(mp));
+            MCB_LAUNCH_CHECK();
+        }
+        if (balanced.widest > 32 * MP_MAX_ROUNDS) {
+            const size_t cache_bytes = (size_t)4 * MP_CACHE * sizeof(uint32_t);
+            MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(mirror_prune_kernel<0>), cache_bytes));
+            MCB_PROFILED("mirror_prune_widest", stream, mirror_prune_kernel<0><<<narrow_grid, 128, cache_bytes, stream>>>(mp));
+            MCB_LAUNCH_CHECK();
+        }
+        MCB_TRY(out_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
+        MCB_TRY(exclusive_scan_i32(kept_sizes.as<int32_t>(), out_indptr.as<int32_t>(), n, nullptr, stream));
+        int32_t kept_nnz = 0, overflowed = 0;
+        MCB_TRY(read_i32(out_indptr.as<int32_t>() + n, &kept_nnz, stream));
+        MCB_TRY(read_i32(overflow.as<int32_t>(), &overflowed, stream));
+        if (overflowed) {
+            mirrored = false;  // a row with more than 32 foreign preserved entries: the general path
+        } else {
+            MCB_TRY(out_data.alloc((size_t)kept_nnz * sizeof(float), stream));
+            MCB_TRY(out_indices.alloc((size_t)kept_nnz * sizeof(int32_t), stream));
+            MCB_PROFILED("compact_rows", stream, compact_rows_kernel<<<warp_blocks, 256, 0, stream>>>(
+                             padded_data.as<float>(), padded_indices.as<int32_t>(), n, (int)outgoing_degree, out_indptr.as<int32_t>(),
+                             out_data.as<float>(), out_indices.as<int32_t>()));
+            MCB_LAUNCH_CHECK();
+        }
+    }
+    if (!mirrored) {
+        Scratch fresh_data, fresh_indices, fresh_indptr;
+        std::swap(out_data.ptr, fresh_data.ptr), std::swap(out_data.stream, fresh_data.stream);
+        std::swap(out_indices.ptr, fresh_indices.ptr), std::swap(out_indices.stream, fresh_indices.stream);
+        std::swap(out_indptr.ptr, fresh_indptr.ptr), std::swap(out_indptr.stream, fresh_indptr.stream);
+        // (1) knn_graph.py:371-374: the CSR arrays reinterpreted as CSC; keep the best `incoming_degree` per column
+        Scratch in_data, in_indices, in_indptr;
+        MCB_TRY(in_data.alloc((size_t)balanced.nnz * sizeof(float), stream));
+        MCB_TRY(in_indices.alloc((size_t)balanced.nnz * sizeof(int32_t), stream));
+        MCB_TRY(in_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
+        MCB_TRY(collect_pruned_launch(incoming_degree, balanced.data.as<float>(), balanced.indices.as<int32_t>(),
+                                      balanced.indptr.as<int32_t>(), n, in_data.as<float>(), in_indices.as<int32_t>(),
+                                      in_indptr.as<int32_t>(), stream));
+        int32_t in_nnz = 0;
+        MCB_TRY(read_i32(in_indptr.as<int32_t>() + n, &in_nnz, stream));
+        // (2) knn_graph.py:377: CSC -> CSR
+        Scratch row_data, row_indices, row_indptr;
+        MCB_TRY(row_data.alloc((size_t)in_nnz * sizeof(float), stream));
+        MCB_TRY(row_indices.alloc((size_t)in_nnz * sizeof(int32_t), stream));
+        MCB_TRY(row_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
+        trace_lap("prune: incoming", stream);
+        MCB_TRY(relayout_launch(in_data.as<float>(), in_indices.as<int32_t>(), in_indptr.as<int32_t>(), n, n, in_nnz,
+                                row_data.as<float>(), row_indices.as<int32_t>(), row_indptr.as<int32_t>(), stream));
+        trace_lap("prune: relayout", stream);
+        // (3) knn_graph.py:380: keep the best `outgoing_degree` per row
+        MCB_TRY(out_data.alloc((size_t)in_nnz * sizeof(float), stream));
+        MCB_TRY(out_indices.alloc((size_t)in_nnz * sizeof(int32_t), stream));
+        MCB_TRY(out_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
+        MCB_TRY(collect_pruned_launch(outgoing_degree, row_data.as<float>(), row_indices.as<int32_t>(), row_indptr.as<int32_t>(), n,
+                                      out_data.as<float>(), out_indices.as<int32_t>(), out_indptr.as<int32_t>(), stream));
+        trace_lap("prune: outgoing", stream);
+    }
     MergeParams m{};
     m.data = out_data.as<float>();
     m.indices = out_indices.as<int32_t>();

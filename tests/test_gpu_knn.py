@@ -311,3 +311,29 @@ def test_piles_walked_by_several_threads_match_the_single_pile_path():
         assert np.array_equal(details["feature_genes"], alone_details["feature_genes"])
         assert np.array_equal(weights.indptr, alone.indptr) and np.array_equal(weights.indices, alone.indices)
         assert np.array_equal(weights.data, alone.data)
+
+
+@pytest.mark.parametrize("cells,k,factors,kind", [
+    (300, 2, (3.0, 1.0), "ties"), (300, 1, (1.0, 1.0), "ties"), (257, 3, (1.5, 0.5), "ties"), (700, 9, (1.0, 0.34), "smooth"),
+    (400, 6, (2.0, 1.0), "hub"), (400, 2, (1.0, 1.0), "hub"), (1200, 40, (1.0, 0.25), "ties"), (2100, 90, (3.0, 1.0), "smooth"),
+    (5000, 400, (3.0, 1.0), "smooth"), (5000, 450, (2.0, 0.5), "ties"), (6000, 700, (2.0, 0.5), "ties"),
+])
+def test_knn_graph_prune_corner_cases(cells, k, factors, kind):
+    """The pruning without the transposition (prune_mirror.cuh) against the oracle where its cases differ from the plain
+    one: cuts inside groups of equal values, preserved edges that fail the threshold (tiny k), rows that are the preserved
+    column of more rows than a warp holds (a hub: the general path takes over), bands wider than 1024 and than 2048
+    entries."""
+    from metacells_b200 import tools as tl
+
+    sim = _similarity(cells, 1000 + cells + k, ties=kind != "smooth")
+    if kind == "hub":  # every cell's most similar cell is cell 0
+        sim[0, 1:] = sim[1:, 0] = np.float32(0.999)
+    incoming, outgoing = factors
+    expected_weights, expected_pruned, _, expected_k = oracle.knn_graph(sim, k, incoming_degree_factor=incoming,
+                                                                        outgoing_degree_factor=outgoing, min_outgoing_degree=1)
+    weights, pruned, used_k = tl.compute_obs_obs_knn_graph(sim, k=k, incoming_degree_factor=incoming,
+                                                           outgoing_degree_factor=outgoing, min_outgoing_degree=1,
+                                                           return_details=True)
+    assert used_k == expected_k
+    _assert_same_csr(pruned, expected_pruned)
+    _assert_same_csr(weights, expected_weights)
