@@ -644,29 +644,38 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
 
 def time_candidates(args, umis):
     """What follows the k-NN graph in a pile (tools/candidates.py:128-196, 351-368): choose_seeds and the first
-    optimize_partitions, through the reference's own entry points with host arrays.  Both are one persistent CTA, so the
-    piles of a worker run side by side, one SM and one host thread each; every pile here is the bench pile's graph."""
-    from metacells_b200 import extensions as xt, pipeline
+    optimize_partitions, on the pile's graph as it lies on the device.  Both are one persistent CTA, so the piles of a
+    worker run side by side, one SM and one host thread each; every pile here is the bench pile's graph."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from metacells_b200 import pipeline
 
     cells = umis.shape[0]
-    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
-    weights, _ = pipeline.compute_pile_knn_graph(umis, features=args.features, random_seed=SEED)
-    pipeline.compute_pile_seed_partition(weights, cell_umis, random_seed=SEED)  # warm-up: pools, attributes
-    start = time.perf_counter()
-    communities, score, seeds = pipeline.compute_pile_seed_partition(weights, cell_umis, random_seed=SEED)
-    alone_s = time.perf_counter() - start
-    piles = [(weights, cell_umis)] * args.candidate_piles
-    start = time.perf_counter()
-    results = pipeline.compute_piles_seed_partitions(piles, random_seed=SEED)
-    together_s = time.perf_counter() - start
+    graph, cell_umis = pipeline.pile_knn_graph_on_device(umis, features=args.features, random_seed=SEED)
+    bounds = pipeline.metacell_bounds()
+    wanted = pipeline.seeds_count_for(float(sum(cell_umis)), cells, bounds)
+
+    def candidates(_=None):
+        return graph.seed_partition(cell_umis, bounds, wanted, random_seed=SEED)
+
+    try:
+        candidates()  # warm-up: pools, attributes
+        start = time.perf_counter()
+        communities, score, seeds = candidates()
+        alone_s = time.perf_counter() - start
+        with ThreadPoolExecutor(max_workers=args.candidate_piles) as pool:
+            start = time.perf_counter()
+            results = list(pool.map(candidates, range(args.candidate_piles)))
+            together_s = time.perf_counter() - start
+    finally:
+        graph.close()
     identical = all(np.array_equal(communities, other[0]) and score == other[1] for other in results)
     return {"metric": "seeds_and_first_partition_optimisation_wall_time", "cells_per_pile": int(cells), "seeds": int(seeds),
             "one_pile_s": alone_s, "piles_side_by_side": int(args.candidate_piles), "side_by_side_s": together_s,
             "s_per_pile_side_by_side": together_s / args.candidate_piles, "identical_results": bool(identical),
-            "optimize_partitions_stats": {name: int(value) for name, value in
-                                          zip(("passes", "visits", "moves", "skipped", "batches"), xt.last_optimize_stats[:5])},
-            "note": "host arrays in, partition out (uploads and the relayout to the incoming layout included); one CTA = one "
-                    "SM per pile, one host thread and stream per pile"}
+            "note": "mcb_graph_seed_partition on the pile's k-NN graph as it lies on the device (incoming layout, choose_seeds, "
+                    "optimize_partitions; cell UMIs up, partition down); one CTA = one SM per pile, one host thread and stream "
+                    "per pile"}
 
 
 def ncu_traffic(kernel, cells, features):

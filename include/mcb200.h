@@ -257,6 +257,18 @@ int mcb_dev_choose_seeds(const float* outgoing_weights, const int32_t* outgoing_
                          int64_t nodes, uint64_t random_seed, int64_t max_seeds_count, float min_seed_size_quantile,
                          float max_seed_size_quantile, int32_t* seed_of_nodes, int64_t* seeds_count, void* stream);
 
+/* The opening of compute_candidate_metacells on a device-resident k-NN graph (tools/candidates.py:128-196 and the
+ * first _optimize_partitions of _reduce_communities, :351-368): the incoming layout is built on the device, choose_seeds
+ * fills the partition, optimize_partitions (every community hot) improves it; only mass_of_nodes goes up and the
+ * partition comes back.  Runs on the calling thread's own stream: graphs of different piles are handled side by side by
+ * as many host threads, one SM each.  partition_of_nodes int32[nodes] (host, output); *seeds_count and *score as
+ * mcb_host_choose_seeds / mcb_host_optimize_partitions return them.  Bit-identical to the reference's two calls. */
+int mcb_graph_seed_partition(const mcb_graph* graph, const float* mass_of_nodes, uint64_t random_seed, int64_t max_seeds_count,
+                             float min_seed_size_quantile, float max_seed_size_quantile, double low_mass, double target_mass,
+                             double high_mass, double low_size, double target_size, double high_size, double cooldown_pass,
+                             double cooldown_node, double cold_temperature, int32_t* partition_of_nodes, int64_t* seeds_count,
+                             double* score);
+
 /* ---- partitions.cpp ----------------------------------------------------------------------------- */
 
 /* optimize_partitions (partitions.cpp:1234-1302; bound as xt.optimize_partitions, tools/candidates.py:853-873).

@@ -18,7 +18,7 @@ from . import tools as tl
 from ._lib import check, lib
 
 __all__ = ["Pile", "compute_pile_knn_graph", "knn_k_of_pile", "log_fraction_table", "compute_pile_seed_partition",
-           "compute_piles_seed_partitions", "metacell_bounds", "seeds_count_for"]
+           "compute_piles_seed_partitions", "compute_piles_candidates", "metacell_bounds", "seeds_count_for"]
 
 # metacells/parameters.py
 CELLS_SIMILARITY_VALUE_REGULARIZATION = 1 / 7
@@ -345,3 +345,55 @@ def compute_piles_seed_partitions(piles, *, workers: Optional[int] = None, **arg
 
     with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(piles))), initializer=on_device) as pool:
         return list(pool.map(lambda pile: compute_pile_seed_partition(pile[0], pile[1], **arguments), piles))
+
+
+def pile_knn_graph_on_device(umis: sp.csr_matrix, *, features: int = 2000, random_seed: int = 123456):
+    """``compute_pile_knn_graph`` that leaves the graph on the device: ``(KnnGraph, cell_umis)``; the caller closes the
+    graph."""
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    samples = int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(cell_umis, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
+                            np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
+    k = knn_k_of_pile(umis.shape[0], cell_umis)
+    with Pile(umis, max_cell_total=float(cell_umis.max(initial=0))) as pile:
+        pile.downsample(samples, random_seed)
+        pile.select_top_genes(features)
+        return pile.knn_graph(None, k=k), cell_umis
+
+
+def compute_piles_candidates(piles: Iterable[sp.csr_matrix], *, features: int = 2000, random_seed: int = 123456,
+                             workers: Optional[int] = None, **bounds_arguments):
+    """One phase of the divide-and-conquer loop on one GPU, as far as this package goes: for every pile (a cells x genes
+    UMI matrix) the k-NN graph (``compute_pile_knn_graph``'s steps, one pile after the other: each uses the whole GPU
+    for ~10 ms) and then, for all piles side by side, the seeds and the first partition optimisation on the graphs as
+    they lie on the device (``KnnGraph.seed_partition``: one SM, one host thread and stream per pile).  Returns a list of
+    ``(community_of_nodes, score, seeds_count, k)``.  The graphs stay on the device in between (12 bytes per edge)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    bounds = metacell_bounds(**bounds_arguments)
+    graphs = []
+    try:
+        for umis in piles:
+            graphs.append(pile_knn_graph_on_device(umis, features=features, random_seed=random_seed))
+        if not graphs:
+            return []
+        if workers is None:
+            count = ctypes.c_int(0)
+            check(lib().mcb_device_sm_count(ctypes.byref(count)))
+            workers = count.value
+        device = ctypes.c_int(0)
+        check(lib().mcb_current_device(ctypes.byref(device)))
+
+        def on_device() -> None:  # the current device is per thread
+            check(lib().mcb_set_device(device))
+
+        def candidates(entry):
+            graph, cell_umis = entry
+            wanted = seeds_count_for(float(sum(cell_umis)), graph.shape[0], bounds)
+            communities, score, seeds = graph.seed_partition(cell_umis, bounds, wanted, random_seed=random_seed)
+            return communities, score, seeds, graph.k
+
+        with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(graphs))), initializer=on_device) as pool:
+            return list(pool.map(candidates, graphs))
+    finally:
+        for graph, _ in graphs:
+            graph.close()

@@ -194,6 +194,27 @@ class KnnGraph:
         function.restype = ctypes.c_int
         check(function(self._handle))
 
+    def seed_partition(self, cell_umis: np.ndarray, bounds, max_seeds_count: int, *, random_seed: int,
+                       min_seed_size_quantile: float = 0.85, max_seed_size_quantile: float = 0.95,
+                       cooldown_pass: float = 0.02, cooldown_node: float = 0.25) -> Tuple[np.ndarray, float, int]:
+        """``choose_seeds`` + the first ``optimize_partitions`` of ``compute_candidate_metacells`` on this graph without
+        taking it off the device (``mcb_graph_seed_partition``).  ``bounds``: ``(low, target, high)`` UMIs then
+        ``(low, target, high)`` sizes.  Returns ``(community_of_nodes, score, seeds_count)``."""
+        cell_umis = np.ascontiguousarray(cell_umis, dtype="float32")
+        size = self.shape[0]
+        if len(cell_umis) != size:
+            raise ValueError("cell_umis must have one entry per node")
+        communities = np.empty(size, dtype="int32")
+        seeds, score = ctypes.c_int64(0), ctypes.c_double(0.0)
+        function = lib().mcb_graph_seed_partition
+        function.restype = ctypes.c_int
+        check(function(self._handle, ctypes.c_void_p(cell_umis.ctypes.data), ctypes.c_uint64(int(random_seed)),
+                       ctypes.c_int64(int(max_seeds_count)), ctypes.c_float(min_seed_size_quantile),
+                       ctypes.c_float(max_seed_size_quantile), *(ctypes.c_double(float(bound)) for bound in bounds),
+                       ctypes.c_double(cooldown_pass), ctypes.c_double(cooldown_node), ctypes.c_double(1 - cooldown_pass),
+                       ctypes.c_void_p(communities.ctypes.data), ctypes.byref(seeds), ctypes.byref(score)))
+        return communities, score.value, seeds.value
+
     def to_scipy(self, arrays=None) -> Tuple[sp.csr_matrix, sp.csr_matrix]:
         """``(outgoing_weights, pruned_ranks)`` as CSR float32 / int32 / int32; ``arrays``: what ``read_start`` returned."""
         size = self.shape[0]

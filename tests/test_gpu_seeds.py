@@ -154,3 +154,22 @@ def test_piles_side_by_side(xt):
         expected_score = oracle.optimize_partitions(outgoing, incoming, SEED, masses, *bounds, 0.02, 0.25, expected,
                                                     np.ones(max(seeds_count, 2), dtype="int8"), 0.98)
         assert np.array_equal(communities, expected) and score == expected_score
+
+
+def test_pile_candidates_without_leaving_the_device(xt):
+    # k-NN graph -> seeds -> first optimisation with the graph staying on the device (mcb_graph_seed_partition), several
+    # piles side by side: the same partitions as the host-array entry points give on the graph read back
+    from metacells_b200 import pipeline
+
+    piles = [synth_umis(cells, 3000, seed=70 + cells) for cells in (500, 640, 420)]
+    arguments = dict(target_metacell_size=40, target_metacell_umis=60000)
+    together = pipeline.compute_piles_candidates(piles, features=300, random_seed=SEED, workers=3, **arguments)
+    assert len(together) == len(piles)
+    for umis, (communities, score, seeds_count, k) in zip(piles, together):
+        outgoing, details = pipeline.compute_pile_knn_graph(umis, features=300, random_seed=SEED)
+        assert details["k"] == k
+        cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+        expected, expected_score, expected_count = pipeline.compute_pile_seed_partition(outgoing, cell_umis, random_seed=SEED,
+                                                                                       **arguments)
+        assert seeds_count == expected_count and score == expected_score
+        assert np.array_equal(communities, expected)
