@@ -221,6 +221,26 @@ def p(pointer):
     return ctypes.c_void_p(pointer)
 
 
+def near_gpu_cpus(local_rank):
+    """The host cores next to the rank's GPU (NVML's CPU affinity of the device), or None.  The rank's threads and the
+    page-locked buffers they touch first then sit on the GPU's NUMA node: a pile's 0.47 GB upload runs at the link's
+    speed instead of crossing the socket interconnect (what `numactl` does for a worker process)."""
+    try:
+        import pynvml
+        import torch
+
+        pynvml.nvmlInit()
+        properties = torch.cuda.get_device_properties(local_rank)
+        bus = "%08x:%02x:%02x.0" % (properties.pci_domain_id, properties.pci_bus_id, properties.pci_device_id)
+        handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = {64 * index + bit for index, word in enumerate(words) for bit in range(64) if word >> bit & 1}
+        cpus &= os.sched_getaffinity(0)
+        return cpus or None
+    except Exception:  # noqa: BLE001 (NVML missing or the attribute absent: stay where the launcher put us)
+        return None
+
+
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -233,6 +253,10 @@ def run_gpu_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: there is no CPU fallback for the metacells_b200 hot path")
     torch.cuda.set_device(local_rank)
+    launcher_cpus = os.sched_getaffinity(0)
+    gpu_cpus = None if os.environ.get("MCB_BENCH_NO_AFFINITY") else near_gpu_cpus(local_rank)
+    if gpu_cpus:
+        os.sched_setaffinity(0, gpu_cpus)  # before the page-locked buffers are allocated and touched
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     library = Library()
@@ -514,6 +538,7 @@ def run_gpu_arm(args):
                    "downsample_samples": samples, "umis_nnz": int(umis.nnz), "graph_nnz": int(nnz), "piles_per_step": world,
                    "l2": "inputs larger than L2 (CSR pile 0.45 GB, similarity and rank matrices 1 GB each per step)"},
         "clocks": clocks,
+        "host": {"cpus_near_gpu": len(gpu_cpus) if gpu_cpus else None, "cpus": len(launcher_cpus)},
         "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                 "unpipelined_ms_per_step": e2e_sequential_ms / args.steps,
                 "mode": e2e_mode, "one_thread_prefetch_ms_per_step": e2e_prefetch_ms / args.steps,
@@ -535,6 +560,7 @@ def run_gpu_arm(args):
         line["atlas"] = atlas
     if world == 1 and args.candidate_piles > 0:
         line["candidates"] = time_candidates(args, umis)
+    os.sched_setaffinity(0, launcher_cpus)  # the CPU baseline uses every core the launcher gave us
     if world == 1 and not args.no_cpu_baseline:
         step, info, _ = cpu_step_factory(args)
         start = time.perf_counter()
