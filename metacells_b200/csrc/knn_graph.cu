@@ -101,12 +101,23 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t n = p.n;
     const int64_t i0 = (int64_t)tile_i * BT, j0 = (int64_t)tile_j * BT;
-    for (int r = warp; r < BT; r += BAL_THREADS / 32) {
+    if ((n & 3) == 0 && i0 + BT <= n && j0 + BT <= n) {
+        // whole tiles of a matrix whose rows start on 16-byte boundaries: 128-bit loads, 16 lanes per tile row
+        const int quad = (threadIdx.x & 15) * 4;
+        for (int r = threadIdx.x >> 4; r < BT; r += BAL_THREADS / 16) {
+            const float4 a = *reinterpret_cast<const float4*>(p.ranks + (i0 + r) * n + j0 + quad);
+            const float4 b = *reinterpret_cast<const float4*>(p.ranks + (j0 + r) * n + i0 + quad);
+            tile_a[r][quad] = a.x, tile_a[r][quad + 1] = a.y, tile_a[r][quad + 2] = a.z, tile_a[r][quad + 3] = a.w;
+            tile_b[r][quad] = b.x, tile_b[r][quad + 1] = b.y, tile_b[r][quad + 2] = b.z, tile_b[r][quad + 3] = b.w;
+        }
+    } else {
+        for (int r = warp; r < BT; r += BAL_THREADS / 32) {
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int c = lane + 32 * half;
-            tile_a[r][c] = (i0 + r < n && j0 + c < n) ? p.ranks[(i0 + r) * n + j0 + c] : 0.0f;
-            tile_b[r][c] = (j0 + r < n && i0 + c < n) ? p.ranks[(j0 + r) * n + i0 + c] : 0.0f;
+            for (int half = 0; half < 2; ++half) {
+                const int c = lane + 32 * half;
+                tile_a[r][c] = (i0 + r < n && j0 + c < n) ? p.ranks[(i0 + r) * n + j0 + c] : 0.0f;
+                tile_b[r][c] = (j0 + r < n && i0 + c < n) ? p.ranks[(j0 + r) * n + i0 + c] : 0.0f;
+            }
         }
     }
     __syncthreads();

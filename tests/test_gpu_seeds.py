@@ -173,3 +173,18 @@ def test_pile_candidates_without_leaving_the_device(xt):
                                                                                        **arguments)
         assert seeds_count == expected_count and score == expected_score
         assert np.array_equal(communities, expected)
+
+
+def test_runtime_helpers_for_side_by_side_calls():
+    import ctypes
+
+    from metacells_b200 import _lib
+
+    library = _lib.lib()
+    device, count = ctypes.c_int(-1), ctypes.c_int(0)
+    _lib.check(library.mcb_current_device(ctypes.byref(device)))
+    _lib.check(library.mcb_device_sm_count(ctypes.byref(count)))
+    assert device.value >= 0 and count.value >= 100  # a B200 has 148 SMs
+    _lib.call("mcb_reserve_scratch", ("i64", 64 << 20))
+    with pytest.raises(_lib.McbError):
+        _lib.call("mcb_reserve_scratch", ("i64", -1))
