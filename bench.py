@@ -46,6 +46,9 @@ def parse_args():
                         help="cells of the divide-and-conquer atlas whose piles are timed after the per-pile steps (0: skip)")
     parser.add_argument("--e2e-workers", type=int, default=2,
                         help="host threads of a rank that walk its piles end to end, each on a stream of its own")
+    parser.add_argument("--atlas-candidates", type=int, default=1,
+                        help="1: after the atlas' k-NN graphs, time graphs + seeds + first partition optimisation of all its "
+                             "piles (graphs stay on the device, the optimisations run side by side); 0: skip")
     parser.add_argument("--candidate-piles", type=int, default=16,
                         help="piles whose seeds and first partition optimisation run side by side after the k-NN steps "
                              "(N = 1 only; 0: skip)")
@@ -660,12 +663,66 @@ def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, strea
         dist.all_reduce(both, op=dist.ReduceOp.SUM)
         edges = int(both[2].item())
     device_s, wall_s = float(numbers[0].item()), float(numbers[1].item())
-    return {"metric": "divide_and_conquer_knn_graphs_wall_time", "cells": int(args.atlas_cells), "piles": int(len(sizes)),
+    line = {"metric": "divide_and_conquer_knn_graphs_wall_time", "cells": int(args.atlas_cells), "piles": int(len(sizes)),
             "pile_cells": [int(sizes.min()), int(sizes.max())], "phases": 1, "n_gpus": world, "scaling": "strong",
             "wall_s": wall_s, "device_s": device_s, "cells_per_s": args.atlas_cells / wall_s, "graph_nnz": int(edges),
             "data": "synthetic; every pile is a row prefix of the rank's synthetic pile, uploaded from pinned host memory and its "
                     "graph read back; the rank's worker threads (e2e_workers) take piles off one list, each on its own stream "
                     "(max over ranks, barrier on both sides)", "workers": workers}
+    if args.atlas_candidates:
+        line["with_candidates"] = time_atlas_candidates(args, library, upload, hot_path, barrier, device, world, sizes, mine, ks,
+                                                        cell_umis)
+    return line
+
+
+def time_atlas_candidates(args, library, upload, hot_path, barrier, device, world, sizes, mine, ks, cell_umis):
+    """The same phase carried on to the opening of compute_candidate_metacells: the k-NN graph of every pile of the rank
+    (uploaded from pinned memory, left on the device), then choose_seeds and the first optimize_partitions of all of them
+    side by side (mcb_graph_seed_partition: one SM, one host thread and stream per pile), partitions read back."""
+    import torch
+    import torch.distributed as dist
+    from concurrent.futures import ThreadPoolExecutor
+
+    from metacells_b200 import pipeline, tools as tl
+
+    bounds = pipeline.metacell_bounds()
+    barrier()
+    start = time.perf_counter()
+    graphs = []
+    try:
+        for pile in mine:
+            size = int(sizes[pile])
+            handle = upload(size)
+            graphs.append((tl.KnnGraph(hot_path(handle, ks[size])), size))
+            library.lib.mcb_pile_free(handle)
+        graphs_s = time.perf_counter() - start
+
+        def on_device():
+            library.call("mcb_set_device", ctypes.c_int(device.index))  # the current device is per thread
+
+        def candidates(entry):
+            graph, size = entry
+            umis_of_cells = cell_umis[:size]
+            wanted = pipeline.seeds_count_for(float(sum(umis_of_cells)), size, bounds)
+            return graph.seed_partition(umis_of_cells, bounds, wanted, random_seed=SEED)
+
+        seeds = 0
+        if graphs:
+            with ThreadPoolExecutor(max_workers=len(graphs), initializer=on_device) as pool:
+                seeds = sum(result[2] for result in pool.map(candidates, graphs))
+    finally:
+        for graph, _ in graphs:
+            graph.close()
+    barrier()
+    numbers = torch.tensor([time.perf_counter() - start, graphs_s, float(seeds)], dtype=torch.float64, device=device)
+    if world > 1:
+        total = numbers.clone()
+        dist.all_reduce(numbers, op=dist.ReduceOp.MAX)
+        dist.all_reduce(total, op=dist.ReduceOp.SUM)
+        seeds = int(total[2].item())
+    return {"metric": "divide_and_conquer_graphs_seeds_first_optimisation_wall_time", "wall_s": float(numbers[0].item()),
+            "graphs_s": float(numbers[1].item()), "seeds": int(seeds), "scaling": "strong",
+            "note": "max over ranks; every rank's piles optimised side by side, one SM each"}
 
 
 def time_candidates(args, umis):
