@@ -90,7 +90,9 @@ int allow_dynamic_shared(const void* kernel, size_t bytes) {
 }
 
 // A stream of the calling host thread's own (per device): host entry points that may be called from several
-// threads at once (one pile each) run side by side instead of queueing on the legacy default stream.
+// threads at once (one pile each) run side by side instead of queueing on the legacy default stream.  The stream
+// outlives its thread on purpose: piles and graphs created by a worker thread keep using it (their scratch is freed on
+// it) after the thread has gone; keep worker threads in a pool rather than spawning one per call.
 int thread_stream(cudaStream_t* stream) {
     static thread_local cudaStream_t streams[64] = {};
     int device = 0;
