@@ -7,6 +7,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstring>
 
 #define MCB_OK 0
 #define MCB_ERR_CUDA 1
@@ -83,7 +84,16 @@ struct Scratch {
 
 // Device -> host copy of a result the caller waits for.  Waits for the stream FIRST: a copy into pageable memory waits
 // for the stream's earlier work inside the driver call, and host threads driving other streams cannot launch meanwhile.
+int pinned_staging(void** buffer);  // 256 page-locked bytes of the calling host thread
 static inline int copy_to_host(void* host, const void* device, size_t bytes, cudaStream_t stream) {
+    if (bytes > 0 && bytes <= 256) {  // a count or a flag: through page-locked memory, no staging inside the driver
+        void* staging = nullptr;
+        MCB_TRY(pinned_staging(&staging));
+        MCB_CUDA(cudaMemcpyAsync(staging, device, bytes, cudaMemcpyDeviceToHost, stream));
+        MCB_CUDA(cudaStreamSynchronize(stream));
+        memcpy(host, staging, bytes);
+        return MCB_OK;
+    }
     MCB_CUDA(cudaStreamSynchronize(stream));
     if (bytes)
         MCB_CUDA(cudaMemcpyAsync(host, device, bytes, cudaMemcpyDeviceToHost, stream));

@@ -390,9 +390,7 @@ int relayout_launch(const float* data, const int32_t* indices, const int32_t* in
                     int64_t nnz, float* out_data, int32_t* out_indices, int32_t* out_indptr, cudaStream_t stream);
 
 static int read_i32(const int32_t* device, int32_t* host, cudaStream_t stream) {
-    MCB_TRY(copy_to_host(host, device, sizeof(int32_t), stream));
-    MCB_CUDA(cudaStreamSynchronize(stream));
-    return MCB_OK;
+    return copy_to_host(host, device, sizeof(int32_t), stream);  // waits for the stream
 }
 
 // knn_graph.py:285-297 (_rank_outgoing) on a private copy: diagonal below the minimum, descending ranks.

@@ -89,6 +89,15 @@ int allow_dynamic_shared(const void* kernel, size_t bytes) {
     return MCB_OK;
 }
 
+// 256 page-locked bytes per host thread for the small read-backs (counts, flags) every stage ends with.
+int pinned_staging(void** buffer) {
+    static thread_local void* mine = nullptr;
+    if (mine == nullptr)
+        MCB_CUDA(cudaHostAlloc(&mine, 256, cudaHostAllocPortable));
+    *buffer = mine;
+    return MCB_OK;
+}
+
 // A stream of the calling host thread's own (per device): host entry points that may be called from several
 // threads at once (one pile each) run side by side instead of queueing on the legacy default stream.  The stream
 // outlives its thread on purpose: piles and graphs created by a worker thread keep using it (their scratch is freed on
