@@ -82,19 +82,23 @@ struct Scratch {
     }
 };
 
-// Device -> host copy of a result the caller waits for.  Waits for the stream FIRST: a copy into pageable memory waits
-// for the stream's earlier work inside the driver call, and host threads driving other streams cannot launch meanwhile.
-int pinned_staging(void** buffer);  // 256 page-locked bytes of the calling host thread
+// Device -> host copy of a result the caller waits for.  Waits for the stream FIRST, whatever the host memory is: a copy
+// into pageable memory waits for the stream's earlier work inside the driver call, and a copy into page-locked memory
+// that is queued behind a long kernel sits at the head of a copy-engine queue the uploads of other host threads' streams
+// line up in; either way calls that should run side by side end up one after the other (measured: 16 optimisations in
+// 11 s instead of 3.8 s).  Small results then go through page-locked staging (no second staging inside the driver).
+int pinned_staging(void** buffer);  // 256 page-locked bytes of the calling host thread, or nullptr
 static inline int copy_to_host(void* host, const void* device, size_t bytes, cudaStream_t stream) {
-    if (bytes > 0 && bytes <= 256) {  // a count or a flag: through page-locked memory, no staging inside the driver
-        void* staging = nullptr;
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    void* staging = nullptr;
+    if (bytes > 0 && bytes <= 256)
         MCB_TRY(pinned_staging(&staging));
+    if (staging != nullptr) {
         MCB_CUDA(cudaMemcpyAsync(staging, device, bytes, cudaMemcpyDeviceToHost, stream));
         MCB_CUDA(cudaStreamSynchronize(stream));
         memcpy(host, staging, bytes);
         return MCB_OK;
     }
-    MCB_CUDA(cudaStreamSynchronize(stream));
     if (bytes)
         MCB_CUDA(cudaMemcpyAsync(host, device, bytes, cudaMemcpyDeviceToHost, stream));
     return MCB_OK;

@@ -89,11 +89,35 @@ int allow_dynamic_shared(const void* kernel, size_t bytes) {
     return MCB_OK;
 }
 
-// 256 page-locked bytes per host thread for the small read-backs (counts, flags) every stage ends with.
+// 256 page-locked bytes per host thread for the small read-backs (counts, flags) every stage ends with.  One block for
+// the whole process, allocated at the first call (page-locking memory waits for running kernels, so worker threads must
+// not each do it while other threads' optimisations run); a thread takes the next slot, and a process that has used all
+// of them gets nullptr: its read-backs go through pageable memory.
 int pinned_staging(void** buffer) {
+    constexpr size_t SLOT = 256, SLOTS = 16384;
+    static std::mutex mutex;
+    static unsigned char* block = nullptr;
+    static bool tried = false;
+    static std::atomic<size_t> next{0};
     static thread_local void* mine = nullptr;
-    if (mine == nullptr)
-        MCB_CUDA(cudaHostAlloc(&mine, 256, cudaHostAllocPortable));
+    static thread_local bool asked = false;
+    if (!asked) {
+        asked = true;
+        {
+            std::lock_guard<std::mutex> lock(mutex);
+            if (!tried) {
+                tried = true;
+                void* allocated = nullptr;
+                if (cudaHostAlloc(&allocated, SLOT * SLOTS, cudaHostAllocPortable) == cudaSuccess)
+                    block = static_cast<unsigned char*>(allocated);
+                else
+                    cudaGetLastError();  // not fatal: the pageable path remains
+            }
+        }
+        const size_t slot = next.fetch_add(1);
+        if (block != nullptr && slot < SLOTS)
+            mine = block + slot * SLOT;
+    }
     *buffer = mine;
     return MCB_OK;
 }
