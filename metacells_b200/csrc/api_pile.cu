@@ -4,6 +4,9 @@
 #include <memory>
 #include <vector>
 
+#include <cstring>
+#include <vector>
+
 #include "common.cuh"
 #include "../../include/mcb200.h"
 
@@ -281,18 +284,43 @@ int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t featur
         genes_device = d_genes.as<int32_t>();
     }
     MCB_TRY(d_slot.alloc((size_t)pile->genes * sizeof(int32_t), stream));
-    MCB_TRY(d_table.alloc((size_t)table_size * sizeof(float), stream));
     MCB_TRY(d_dense.alloc((size_t)pile->cells * features * sizeof(float), stream));
     MCB_TRY(d_flag.alloc(2 * sizeof(int), stream));
     MCB_CUDA(cudaMemsetAsync(d_slot.ptr, 0xff, (size_t)pile->genes * sizeof(int32_t), stream));
-    MCB_CUDA(cudaMemcpyAsync(d_table.ptr, log_table, (size_t)table_size * sizeof(float), cudaMemcpyHostToDevice, stream));
+    // The log table of the calling thread's previous pile is still on the device when it is the same table (a worker
+    // walks piles with one table): no host-to-device copy here, where it would queue behind the next pile's upload.
+    const float* table_device = nullptr;
+    {
+        struct TableCache {
+            std::vector<float> host;
+            float* device = nullptr;
+            int device_index = -1;
+        };
+        static thread_local TableCache cache;
+        int device_index = 0;
+        MCB_CUDA(cudaGetDevice(&device_index));
+        const bool same = getenv("MCB_NO_TABLE_CACHE") == nullptr && cache.device != nullptr && cache.device_index == device_index &&
+                          (int64_t)cache.host.size() == table_size &&
+                          memcmp(cache.host.data(), log_table, (size_t)table_size * sizeof(float)) == 0;
+        if (!same) {
+            MCB_CUDA(cudaStreamSynchronize(stream));  // nothing of this thread still reads the old table
+            if (cache.device != nullptr)
+                cudaFree(cache.device);
+            cache.device = nullptr;
+            MCB_CUDA(cudaMalloc(&cache.device, (size_t)table_size * sizeof(float)));
+            cache.host.assign(log_table, log_table + table_size);
+            cache.device_index = device_index;
+            MCB_CUDA(cudaMemcpyAsync(cache.device, cache.host.data(), (size_t)table_size * sizeof(float), cudaMemcpyHostToDevice, stream));
+        }
+        table_device = cache.device;
+    }
     MCB_CUDA(cudaMemsetAsync(d_flag.ptr, 0, 2 * sizeof(int), stream));
     gene_slots_kernel<<<(unsigned)ceil_div(features, 256), 256, 0, stream>>>(genes_device, features, pile->genes,
                                                                              d_slot.as<int32_t>(), d_flag.as<int>() + 1);
     MCB_LAUNCH_CHECK();
     const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     MCB_TRY(log_fraction_dense_launch(values, pile->indices, pile->indptr, pile->cells, d_slot.as<int32_t>(), features,
-                                      d_table.as<float>(), table_size, regularization, d_dense.as<float>(), d_flag.as<int>(), stream));
+                                      table_device, table_size, regularization, d_dense.as<float>(), d_flag.as<int>(), stream));
     trace_lap("similarity: log_fraction", stream);
     MCB_TRY(correlate_dense_with_min(d_dense.as<float>(), pile->cells, features, features, similarity_dev, pile->cells, absolute,
                                      min_key, stream));

@@ -103,6 +103,11 @@ int pinned_staging(void** buffer) {
     static thread_local bool asked = false;
     if (!asked) {
         asked = true;
+        static const bool disabled = getenv("MCB_NO_STAGING") != nullptr;  // developer aid: read back through pageable memory
+        if (disabled) {
+            *buffer = nullptr;
+            return MCB_OK;
+        }
         {
             std::lock_guard<std::mutex> lock(mutex);
             if (!tried) {
