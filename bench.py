@@ -40,7 +40,9 @@ def parse_args():
     parser.add_argument("--cells", type=int, default=16000)
     parser.add_argument("--genes", type=int, default=27000)
     parser.add_argument("--features", type=int, default=2000)
-    parser.add_argument("--cpu-cells", type=int, default=8000, help="cells of the bounded CPU-baseline sample")
+    parser.add_argument("--cpu-cells", type=int, default=0,
+                        help="cells of the pile the CPU legs (--impl reference, cpu_baseline) time; 0 = --cells, the same pile "
+                             "as the GPU arm (the path is O(cells^2): any other value is not a like-for-like baseline)")
     parser.add_argument("--no-cpu-baseline", action="store_true")
     parser.add_argument("--atlas-cells", type=int, default=1000000,
                         help="cells of the divide-and-conquer atlas whose piles are timed after the per-pile steps (0: skip)")
@@ -60,6 +62,33 @@ def workload_name(args, cells):
             f"(downsample+log-fraction+correlate+rank+balance+prune_per)")
 
 
+def config_of(args, cells, genes, k, samples, nnz):
+    """The workload description both arms print (the driver compares them)."""
+    return {"workload": workload_name(args, cells), "cells": int(cells), "genes": int(genes), "feature_genes": int(args.features),
+            "k": int(k), "downsample_samples": int(samples), "umis_nnz": int(nnz),
+            "l2": "inputs larger than L2 (CSR pile 0.45 GB, similarity and rank matrices 1 GB each per step)"}
+
+
+def graph_digest(weights, indices, indptr):
+    """sha256 over the k-NN graph's indptr, indices and float32 weights (tests/test_gpu_bench_pile.py pins the bench
+    pile's digest against the oracle and tests/golden/bench_pile.json)."""
+    import hashlib
+
+    digest = hashlib.sha256()
+    for array in (indptr, indices, weights):
+        digest.update(np.ascontiguousarray(array).tobytes())
+    return digest.hexdigest()
+
+
+def golden_digest(cells, genes, features, seed):
+    path = os.path.join(ROOT, "tests", "golden", "bench_pile.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as handle:
+        golden = json.load(handle)
+    return golden.get(f"{cells}x{genes}x{features}@{seed}")
+
+
 def make_pile(cells, genes, seed):
     from synth import synth_umis
 
@@ -71,6 +100,7 @@ def make_pile(cells, genes, seed):
                             np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
     k = pipeline.knn_k_of_pile(cells, cell_umis)
     make_pile.max_cell_total = int(cell_umis.max())  # the pipeline has the totals (samples and k come from them)
+    make_pile.samples = samples
     return umis, samples, k
 
 
@@ -142,6 +172,10 @@ def cpu_threads():
         return os.cpu_count() or 1
 
 
+def cpu_cells_of(args):
+    return min(args.cpu_cells, args.cells) if args.cpu_cells > 0 else args.cells
+
+
 def cpu_step_factory(args):
     """Returns (step, description): step() runs the whole path once on the host cores."""
     from oracle import oracle
@@ -150,14 +184,15 @@ def cpu_step_factory(args):
     threads = cpu_threads() if ref is not None else 1
     if ref is not None:
         ref.set_threads_count(threads)
-    cells = min(args.cpu_cells, args.cells)
-    umis, _, k = make_pile(cells, args.genes, SEED)
+    cells = cpu_cells_of(args)
+    umis, samples, k = make_pile(cells, args.genes, SEED)
     timings = {}
 
     def step():
-        oracle.cpu_pile_knn_graph(umis, args.features, k, SEED, ref=ref, timings=timings)
+        step.graph = oracle.cpu_pile_knn_graph(umis, args.features, k, SEED, ref=ref, timings=timings)
         return cells
 
+    step.config = config_of(args, cells, args.genes, k, samples, umis.nnz)
     info = {"cores": threads, "kind": "reference" if ref is not None else "port",
             "sample": f"one {cells}-cell pile of the same generator ({args.genes} genes, {args.features} feature genes, k={k}), whole path"}
     return step, info, timings
@@ -181,7 +216,7 @@ def run_reference_arm(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1000.0 * elapsed / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "impl": "reference",
-        "config": {"workload": workload_name(args, min(args.cpu_cells, args.cells)), "timing": "host wall clock"},
+        "config": step.config, "timing": "host wall clock", "piles_per_step": 1, "graph_nnz": int(step.graph.nnz),
         "cpu_baseline": dict(info, value=value, unit=UNIT),
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "stage_seconds_per_step": {name: seconds / max(args.steps, 1) for name, seconds in timings.items()},
@@ -471,9 +506,18 @@ def run_gpu_arm(args):
     steps_e2e_workers(2 * workers)
     e2e_workers_ms, _ = timed(steps_e2e_workers, args.steps, whole_run=True)
     e2e_prefetch_ms = e2e_ms
+    # the headline is fixed beforehand (not the faster of the two): one host thread with the next upload in flight
     e2e_mode = "one host thread, next upload and previous read under the current pile's kernels"
-    if e2e_workers_ms < e2e_ms:  # both walk the same piles through the same entry points: the faster is the headline
-        e2e_ms, e2e_mode = e2e_workers_ms, f"{workers} host threads, each pile on its thread's own stream"
+    # the graph of one more end-to-end step, as it arrived in the page-locked result buffers, against the digest the
+    # test suite pins (tests/test_gpu_bench_pile.py: == oracle on the same pile, == tests/golden/bench_pile.json)
+    check_nnz = step_e2e()
+    digest = graph_digest(result["weights"].numpy()[:check_nnz], result["indices"].numpy()[:check_nnz], result["indptr"].numpy())
+    expected_digest = golden_digest(cells, genes, args.features, SEED + rank)
+    graph_check = {"sha256": digest, "expected": expected_digest,
+                   "ok": (digest == expected_digest) if expected_digest else None,
+                   "source": "tests/golden/bench_pile.json (pinned by tests/test_gpu_bench_pile.py against the oracle)"}
+    if expected_digest and digest != expected_digest:
+        raise SystemExit(f"bench: the timed pile's k-NN graph differs from the pinned digest ({digest} != {expected_digest})")
 
     atlas = None
     if args.atlas_cells > 0:
@@ -488,13 +532,14 @@ def run_gpu_arm(args):
     if os.path.exists(peaks_path):
         with open(peaks_path) as handle:
             peaks = json.load(handle)
-    # FP32-emulated tensor peak := dense TF32 peak / 3 (3 MMAs per algorithmic FMA) = (bf16 / 2) / 3; the
-    # correlate kernel runs inside a long step, so the sustained figure applies (B200_PROFILING.md).
-    bf16 = peaks.get("bf16_tflops_sustained")
-    peak_source = "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (tf32) / 3 (3xTF32)"
-    if bf16 is None:
-        bf16, peak_source = 1400.0, "fallback 1.4 PFLOP/s sustained bf16 (B200_PROFILING.md) / 2 / 3"
-    peak = bf16 / 6.0
+    # FP32-emulated tensor peak := dense TF32 peak / 3 (3 MMAs per algorithmic FMA).  The TF32 peak is measured here
+    # (torch.matmul with TF32 allowed, 8192^3: cuBLAS as the yardstick only, never on the path).  The contraction runs
+    # ~2 ms at a time inside a timed region of a fraction of a second with the clocks at their maximum, so the BURST
+    # figure is the denominator (B200_PROFILING.md: burst for a kernel timed alone / in a short region); the fraction
+    # against the sustained figure and the tensor-pipe utilisation of the ncu capture are given beside it.
+    tf32 = measure_tf32_peak(device)
+    peak = tf32["burst_tflops"] / 3.0
+    peak_source = "measured in this run: torch.matmul TF32 8192^3 best of 10 (burst) / 3 (3xTF32)"
     hbm = peaks.get("hbm_gbs")
     hbm_source = "MEASURED_PEAKS.json hbm_gbs"
     if hbm is None:
@@ -523,7 +568,12 @@ def run_gpu_arm(args):
     correlate_line = {"bound": "tensor", "kernel": "correlate_umma_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                       "frac": achieved / peak if achieved else None, "traffic": ncu_traffic("correlate_umma", cells, args.features),
                       "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_correlate_umma.txt",
-                      "peak_source": peak_source, "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms}
+                      "peak_source": peak_source, "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms,
+                      "tf32_peak_measured": tf32,
+                      "frac_of_sustained": achieved / (tf32["sustained_tflops"] / 3.0) if achieved else None,
+                      "frac_of_bf16_burst_over_6": achieved / (peaks["bf16_tflops"] / 6.0) if achieved and peaks.get("bf16_tflops") else None,
+                      "ncu_tensor_pipe_pct": 67.0,
+                      "ncu_tensor_pipe_source": "sm__pipe_tensor_cycles_active of profiles/r01_ncu_full_correlate_umma.txt"}
     # SURVEY 8d's algorithmic bytes: ranks read and write the whole square matrix; the downsample reads and writes the
     # pile's values and reads the row pointers; balance reads every rank once (count and fill passes are one stage).
     rank_line = hbm_line("rank_matrix_bucket_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, args.features),
@@ -537,18 +587,16 @@ def run_gpu_arm(args):
         "metric": METRIC, "value": world * cells * args.steps / (resident_ms * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": resident_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args, cells), "cells": cells, "genes": genes, "feature_genes": args.features, "k": k,
-                   "downsample_samples": samples, "umis_nnz": int(umis.nnz), "graph_nnz": int(nnz), "piles_per_step": world,
-                   "l2": "inputs larger than L2 (CSR pile 0.45 GB, similarity and rank matrices 1 GB each per step)"},
+        "config": config_of(args, cells, genes, k, samples, umis.nnz), "graph_nnz": int(nnz), "piles_per_step": world,
         "clocks": clocks,
         "host": {"cpus_near_gpu": len(gpu_cpus) if gpu_cpus else None, "cpus": len(launcher_cpus)},
         "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                 "unpipelined_ms_per_step": e2e_sequential_ms / args.steps,
-                "mode": e2e_mode, "one_thread_prefetch_ms_per_step": e2e_prefetch_ms / args.steps,
+                "mode": e2e_mode, "graph_check": graph_check, "one_thread_prefetch_ms_per_step": e2e_prefetch_ms / args.steps,
                 "worker_threads_ms_per_step": e2e_workers_ms / args.steps, "worker_threads": workers,
                 "note": "every step uploads its pile from pinned host memory and reads its graph back into pinned memory, both "
-                        "inside the timed region, walked as a worker of the divide-and-conquer loop walks its piles, two ways (the "
-                        "faster is `value`, see `mode`): one_thread_prefetch_ms_per_step = one host thread, the upload of the next "
+                        "inside the timed region, walked as a worker of the divide-and-conquer loop walks its piles, two ways (`value` "
+                        "is always the first, see `mode`): one_thread_prefetch_ms_per_step = one host thread, the upload of the next "
                         "pile (chunks on a copy stream) and the read of the previous graph (mcb_graph_read_start) under the "
                         "kernels of the current pile; worker_threads_ms_per_step = `worker_threads` host threads, each pile on its "
                         "thread's own stream, nothing prefetched.  unpipelined_ms_per_step: one pile at a time",
@@ -771,6 +819,43 @@ def time_candidates(args, umis):
             "note": "mcb_graph_seed_partition on the pile's k-NN graph as it lies on the device (incoming layout, choose_seeds, "
                     "optimize_partitions; cell UMIs up, partition down); one CTA = one SM per pile, one host thread and stream "
                     "per pile"}
+
+
+def measure_tf32_peak(device):
+    """Dense TF32 throughput of this GPU: the denominator of the contraction's roofline line, nothing else."""
+    import torch
+
+    previous = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        size = 8192
+        left = torch.randn(size, size, device=device)
+        right = torch.randn(size, size, device=device)
+        out = torch.empty(size, size, device=device)
+        for _ in range(3):
+            torch.matmul(left, right, out=out)
+        torch.cuda.synchronize(device)
+        flops = 2.0 * size ** 3
+        best = float("inf")
+        for _ in range(10):
+            begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            begin.record()
+            torch.matmul(left, right, out=out)
+            end.record()
+            end.synchronize()
+            best = min(best, begin.elapsed_time(end))
+        begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        count = max(10, int(2000.0 / best))  # about two seconds back to back
+        begin.record()
+        for _ in range(count):
+            torch.matmul(left, right, out=out)
+        end.record()
+        end.synchronize()
+        sustained = begin.elapsed_time(end) / count
+        return {"burst_tflops": flops / (best * 1e-3) / 1e12, "sustained_tflops": flops / (sustained * 1e-3) / 1e12,
+                "how": "torch.matmul float32 with allow_tf32, 8192^3: best of 10 (burst), back to back for ~2 s (sustained)"}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = previous
 
 
 def ncu_traffic(kernel, cells, features):

@@ -223,11 +223,21 @@ int mcb_pile_gene_totals(mcb_pile* pile, float* totals);
  * mcb_pile_similarity / mcb_pile_knn_graph (pass feature_genes = NULL there); genes_host (nullable) receives a
  * copy.  A stand-in for pipeline/select.py on synthetic data, computed without leaving the GPU. */
 int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host);
+int64_t mcb_pile_top_genes_count(const mcb_pile* pile); /* the length of the list on the device (0: none yet) */
+
+/* direct.py:242-249 -> computation.py:679-741 (log_data): the dense float32 [cells, features] operand of the similarity,
+ * dense_host[c, f] = log_table[count of gene feature_genes[f] in cell c] (log_table[c] = np.log2(float32(c) +
+ * regularization), made by numpy on the host, so the result is bit-identical to the reference's `data += 1/7;
+ * np.log2(data)`).  feature_genes as for mcb_pile_similarity.  A value that is not an integer count below table_size
+ * is an error (MCB_ERR_ARG; *outside_table, nullable, is set to 1). */
+int mcb_pile_log_fraction(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
+                          int64_t table_size, float regularization, float* dense_host, int* outside_table);
 
 /* direct.py:242-249 + tools/similarity.py:178-246: dense slice of `feature_genes` (host, distinct
  * gene indices; NULL = the list of mcb_pile_top_genes), log2(x + regularization) through `log_table` (host; log_table[c] = np.log2(c +
  * regularization) for c = 0 .. table_size-1), Pearson (absolute != 0: |r|) into similarity_dev
- * [cells, cells] (device).  *outside_table (host, may be NULL) reports values the table missed. */
+ * [cells, cells] (device).  Values the table misses are an error (see mcb_pile_log_fraction); *outside_table (host,
+ * may be NULL) reports them. */
 int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
                         int64_t table_size, float regularization, int absolute, float* similarity_dev, int* outside_table);
 /* ... followed by compute_obs_obs_knn_graph (see mcb_dev_knn_graph_f32). */
@@ -236,6 +246,35 @@ int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t fea
                        double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
                        int* outside_table, mcb_graph** out);
 void mcb_pile_free(mcb_pile* pile);
+
+/* ---- pipeline/divide_and_conquer.py:1250-1309: the atlas resident in HBM, piles gathered on the device ------------
+ *
+ * _compute_metacells_of_piles forces the whole cells x genes matrix to CSR once (:1286) and every pile of every phase
+ * (preliminary, final, outlier levels: :990-1079) is `ut.slice(adata, obs=pile mask)` of it (:1267).  Here the atlas is
+ * uploaded once and stays in HBM (float32 values, int32 gene indices, 64-bit row pointers: a million cells hold more
+ * than 2^31 non-zeros; 8 bytes per non-zero, 29 GB for a million cells of 3 600 genes); a pile is a list of atlas
+ * rows, gathered by a kernel, so that a pile of any phase costs its index list on the host link, not its UMIs. */
+typedef struct mcb_atlas mcb_atlas;
+/* Host arrays in (page-locked sources upload at the link's speed); returns when the atlas is resident. */
+int mcb_atlas_create_host(const float* data, const int32_t* indices, const int64_t* indptr, int64_t cells, int64_t genes,
+                          mcb_atlas** out);
+/* Borrowed device arrays (they must outlive the atlas), e.g. blocks uploaded rank by rank and exchanged over NVLink;
+ * the row pointers are given on the device and on the host. */
+int mcb_atlas_create_dev(const float* data, const int32_t* indices, const int64_t* indptr_device, const int64_t* indptr_host,
+                         int64_t cells, int64_t genes, mcb_atlas** out);
+int64_t mcb_atlas_cells(const mcb_atlas* atlas);
+int64_t mcb_atlas_nnz(const mcb_atlas* atlas);
+/* Total UMIs of every cell (direct.py:214-218: the row sums, float32) to a host array of `cells` floats. */
+int mcb_atlas_cell_totals(const mcb_atlas* atlas, float* totals_host);
+/* sums_device[g, :] (device, float32 [groups, genes], overwritten) = the sum of the rows of the cells with
+ * group_of_cells[c] == g (host int32 [cells]; negative: the cell is left out): the per-metacell totals of
+ * collect_metacells (pipeline/collect.py:162-201 -> ut.sum_groups), which the grouping of the preliminary metacells
+ * into the final piles starts from (divide_and_conquer.py:1153-1245). */
+int mcb_atlas_sum_groups(const mcb_atlas* atlas, const int32_t* group_of_cells, int64_t groups, float* sums_device, void* stream);
+void mcb_atlas_free(mcb_atlas* atlas);
+/* The pile of the atlas rows `rows` (host int64 [count], in pile order, = ut.slice(adata, obs=...)): owned device
+ * copies of the rows, on the calling thread's own stream; every mcb_pile_* call works on it as on an uploaded pile. */
+int mcb_pile_create_from_atlas(const mcb_atlas* atlas, const int64_t* rows, int64_t count, mcb_pile** out);
 
 /* ---- choose_seeds.cpp --------------------------------------------------------------------------- */
 

@@ -46,7 +46,10 @@ struct mcb_graph {
     Scratch weights, ranks, indices, indptr;
     cudaStream_t stream = nullptr;
     cudaStream_t read_stream = nullptr;  // mcb_graph_read_start: the copies to the host run beside the next pile's kernels
+    cudaEvent_t complete = nullptr;      // recorded on `stream` behind the last kernel that writes the graph
     ~mcb_graph() {
+        if (complete)
+            cudaEventDestroy(complete);
         if (read_stream) {
             cudaStreamSynchronize(read_stream);
             cudaStreamDestroy(read_stream);
@@ -127,12 +130,23 @@ int knn_graph_device(const float* similarity, int64_t n, int64_t k, double balan
     std::swap(graph->indices.stream, pruned.indices.stream);
     std::swap(graph->indptr.ptr, pruned.indptr.ptr);
     std::swap(graph->indptr.stream, pruned.indptr.stream);
+    // Other streams (mcb_graph_seed_partition on a worker thread's stream, mcb_graph_read_start) order themselves
+    // behind this event: the weights are still being written when this function returns.
+    MCB_CUDA(cudaEventCreateWithFlags(&graph->complete, cudaEventDisableTiming));
+    MCB_CUDA(cudaEventRecord(graph->complete, stream));
     return MCB_OK;
 }
 
 }  // namespace
 
 namespace mcb {
+// Orders `stream` behind the kernels that write the graph (a no-op on the graph's own stream).
+int graph_wait_complete(const mcb_graph* graph, cudaStream_t stream) {
+    if (graph->complete != nullptr && stream != graph->stream)
+        MCB_CUDA(cudaStreamWaitEvent(stream, graph->complete, 0));
+    return MCB_OK;
+}
+
 // The pile path: `similarity` (device, n x n) is consumed; known_min as in rank_outgoing_launch.
 int knn_graph_consuming(float* similarity, const uint32_t* known_min, int64_t n, int64_t k, double balanced_ranks_factor,
                         double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
@@ -349,11 +363,7 @@ int mcb_graph_read_start(mcb_graph* graph, float* weights, float* ranks, int32_t
     MCB_REQUIRE(graph != nullptr, "graph: null handle");
     if (graph->read_stream == nullptr)
         MCB_CUDA(cudaStreamCreateWithFlags(&graph->read_stream, cudaStreamNonBlocking));
-    cudaEvent_t complete;
-    MCB_CUDA(cudaEventCreateWithFlags(&complete, cudaEventDisableTiming));
-    MCB_CUDA(cudaEventRecord(complete, graph->stream));
-    MCB_CUDA(cudaStreamWaitEvent(graph->read_stream, complete, 0));
-    cudaEventDestroy(complete);
+    MCB_TRY(graph_wait_complete(graph, graph->read_stream));
     cudaStream_t stream = graph->read_stream;
     if (weights) MCB_TRY(to_host(weights, graph->weights, (size_t)graph->nnz, stream));
     if (ranks) MCB_TRY(to_host(ranks, graph->ranks, (size_t)graph->nnz, stream));

@@ -60,6 +60,19 @@ struct mcb_pile {
     }
 };
 
+// The atlas: the cells x genes UMI matrix of a whole divide-and-conquer run (CSR float32 / int32 with 64-bit row
+// pointers: a million cells hold more than 2^31 non-zeros), resident in HBM for all phases.  Piles are row subsets
+// gathered on the device (mcb_pile_create_from_atlas), so a pile costs an index list on the host link, not its UMIs.
+struct mcb_atlas {
+    int64_t cells = 0, genes = 0, nnz = 0;
+    Scratch own_data, own_indices, own_indptr;  // owned copies (create_host); empty when the arrays are borrowed
+    const float* data = nullptr;
+    const int32_t* indices = nullptr;
+    const int64_t* indptr = nullptr;   // device
+    std::vector<int64_t> host_indptr;  // the same row pointers on the host: pile sizes without a device round trip
+    int device = 0;
+};
+
 namespace {
 
 // Orders the pile's stream after the upload of a host pile (a no-op for a device pile).
@@ -184,6 +197,8 @@ int mcb_pile_create_dev(const float* data, const int32_t* indices, const int32_t
     MCB_TRY(copy_to_host(host_indptr.data(), indptr, (size_t)(cells + 1) * sizeof(int32_t), pile->stream));
     MCB_CUDA(cudaStreamSynchronize(pile->stream));
     MCB_TRY(finish_create(pile.get(), host_indptr.data()));
+    MCB_TRY(pile->status.alloc(sizeof(int), pile->stream));  // deferred errors of the downsampling (a row above the hint)
+    MCB_CUDA(cudaMemsetAsync(pile->status.ptr, 0, sizeof(int), pile->stream));
     pile->data = data;
     pile->indices = indices;
     pile->indptr = indptr;
@@ -202,8 +217,8 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
     float* totals = pile->gene_totals.as<float>();
     if (pile->chunk_ready.empty()) {
         MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples, 0, pile->cells, 0,
-                                       pile->widest, random_seed, 1, pile->max_row_total, nullptr, pile->stream, pile->indices,
-                                       totals));
+                                       pile->widest, random_seed, 1, pile->max_row_total,
+                                       pile->max_row_total ? pile->status.as<int>() : nullptr, pile->stream, pile->indices, totals));
     } else {
         // Every chunk as soon as it has arrived; with the largest cell total known nothing here waits on the device.
         // Chunks that have arrived already (a pile uploaded under the previous pile's kernels) go in one launch: a
@@ -263,20 +278,21 @@ __global__ void gene_slots_kernel(const int32_t* __restrict__ feature_genes, int
     if (atomicCAS(&slot_of_gene[gene], -1, (int32_t)f) != -1) atomicOr(bad, 2);
 }
 
-// feature_genes: host pointer, or nullptr to use the list mcb_pile_top_genes left on the device.
-// min_key (optional, device uint32 preset to 0xffffffff) receives the minimum of the similarity.
-int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table, int64_t table_size,
-                    float regularization, int absolute, float* similarity_dev, int* outside_table, unsigned int* min_key) {
-    MCB_REQUIRE(pile != nullptr && log_table && similarity_dev, "pile: null argument");
+// direct.py:242-249: the dense [cells, features] log-fraction operand of the feature genes, left in `d_dense`.
+// feature_genes: host pointer, or nullptr to use the list mcb_pile_top_genes left on the device (*features is then set).
+// d_flag (2 device ints) receives: [0] a value the table does not cover, [1] a bad feature gene list.
+int pile_log_fraction(mcb_pile* pile, const int32_t* feature_genes, int64_t* features_io, const float* log_table,
+                      int64_t table_size, float regularization, Scratch& d_dense, Scratch& d_flag) {
+    int64_t features = *features_io;
     if (feature_genes == nullptr) {
         MCB_REQUIRE(pile->top_genes_count > 0, "pile: no feature genes given and mcb_pile_top_genes was not called");
         features = pile->top_genes_count;
     }
     MCB_REQUIRE(features >= 1 && features <= pile->genes, "pile: bad feature genes count %lld", (long long)features);
+    *features_io = features;
     cudaStream_t stream = pile->stream;
     MCB_TRY(wait_for_upload(pile));
-    trace_lap("similarity: enter", stream);
-    Scratch d_genes, d_slot, d_table, d_dense, d_flag;
+    Scratch d_genes, d_slot;
     const int32_t* genes_device = pile->top_genes.as<int32_t>();
     if (feature_genes != nullptr) {
         MCB_TRY(d_genes.alloc((size_t)features * sizeof(int32_t), stream));
@@ -321,18 +337,37 @@ int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t featur
     const float* values = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     MCB_TRY(log_fraction_dense_launch(values, pile->indices, pile->indptr, pile->cells, d_slot.as<int32_t>(), features,
                                       table_device, table_size, regularization, d_dense.as<float>(), d_flag.as<int>(), stream));
-    trace_lap("similarity: log_fraction", stream);
-    MCB_TRY(correlate_dense_with_min(d_dense.as<float>(), pile->cells, features, features, similarity_dev, pile->cells, absolute,
-                                     min_key, stream));
-    trace_lap("similarity: correlate", stream);
+    return MCB_OK;
+}
+
+// Reads the two flags of pile_log_fraction (synchronises the stream) and turns them into errors.  A value outside
+// the table (not a non-negative integer below table_size) is an error: only the table, made by numpy's own log2 on the
+// host, is bit-exact with direct.py:245-249; *outside_table (nullable) still reports it.
+int check_log_fraction_flags(mcb_pile* pile, Scratch& d_flag, int* outside_table) {
     int flags[2] = {0, 0};
-    MCB_TRY(copy_to_host(flags, d_flag.ptr, sizeof(flags), stream));
+    MCB_TRY(copy_to_host(flags, d_flag.ptr, sizeof(flags), pile->stream));
     MCB_TRY(check_status(pile));  // synchronises the stream
     MCB_REQUIRE((flags[1] & 1) == 0, "pile: a feature gene is out of range");
     MCB_REQUIRE((flags[1] & 2) == 0, "pile: a feature gene is listed twice");
     if (outside_table)
         *outside_table = flags[0];
+    MCB_REQUIRE(flags[0] == 0, "pile: a value of a feature gene is not an integer count below the log table's size");
     return MCB_OK;
+}
+
+// min_key (optional, device uint32 preset to 0xffffffff) receives the minimum of the similarity.
+int pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table, int64_t table_size,
+                    float regularization, int absolute, float* similarity_dev, int* outside_table, unsigned int* min_key) {
+    MCB_REQUIRE(pile != nullptr && log_table && similarity_dev, "pile: null argument");
+    cudaStream_t stream = pile->stream;
+    trace_lap("similarity: enter", stream);
+    Scratch d_dense, d_flag;
+    MCB_TRY(pile_log_fraction(pile, feature_genes, &features, log_table, table_size, regularization, d_dense, d_flag));
+    trace_lap("similarity: log_fraction", stream);
+    MCB_TRY(correlate_dense_with_min(d_dense.as<float>(), pile->cells, features, features, similarity_dev, pile->cells, absolute,
+                                     min_key, stream));
+    trace_lap("similarity: correlate", stream);
+    return check_log_fraction_flags(pile, d_flag, outside_table);
 }
 
 }  // namespace
@@ -343,6 +378,17 @@ int mcb_pile_similarity(mcb_pile* pile, const int32_t* feature_genes, int64_t fe
                         int64_t table_size, float regularization, int absolute, float* similarity_dev, int* outside_table) {
     return pile_similarity(pile, feature_genes, features, log_table, table_size, regularization, absolute, similarity_dev,
                            outside_table, nullptr);
+}
+
+int mcb_pile_log_fraction(mcb_pile* pile, const int32_t* feature_genes, int64_t features, const float* log_table,
+                          int64_t table_size, float regularization, float* dense_host, int* outside_table) {
+    MCB_REQUIRE(pile != nullptr && log_table && dense_host, "pile: null argument");
+    Scratch d_dense, d_flag;
+    MCB_TRY(pile_log_fraction(pile, feature_genes, &features, log_table, table_size, regularization, d_dense, d_flag));
+    MCB_TRY(check_log_fraction_flags(pile, d_flag, outside_table));
+    MCB_TRY(copy_to_host(dense_host, d_dense.ptr, (size_t)pile->cells * features * sizeof(float), pile->stream));
+    MCB_CUDA(cudaStreamSynchronize(pile->stream));
+    return MCB_OK;
 }
 
 int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host) {
@@ -391,7 +437,198 @@ int mcb_pile_knn_graph(mcb_pile* pile, const int32_t* feature_genes, int64_t fea
                                incoming_degree_factor, outgoing_degree_factor, min_outgoing_degree, pile->stream, out);
 }
 
+}  // extern "C" (reopened below)
+
+namespace {
+
+// One CTA per pile row: the row's values and gene indices are copied from the atlas to the pile's own arrays.
+__global__ void __launch_bounds__(256) gather_rows_kernel(const float* __restrict__ data, const int32_t* __restrict__ indices,
+                                                         const int64_t* __restrict__ atlas_indptr, const int64_t* __restrict__ rows,
+                                                         const int32_t* __restrict__ pile_indptr, int64_t count,
+                                                         float* __restrict__ out_data, int32_t* __restrict__ out_indices) {
+    for (int64_t r = blockIdx.x; r < count; r += gridDim.x) {
+        const int64_t source = atlas_indptr[rows[r]];
+        const int32_t target = pile_indptr[r], size = pile_indptr[r + 1] - target;
+        for (int e = threadIdx.x; e < size; e += blockDim.x) {
+            out_data[target + e] = data[source + e];
+            out_indices[target + e] = indices[source + e];
+        }
+    }
+}
+
+// Row sums of a CSR matrix with 64-bit row pointers, one warp per row (UMI counts: exact in float32 in any order).
+__global__ void __launch_bounds__(256) atlas_row_totals_kernel(const float* __restrict__ data, const int64_t* __restrict__ indptr,
+                                                              int64_t rows, float* __restrict__ totals) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    float sum = 0.0f;
+    for (int64_t e = indptr[row] + lane; e < indptr[row + 1]; e += 32) sum += data[e];
+    for (int offset = 16; offset > 0; offset >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, offset);
+    if (lane == 0) totals[row] = sum;
+}
+
+// sums[group_of_row[r], gene] += value for every element of the rows with group_of_row[r] >= 0: the per-metacell UMI
+// totals of collect_metacells (pipeline/collect.py:162-201, `ut.sum_groups`), dense float32 [groups, genes] (integers
+// far below 2^24: exact in any order).
+__global__ void __launch_bounds__(256) atlas_sum_groups_kernel(const float* __restrict__ data, const int32_t* __restrict__ indices,
+                                                              const int64_t* __restrict__ indptr, int64_t rows,
+                                                              const int32_t* __restrict__ group_of_row, int64_t genes,
+                                                              float* __restrict__ sums) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int32_t group = group_of_row[row];
+    if (group < 0) return;
+    float* target = sums + (int64_t)group * genes;
+    for (int64_t e = indptr[row] + lane; e < indptr[row + 1]; e += 32) atomicAdd(&target[indices[e]], data[e]);
+}
+
+int check_atlas_indptr(const int64_t* indptr, int64_t cells) {
+    MCB_REQUIRE(indptr[0] == 0, "atlas: indptr[0] must be 0");
+    for (int64_t c = 0; c < cells; ++c)
+        MCB_REQUIRE(indptr[c + 1] >= indptr[c], "atlas: indptr is not monotone at cell %lld", (long long)c);
+    return MCB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcb_atlas_create_dev(const float* data, const int32_t* indices, const int64_t* indptr_device, const int64_t* indptr_host,
+                         int64_t cells, int64_t genes, mcb_atlas** out) {
+    MCB_REQUIRE(out && data && indices && indptr_device && indptr_host && cells >= 1 && genes >= 1, "atlas: bad arguments");
+    MCB_TRY(check_atlas_indptr(indptr_host, cells));
+    std::unique_ptr<mcb_atlas> atlas(new mcb_atlas());
+    atlas->cells = cells;
+    atlas->genes = genes;
+    atlas->nnz = indptr_host[cells];
+    atlas->data = data;
+    atlas->indices = indices;
+    atlas->indptr = indptr_device;
+    atlas->host_indptr.assign(indptr_host, indptr_host + cells + 1);
+    MCB_CUDA(cudaGetDevice(&atlas->device));
+    *out = atlas.release();
+    return MCB_OK;
+}
+
+int mcb_atlas_create_host(const float* data, const int32_t* indices, const int64_t* indptr, int64_t cells, int64_t genes,
+                          mcb_atlas** out) {
+    MCB_REQUIRE(out && data && indices && indptr && cells >= 1 && genes >= 1, "atlas: bad arguments");
+    MCB_TRY(check_atlas_indptr(indptr, cells));
+    std::unique_ptr<mcb_atlas> atlas(new mcb_atlas());
+    atlas->cells = cells;
+    atlas->genes = genes;
+    atlas->nnz = indptr[cells];
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    MCB_TRY(atlas->own_data.alloc((size_t)atlas->nnz * sizeof(float), stream));
+    MCB_TRY(atlas->own_indices.alloc((size_t)atlas->nnz * sizeof(int32_t), stream));
+    MCB_TRY(atlas->own_indptr.alloc((size_t)(cells + 1) * sizeof(int64_t), stream));
+    MCB_CUDA(cudaMemcpyAsync(atlas->own_indptr.ptr, indptr, (size_t)(cells + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    // one cudaMemcpyAsync per 256 MiB block: page-locked sources stream at the link's speed, pageable ones are staged
+    const int64_t block = 64ll << 20;
+    for (int64_t start = 0; start < atlas->nnz; start += block) {
+        const size_t count = (size_t)std::min<int64_t>(block, atlas->nnz - start);
+        MCB_CUDA(cudaMemcpyAsync(atlas->own_data.as<float>() + start, data + start, count * sizeof(float), cudaMemcpyHostToDevice, stream));
+        MCB_CUDA(cudaMemcpyAsync(atlas->own_indices.as<int32_t>() + start, indices + start, count * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, stream));
+    }
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    atlas->data = atlas->own_data.as<float>();
+    atlas->indices = atlas->own_indices.as<int32_t>();
+    atlas->indptr = atlas->own_indptr.as<int64_t>();
+    atlas->host_indptr.assign(indptr, indptr + cells + 1);
+    MCB_CUDA(cudaGetDevice(&atlas->device));
+    *out = atlas.release();
+    return MCB_OK;
+}
+
+int64_t mcb_atlas_cells(const mcb_atlas* atlas) { return atlas ? atlas->cells : 0; }
+int64_t mcb_atlas_nnz(const mcb_atlas* atlas) { return atlas ? atlas->nnz : 0; }
+
+int mcb_atlas_cell_totals(const mcb_atlas* atlas, float* totals_host) {
+    MCB_REQUIRE(atlas != nullptr && totals_host != nullptr, "atlas: null argument");
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    Scratch totals;
+    MCB_TRY(totals.alloc((size_t)atlas->cells * sizeof(float), stream));
+    MCB_PROFILED("atlas_row_totals", stream,
+                 atlas_row_totals_kernel<<<(unsigned)ceil_div(atlas->cells, 8), 256, 0, stream>>>(atlas->data, atlas->indptr, atlas->cells,
+                                                                                               totals.as<float>()));
+    MCB_LAUNCH_CHECK();
+    MCB_TRY(copy_to_host(totals_host, totals.ptr, (size_t)atlas->cells * sizeof(float), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_atlas_sum_groups(const mcb_atlas* atlas, const int32_t* group_of_cells, int64_t groups, float* sums_device, void* stream_) {
+    MCB_REQUIRE(atlas != nullptr && group_of_cells != nullptr && sums_device != nullptr && groups >= 1, "atlas: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    for (int64_t c = 0; c < atlas->cells; ++c)
+        MCB_REQUIRE(group_of_cells[c] < groups, "atlas: group %d of cell %lld is out of range", group_of_cells[c], (long long)c);
+    Scratch d_groups;
+    MCB_TRY(d_groups.alloc((size_t)atlas->cells * sizeof(int32_t), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_groups.ptr, group_of_cells, (size_t)atlas->cells * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemsetAsync(sums_device, 0, (size_t)groups * atlas->genes * sizeof(float), stream));
+    MCB_PROFILED("atlas_sum_groups", stream,
+                 atlas_sum_groups_kernel<<<(unsigned)ceil_div(atlas->cells, 8), 256, 0, stream>>>(
+                     atlas->data, atlas->indices, atlas->indptr, atlas->cells, d_groups.as<int32_t>(), atlas->genes, sums_device));
+    MCB_LAUNCH_CHECK();
+    MCB_CUDA(cudaStreamSynchronize(stream));  // d_groups' host source may be pageable
+    return MCB_OK;
+}
+
+void mcb_atlas_free(mcb_atlas* atlas) { delete atlas; }
+
+int mcb_pile_create_from_atlas(const mcb_atlas* atlas, const int64_t* rows, int64_t count, mcb_pile** out) {
+    MCB_REQUIRE(atlas != nullptr && rows != nullptr && out != nullptr && count >= 1, "pile: bad arguments");
+    std::unique_ptr<mcb_pile> pile(new mcb_pile());
+    pile->cells = count;
+    pile->genes = atlas->genes;
+    // the pile's row pointers, from the atlas' row pointers on the host
+    std::vector<int32_t> indptr((size_t)count + 1);
+    int64_t total = 0, widest = 0;
+    indptr[0] = 0;
+    for (int64_t r = 0; r < count; ++r) {
+        MCB_REQUIRE(rows[r] >= 0 && rows[r] < atlas->cells, "pile: atlas row %lld is out of range", (long long)rows[r]);
+        const int64_t size = atlas->host_indptr[rows[r] + 1] - atlas->host_indptr[rows[r]];
+        total += size;
+        widest = std::max(widest, size);
+        MCB_REQUIRE(total < (1ll << 31), "pile: more than 2^31 - 1 non-zeros");
+        indptr[r + 1] = (int32_t)total;
+    }
+    pile->nnz = total;
+    pile->widest = widest;
+    MCB_TRY(thread_stream(&pile->stream));
+    cudaStream_t stream = pile->stream;
+    Scratch d_rows;
+    MCB_TRY(pile->own_data.alloc((size_t)total * sizeof(float), stream));
+    MCB_TRY(pile->own_indices.alloc((size_t)total * sizeof(int32_t), stream));
+    MCB_TRY(pile->own_indptr.alloc((size_t)(count + 1) * sizeof(int32_t), stream));
+    MCB_TRY(pile->status.alloc(sizeof(int), stream));
+    MCB_TRY(d_rows.alloc((size_t)count * sizeof(int64_t), stream));
+    MCB_CUDA(cudaMemsetAsync(pile->status.ptr, 0, sizeof(int), stream));
+    // the two small lists go through one page-locked staging block of the pile (the sources are the caller's / a local)
+    MCB_CUDA(cudaMemcpyAsync(d_rows.ptr, rows, (size_t)count * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemcpyAsync(pile->own_indptr.ptr, indptr.data(), (size_t)(count + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    if (total > 0) {
+        MCB_PROFILED("gather_rows", stream,
+                     gather_rows_kernel<<<(unsigned)std::min<int64_t>(count, 1 << 20), 256, 0, stream>>>(
+                         atlas->data, atlas->indices, atlas->indptr, d_rows.as<int64_t>(), pile->own_indptr.as<int32_t>(), count,
+                         pile->own_data.as<float>(), pile->own_indices.as<int32_t>()));
+        MCB_LAUNCH_CHECK();
+    }
+    MCB_CUDA(cudaStreamSynchronize(stream));  // `rows` and the local row pointers may be pageable: they have been read now
+    pile->data = pile->own_data.as<float>();
+    pile->indices = pile->own_indices.as<int32_t>();
+    pile->indptr = pile->own_indptr.as<int32_t>();
+    *out = pile.release();
+    return MCB_OK;
+}
+
 int64_t mcb_pile_nnz(const mcb_pile* pile) { return pile ? pile->nnz : 0; }
+int64_t mcb_pile_top_genes_count(const mcb_pile* pile) { return pile ? pile->top_genes_count : 0; }
 
 int mcb_pile_wait_upload(mcb_pile* pile) {
     MCB_REQUIRE(pile != nullptr, "pile: null handle");

@@ -16,6 +16,7 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
                       int optimize, int with_orphans, double* score, int64_t* stats, cudaStream_t stream);
 int relayout_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t bands_in, int64_t bands_out,
                     int64_t nnz, float* out_data, int32_t* out_indices, int32_t* out_indptr, cudaStream_t stream);
+int graph_wait_complete(const mcb_graph* graph, cudaStream_t stream);
 }  // namespace mcb
 
 using namespace mcb;
@@ -82,7 +83,8 @@ int mcb_graph_seed_partition(const mcb_graph* graph, const float* mass_of_nodes,
     const int64_t nodes = mcb_graph_size(graph), edges = mcb_graph_nnz(graph);
     MCB_REQUIRE(nodes > 0, "graph_seed_partition: empty graph");
     cudaStream_t stream = nullptr;
-    MCB_TRY(thread_stream(&stream));  // the graph is complete: any stream may read it
+    MCB_TRY(thread_stream(&stream));
+    MCB_TRY(graph_wait_complete(graph, stream));  // the graph's last kernels may still be queued on the stream that built it
     // the incoming layout (tools/candidates.py:135: to_layout(..., "column_major")), on the device
     Scratch in_w, in_idx, in_ptr, d_mass, d_partition, d_mask;
     MCB_TRY(in_w.alloc(size_t(edges) * sizeof(float), stream));

@@ -524,6 +524,15 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
             MCB_PROFILED("downsample", stream, downsample_warp_kernel<false><<<(unsigned)grid, warps * 32, smem_bytes, stream>>>(wp));
         }
         MCB_LAUNCH_CHECK();
+        if (known_max_total > 0 && deferred_flag == nullptr) {
+            // the caller's hint sized the bitmap and nobody else reads the flag: a row above the hint must not pass silently
+            int host_flag = 0;
+            MCB_TRY(copy_to_host(&host_flag, flag.ptr, sizeof(int), stream));
+            MCB_CUDA(cudaStreamSynchronize(stream));
+            MCB_REQUIRE(host_flag != 3, "downsample: a row totals more than the stated maximum");
+            if (host_flag == 2)
+                return fail(MCB_ERR_UNSUPPORTED, "downsample: a row totals 2^32 UMIs or more");
+        }
         return MCB_OK;
     }
 

@@ -141,6 +141,30 @@ class Pile:
         check(function(self._handle, ctypes.c_int64(features), _ptr(genes)))
         return genes
 
+    def log_fraction(self, feature_genes: Optional[np.ndarray], *,
+                     regularization: float = CELLS_SIMILARITY_VALUE_REGULARIZATION,
+                     max_count: Optional[int] = None) -> np.ndarray:
+        """direct.py:242-249: the dense float32 [cells, features] operand ``log2(downsampled[:, genes] + 1/7)``
+        (``mcb_pile_log_fraction``); ``feature_genes=None`` uses the list ``select_top_genes`` left on the device."""
+        if feature_genes is not None:
+            feature_genes = np.ascontiguousarray(feature_genes, dtype="int32")
+            features = len(feature_genes)
+        else:
+            features = 0
+        if max_count is None:
+            max_count = int(self.samples if self.samples is not None else self._data.max(initial=0))
+        table = log_fraction_table(min(max_count, 1 << 20), regularization)
+        if feature_genes is None:
+            function = lib().mcb_pile_top_genes_count
+            function.restype = ctypes.c_int64
+            features = int(function(self._handle))
+        dense = np.empty((self.shape[0], features), dtype="float32")
+        function = lib().mcb_pile_log_fraction
+        function.restype = ctypes.c_int
+        check(function(self._handle, _ptr(feature_genes) if feature_genes is not None else None, ctypes.c_int64(features),
+                       _ptr(table), ctypes.c_int64(len(table)), ctypes.c_float(np.float32(regularization)), _ptr(dense), None))
+        return dense
+
     def knn_graph(self, feature_genes: Optional[np.ndarray], *, k: int, method: str = "abs_pearson",
                   regularization: float = CELLS_SIMILARITY_VALUE_REGULARIZATION,
                   balanced_ranks_factor: float = tl.KNN_BALANCED_RANKS_FACTOR,
