@@ -48,9 +48,8 @@ def parse_args():
                         help="cells of the divide-and-conquer atlas whose piles are timed after the per-pile steps (0: skip)")
     parser.add_argument("--e2e-workers", type=int, default=2,
                         help="host threads of a rank that walk its piles end to end, each on a stream of its own")
-    parser.add_argument("--atlas-candidates", type=int, default=1,
-                        help="1: after the atlas' k-NN graphs, time graphs + seeds + first partition optimisation of all its "
-                             "piles (graphs stay on the device, the optimisations run side by side); 0: skip")
+    parser.add_argument("--atlas-extra", default="",
+                        help="comma-separated cell counts of further atlases to walk (BASELINE.json configs C3 / C4: 500000,2000000)")
     parser.add_argument("--candidate-piles", type=int, default=16,
                         help="piles whose seeds and first partition optimisation run side by side after the k-NN steps "
                              "(N = 1 only; 0: skip)")
@@ -521,7 +520,12 @@ def run_gpu_arm(args):
 
     atlas = None
     if args.atlas_cells > 0:
-        atlas = time_atlas(args, library, pinned, result, capacity, hot_path, barrier, stream, device, rank, world, cells, genes)
+        resident.clear()  # the resident pile's arrays are not needed any more
+        torch.cuda.empty_cache()
+        atlas = time_atlas_walk(args, args.atlas_cells, device, rank, world, barrier)
+        extra = [int(text) for text in args.atlas_extra.split(",") if text.strip()]
+        if extra:
+            atlas["other_sizes"] = [time_atlas_walk(args, size, device, rank, world, barrier) for size in extra]
 
     if rank != 0:
         if world > 1:
@@ -622,167 +626,111 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
-def time_atlas(args, library, pinned, result, capacity, hot_path, barrier, stream, device, rank, world, cells, genes):
-    """BASELINE.json's second metric: the wall time of the k-NN graphs of every pile of one divide-and-conquer
-    phase over an atlas of `--atlas-cells` cells (strong scaling: the atlas is fixed, its piles are dealt to the
-    ranks largest first, no collective on the data path).  Every pile goes through the host-buffer path: its CSR is
-    uploaded from pinned memory and its graph is read back.  Generating a million distinct synthetic cells would take
-    longer than the run, so each pile is a row prefix of the rank's synthetic pile; the work of the path depends on
-    the sizes (cells, non-zeros, k), not on the values."""
+def synth_atlas_share(cells, genes, seed, first, last, device, chunk=8192):
+    """Rows [first, last) of a synthetic atlas of `cells` distinct cells (the model of tests/synth.py: cell types with
+    log-normal gene rates, log-normal depth, Poisson counts), generated block by block on the GPU with torch and moved to
+    page-locked HOST memory as CSR float32 / int32 (+ the share's own int64 row pointers): the walk uploads it from there.
+    A block depends on (seed, block index) only, so every rank generates its own share of the same atlas."""
+    import torch
+
+    generator = torch.Generator(device=device)
+    generator.manual_seed(seed)
+    types_count = max(4, cells // 400)
+    base = torch.exp(torch.randn(genes, generator=generator, device=device) * 1.6 - 3.0)
+    fold = torch.randn((types_count, genes), generator=generator, device=device) * 0.7
+    on_device, flushed, sizes, total = [], [], [], 0
+
+    def flush():
+        if on_device:
+            flushed.append((torch.cat([part[0] for part in on_device]).cpu(), torch.cat([part[1] for part in on_device]).cpu()))
+            on_device.clear()
+
+    for start in range(first - first % chunk, last, chunk):
+        stop = min(start + chunk, cells)
+        generator.manual_seed(seed * 1000003 + start)
+        types = torch.randint(0, types_count, (stop - start,), generator=generator, device=device)
+        depth = torch.exp(torch.randn(stop - start, generator=generator, device=device) * 0.4)
+        counts = torch.poisson(base[None, :] * torch.exp(fold[types]) * depth[:, None], generator=generator)
+        counts = counts[max(first - start, 0):min(last, stop) - start]
+        nonzero = counts.nonzero(as_tuple=True)
+        on_device.append((counts[nonzero].to(torch.float32), nonzero[1].to(torch.int32)))
+        sizes.append((counts != 0).sum(dim=1).cpu())
+        total += int(on_device[-1][0].numel())
+        del counts, nonzero
+        if len(on_device) >= 8:
+            flush()
+    flush()
+    data = torch.empty(total, dtype=torch.float32).pin_memory()
+    indices = torch.empty(total, dtype=torch.int32).pin_memory()
+    at = 0
+    for values, columns in flushed:
+        data[at:at + values.numel()] = values
+        indices[at:at + values.numel()] = columns
+        at += values.numel()
+    indptr = np.zeros(last - first + 1, dtype="int64")
+    np.cumsum(torch.cat(sizes).numpy(), out=indptr[1:])
+    assert at == total == int(indptr[-1])
+    return data, indices, indptr
+
+
+def time_atlas_walk(args, cells, device, rank, world, barrier):
+    """BASELINE.json's second metric: the wall time of a divide-and-conquer walk over a synthetic atlas of `cells` DISTINCT
+    cells (configs C3 / C4 and the 1M-cell atlas) at `world` GPUs, strong scaling: every rank's share of the atlas is
+    uploaded from page-locked host memory once and exchanged over NVLink (every rank then holds the atlas in HBM), then
+    preliminary piles (random_piles) -> k-NN graph + seeds + first partition optimisation of every pile -> the preliminary
+    metacells are summed and grouped into the final piles -> the same per-pile path over the final piles.  Piles are row
+    gathers on the device; graphs are left on the device and only the candidate partitions are read back."""
     import torch
     import torch.distributed as dist
 
-    from metacells_b200 import piles as pl, pipeline
+    from metacells_b200 import divide_and_conquer as dc
 
-    piles_count = -(-args.atlas_cells // cells)  # piles no larger than the synthetic pile
-    pile_of_cells = pl.random_piles(args.atlas_cells, args.atlas_cells / piles_count, random_seed=SEED)
-    sizes = np.bincount(pile_of_cells, minlength=int(pile_of_cells.max()) + 1)
-    assert sizes.max() <= cells, (sizes.max(), cells)
-    indptr = pinned["indptr"].numpy()
-    cell_umis = np.add.reduceat(pinned["data"].numpy(), indptr[:-1]).astype("float32")
-    mine = pl.piles_of_rank(sizes, rank, world)
-    ks = {size: pipeline.knn_k_of_pile(int(size), cell_umis[:size]) for size in set(int(sizes[pile]) for pile in mine)}
-
-    def upload(size):
-        pile = ctypes.c_void_p()
-        library.call("mcb_pile_create_host", p(pinned["data"].data_ptr()), p(pinned["indices"].data_ptr()),
-                     p(pinned["indptr"].data_ptr()), ctypes.c_int64(size), ctypes.c_int64(genes), ctypes.byref(pile))
-        return pile
-
-    workers = max(1, args.e2e_workers)
-    buffers_of_worker = [result] + [{name: torch.empty_like(tensor).pin_memory() for name, tensor in result.items()}
-                                    for _ in range(workers - 1)]
-
-    def one_pile(size, buffers):
-        pile = upload(size)
-        graph = hot_path(pile, ks[size])
-        nnz = library.lib.mcb_graph_nnz(graph)
-        if nnz > capacity:
-            raise SystemExit(f"result buffers too small: {nnz} > {capacity}")
-        library.call("mcb_graph_read", graph, p(buffers["weights"].data_ptr()), None, p(buffers["indices"].data_ptr()),
-                     p(buffers["indptr"].data_ptr()))
-        library.lib.mcb_graph_free(graph)
-        library.lib.mcb_pile_free(pile)
-        return nnz
-
-    def walk_piles(piles_of_run):
-        """The rank's worker threads take the rank's piles off one list, largest first (a dynamic queue, as SURVEY 8e),
-        each thread on a stream of its own: one pile's upload and read-back lie under another pile's kernels."""
-
-        remaining = list(piles_of_run)
-        lock = threading.Lock()
-        edges, failures = [0] * workers, []
-
-        def walk(index):
-            try:
-                library.call("mcb_set_device", ctypes.c_int(device.index))  # the current device is per thread
-                while True:
-                    with lock:
-                        if not remaining:
-                            return
-                        pile = remaining.pop(0)
-                    edges[index] += one_pile(int(sizes[pile]), buffers_of_worker[index])
-            except BaseException as failure:  # noqa: BLE001 (reported by the main thread)
-                failures.append(failure)
-
-        threads = [threading.Thread(target=walk, args=(index,)) for index in range(workers)]
-        for thread in threads:
-            thread.start()
-        for thread in threads:
-            thread.join()
-        if failures:
-            raise failures[0]
-        return sum(edges)
-
-    if mine:
-        walk_piles(mine[:workers])  # warm the pools for this pile size
-    runs = []
-    for _ in range(2):  # two walks over the atlas, the faster is reported (a shared host stalls a walk now and then)
-        begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        start = time.perf_counter()
-        begin.record(stream)
-        edges = walk_piles(mine)
-        end.record(stream)
-        barrier()
-        wall = time.perf_counter() - start
-        numbers = torch.tensor([begin.elapsed_time(end) * 1e-3, wall, float(edges)], dtype=torch.float64, device=device)
-        if world > 1:
-            both = numbers.clone()
-            dist.all_reduce(numbers, op=dist.ReduceOp.MAX)
-            dist.all_reduce(both, op=dist.ReduceOp.SUM)
-            edges = int(both[2].item())
-        runs.append((float(numbers[1].item()), float(numbers[0].item())))
-    numbers = torch.tensor([min(runs)[1], min(runs)[0]], dtype=torch.float64)
-    device_s, wall_s = float(numbers[0].item()), float(numbers[1].item())
-    line = {"metric": "divide_and_conquer_knn_graphs_wall_time", "cells": int(args.atlas_cells), "piles": int(len(sizes)),
-            "pile_cells": [int(sizes.min()), int(sizes.max())], "phases": 1, "n_gpus": world, "scaling": "strong",
-            "wall_s": wall_s, "device_s": device_s, "wall_s_of_runs": [run[0] for run in runs],
-            "cells_per_s": args.atlas_cells / wall_s, "graph_nnz": int(edges),
-            "data": "synthetic; every pile is a row prefix of the rank's synthetic pile, uploaded from pinned host memory and its "
-                    "graph read back; the rank's worker threads (e2e_workers) take piles off one list, each on its own stream "
-                    "(max over ranks, barrier on both sides; the faster of two walks, both in wall_s_of_runs)", "workers": workers}
-    if args.atlas_candidates:
-        line["with_candidates"] = time_atlas_candidates(args, library, upload, hot_path, barrier, device, world, sizes, mine, ks,
-                                                        cell_umis)
-    return line
-
-
-def time_atlas_candidates(args, library, upload, hot_path, barrier, device, world, sizes, mine, ks, cell_umis):
-    """The same phase carried on to the opening of compute_candidate_metacells: the k-NN graph of every pile of the rank
-    (uploaded from pinned memory, left on the device), then choose_seeds and the first optimize_partitions of all of them
-    side by side (mcb_graph_seed_partition: one SM, one host thread and stream per pile), partitions read back."""
-    import torch
-    import torch.distributed as dist
-    from concurrent.futures import ThreadPoolExecutor
-
-    from metacells_b200 import pipeline, tools as tl
-
-    bounds = pipeline.metacell_bounds()
+    first, last = cells * rank // world, cells * (rank + 1) // world
+    started = time.perf_counter()
+    data, indices, indptr = synth_atlas_share(cells, args.genes, SEED, first, last, device)
+    generate_s = time.perf_counter() - started
+    torch.cuda.empty_cache()
     barrier()
-    start = time.perf_counter()
-    graphs = []
+    started = time.perf_counter()
+    upload = {}
+    atlas = dc.Atlas.from_host_shares(data, indices, indptr, args.genes, rank=rank, world_size=world, device=device, times=upload)
     try:
-        def on_device():
-            library.call("mcb_set_device", ctypes.c_int(device.index))  # the current device is per thread
-
-        def build(pile):
-            size = int(sizes[pile])
-            handle = upload(size)
-            try:
-                return tl.KnnGraph(hot_path(handle, ks[size])), size
-            finally:
-                library.lib.mcb_pile_free(handle)
-
-        if mine:  # the rank's worker threads, each pile on its thread's own stream (as the k-NN walk above)
-            with ThreadPoolExecutor(max_workers=max(1, args.e2e_workers), initializer=on_device) as pool:
-                for entry in pool.map(build, mine):
-                    graphs.append(entry)
-        graphs_s = time.perf_counter() - start
-
-        def candidates(entry):
-            graph, size = entry
-            umis_of_cells = cell_umis[:size]
-            wanted = pipeline.seeds_count_for(float(sum(umis_of_cells)), size, bounds)
-            return graph.seed_partition(umis_of_cells, bounds, wanted, random_seed=SEED)
-
-        seeds = 0
-        if graphs:
-            with ThreadPoolExecutor(max_workers=len(graphs), initializer=on_device) as pool:
-                seeds = sum(result[2] for result in pool.map(candidates, graphs))
+        atlas.cell_umis  # the cells' totals, on the device (direct.py:214-218)
+        barrier()
+        resident_s = time.perf_counter() - started
+        walk = dc.divide_and_conquer_graphs(atlas, rank=rank, world_size=world, features=args.features, random_seed=SEED,
+                                            workers=max(1, args.e2e_workers))
+        barrier()
+        wall_s = time.perf_counter() - started
     finally:
-        for graph, _ in graphs:
-            graph.close()
-    barrier()
-    numbers = torch.tensor([time.perf_counter() - start, graphs_s, float(seeds)], dtype=torch.float64, device=device)
+        atlas.close()
+        del data, indices
+    times = walk["times"]
+    flat = [resident_s, wall_s, times["preliminary"]["graphs_s"], times["preliminary"]["candidates_s"], times.get("groups_s", 0.0),
+            times.get("final", {}).get("graphs_s", 0.0), times.get("final", {}).get("candidates_s", 0.0), upload["upload_s"],
+            upload["exchange_s"]]
+    numbers = torch.tensor(flat, dtype=torch.float64, device=device)
     if world > 1:
-        total = numbers.clone()
         dist.all_reduce(numbers, op=dist.ReduceOp.MAX)
-        dist.all_reduce(total, op=dist.ReduceOp.SUM)
-        seeds = int(total[2].item())
-    return {"metric": "divide_and_conquer_graphs_seeds_first_optimisation_wall_time", "wall_s": float(numbers[0].item()),
-            "graphs_s": float(numbers[1].item()), "seeds": int(seeds), "scaling": "strong",
-            "note": "max over ranks; every rank's piles optimised side by side, one SM each"}
+    flat = [float(value) for value in numbers.tolist()]
+    final = walk.get("final", walk["preliminary"])
+    sizes = [len(pile["cells"]) for pile in final]
+    return {"metric": "divide_and_conquer_wall_time", "cells": int(cells), "genes": int(args.genes), "n_gpus": world,
+            "scaling": "strong", "phases": 2 if "final" in walk else 1, "wall_s": flat[1], "cells_per_s": cells / flat[1],
+            "atlas_resident_s": flat[0], "upload_s": flat[7], "nvlink_exchange_s": flat[8],
+            "preliminary": {"piles": len(walk["preliminary"]), "graphs_s": flat[2], "candidates_s": flat[3],
+                            "metacells": int(walk.get("preliminary_metacells", walk["metacells"]))},
+            "groups_s": flat[4],
+            "final": {"piles": len(final), "pile_cells": [int(min(sizes)), int(max(sizes))], "graphs_s": flat[5],
+                      "candidates_s": flat[6], "metacells": int(walk["metacells"])},
+            "knn_graphs_s": flat[2] + flat[5],
+            "graph_edges": int(sum(pile["edges"] for pile in walk["preliminary"]) + sum(pile["edges"] for pile in walk.get("final", []))),
+            "h2d_bytes_this_rank": int(upload["h2d_bytes"]), "nvlink_bytes_this_rank": int(upload["exchanged_bytes"]),
+            "target_pile_size": walk["target_pile_size"], "generate_s_untimed": generate_s,
+            "data": "synthetic, distinct cells (tests/synth.py's model, generated per rank on the GPU, moved to page-locked host "
+                    "memory before the timed region); max over ranks, barrier on both sides; wall_s = atlas upload + exchange + "
+                    "cell totals + preliminary phase + groups + final phase; candidates = choose_seeds + first "
+                    "optimize_partitions of every pile, side by side, one SM each"}
 
 
 def time_candidates(args, umis):

@@ -276,6 +276,10 @@ void mcb_atlas_free(mcb_atlas* atlas);
  * copies of the rows, on the calling thread's own stream; every mcb_pile_* call works on it as on an uploaded pile. */
 int mcb_pile_create_from_atlas(const mcb_atlas* atlas, const int64_t* rows, int64_t count, mcb_pile** out);
 
+/* The pile of a dense float32 [cells, genes] matrix on the device (the metacells of collect_metacells as the "cells"
+ * of the grouping pile, divide_and_conquer.py:1153-1245): its non-zeros in column order, as scipy's csr_matrix(dense). */
+int mcb_pile_create_dense_dev(const float* dense, int64_t cells, int64_t genes, mcb_pile** out);
+
 /* ---- choose_seeds.cpp --------------------------------------------------------------------------- */
 
 /* choose_seeds (choose_seeds.cpp:264-372; bound as xt.choose_seeds, tools/candidates.py:733-745).  The graph is

@@ -484,6 +484,39 @@ __global__ void __launch_bounds__(256) atlas_sum_groups_kernel(const float* __re
     for (int64_t e = indptr[row] + lane; e < indptr[row + 1]; e += 32) atomicAdd(&target[indices[e]], data[e]);
 }
 
+// Non-zeros of every row of a dense matrix, one warp per row.
+__global__ void __launch_bounds__(256) dense_row_counts_kernel(const float* __restrict__ dense, int64_t rows, int64_t columns,
+                                                              int32_t* __restrict__ counts) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    int count = 0;
+    for (int64_t c = lane; c < columns; c += 32) count += dense[row * columns + c] != 0.0f ? 1 : 0;
+    count = warp_reduce_sum(count);
+    if (lane == 0) counts[row] = count;
+}
+
+// The non-zeros of every dense row in column order (scipy's csr_matrix(dense)), one warp per row.
+__global__ void __launch_bounds__(256) dense_to_csr_kernel(const float* __restrict__ dense, int64_t rows, int64_t columns,
+                                                          const int32_t* __restrict__ indptr, float* __restrict__ data,
+                                                          int32_t* __restrict__ indices) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    int at = indptr[row];
+    for (int64_t base = 0; base < columns; base += 32) {
+        const int64_t c = base + lane;
+        const float value = c < columns ? dense[row * columns + c] : 0.0f;
+        const unsigned kept = __ballot_sync(0xffffffffu, value != 0.0f);
+        if (value != 0.0f) {
+            const int slot = at + __popc(kept & ((1u << lane) - 1u));
+            data[slot] = value;
+            indices[slot] = (int32_t)c;
+        }
+        at += __popc(kept);
+    }
+}
+
 int check_atlas_indptr(const int64_t* indptr, int64_t cells) {
     MCB_REQUIRE(indptr[0] == 0, "atlas: indptr[0] must be 0");
     for (int64_t c = 0; c < cells; ++c)
@@ -620,6 +653,47 @@ int mcb_pile_create_from_atlas(const mcb_atlas* atlas, const int64_t* rows, int6
         MCB_LAUNCH_CHECK();
     }
     MCB_CUDA(cudaStreamSynchronize(stream));  // `rows` and the local row pointers may be pageable: they have been read now
+    pile->data = pile->own_data.as<float>();
+    pile->indices = pile->own_indices.as<int32_t>();
+    pile->indptr = pile->own_indptr.as<int32_t>();
+    *out = pile.release();
+    return MCB_OK;
+}
+
+int mcb_pile_create_dense_dev(const float* dense, int64_t cells, int64_t genes, mcb_pile** out) {
+    MCB_REQUIRE(dense != nullptr && out != nullptr && cells >= 1 && genes >= 1, "pile: bad arguments");
+    std::unique_ptr<mcb_pile> pile(new mcb_pile());
+    pile->cells = cells;
+    pile->genes = genes;
+    MCB_TRY(thread_stream(&pile->stream));
+    cudaStream_t stream = pile->stream;
+    Scratch counts;
+    MCB_TRY(counts.alloc((size_t)cells * sizeof(int32_t), stream));
+    dense_row_counts_kernel<<<(unsigned)ceil_div(cells, 8), 256, 0, stream>>>(dense, cells, genes, counts.as<int32_t>());
+    MCB_LAUNCH_CHECK();
+    std::vector<int32_t> indptr((size_t)cells + 1);
+    MCB_TRY(copy_to_host(indptr.data() + 1, counts.ptr, (size_t)cells * sizeof(int32_t), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    indptr[0] = 0;
+    int64_t total = 0, widest = 0;
+    for (int64_t c = 0; c < cells; ++c) {
+        widest = std::max<int64_t>(widest, indptr[c + 1]);
+        total += indptr[c + 1];
+        MCB_REQUIRE(total < (1ll << 31), "pile: more than 2^31 - 1 non-zeros");
+        indptr[c + 1] = (int32_t)total;
+    }
+    pile->nnz = total;
+    pile->widest = widest;
+    MCB_TRY(pile->own_data.alloc((size_t)total * sizeof(float), stream));
+    MCB_TRY(pile->own_indices.alloc((size_t)total * sizeof(int32_t), stream));
+    MCB_TRY(pile->own_indptr.alloc((size_t)(cells + 1) * sizeof(int32_t), stream));
+    MCB_TRY(pile->status.alloc(sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(pile->status.ptr, 0, sizeof(int), stream));
+    MCB_CUDA(cudaMemcpyAsync(pile->own_indptr.ptr, indptr.data(), (size_t)(cells + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    dense_to_csr_kernel<<<(unsigned)ceil_div(cells, 8), 256, 0, stream>>>(dense, cells, genes, pile->own_indptr.as<int32_t>(),
+                                                                      pile->own_data.as<float>(), pile->own_indices.as<int32_t>());
+    MCB_LAUNCH_CHECK();
+    MCB_CUDA(cudaStreamSynchronize(stream));  // the local row pointers have been read; `dense` may be reused by the caller
     pile->data = pile->own_data.as<float>();
     pile->indices = pile->own_indices.as<int32_t>();
     pile->indptr = pile->own_indptr.as<int32_t>();

@@ -295,7 +295,16 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
             continue;
         }
         unsigned long long total64 = 0;
-        for (int i = lane; i < n; i += 32) total64 += (uint32_t)in[i];
+        {
+            // four independent loads in flight per lane: the row is streamed, not walked one load at a time
+            int i = lane;
+            for (; i + 96 < n; i += 128) {
+                const float a = in[i], b = in[i + 32], c = in[i + 64], d = in[i + 96];
+                total64 += (unsigned long long)(uint32_t)a + (uint32_t)b;
+                total64 += (unsigned long long)(uint32_t)c + (uint32_t)d;
+            }
+            for (; i < n; i += 32) total64 += (uint32_t)in[i];
+        }
         for (int offset = 16; offset > 0; offset >>= 1) total64 += __shfl_xor_sync(0xffffffffu, total64, offset);
         if (total64 <= (unsigned long long)samples) {  // downsample.cpp:100-105
             if (out != in)
@@ -351,11 +360,22 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
                 r = mulmod_mersenne(state, pow_lane) % (total - (uint32_t)draw);  // downsample.cpp:111
             state = mulmod_mersenne(state, pow_warp);
             // rank among the UMIs left at the start of the batch
+            // replay of the earlier draws of the batch, latest first: lane - 1, lane - 2, ... 0.  shfl.up hands lane l the
+            // value of lane l - s together with the predicate "that lane exists", which gates the comparison: three
+            // instructions per step (shuffle, compare-and, predicated add)
             uint32_t q = r;
 #pragma unroll
-            for (int j = 30; j >= 0; --j) {
-                const uint32_t earlier = __shfl_sync(0xffffffffu, r, j);
-                q += (j < lane && earlier <= q) ? 1u : 0u;
+            for (int s = 1; s <= 31; ++s) {
+                asm volatile(
+                    "{\n\t"
+                    ".reg .pred exists, below;\n\t"
+                    ".reg .b32 earlier;\n\t"
+                    "shfl.sync.up.b32 earlier|exists, %1, %2, 0, 0xffffffff;\n\t"
+                    "setp.le.and.u32 below, earlier, %0, exists;\n\t"
+                    "@below add.u32 %0, %0, 1;\n\t"
+                    "}"
+                    : "+r"(q)
+                    : "r"(r), "r"(s));
             }
             int word = 0;
             uint32_t mark = 0;
@@ -405,9 +425,11 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
 
         // output: drawn UMIs of every gene = set bits in its range
         uint32_t running = 0;
+        float ahead = lane < n ? in[lane] : 0.0f;  // the next 32 counts are loaded while these are turned into bit ranges
         for (int base = 0; base < n; base += 32) {
             const int i = base + lane;
-            const uint32_t count = i < n ? (uint32_t)in[i] : 0u;
+            const uint32_t count = (uint32_t)ahead;
+            ahead = i + 32 < n ? in[i + 32] : 0.0f;
             const uint32_t inclusive = (uint32_t)warp_inclusive_scan((int)count, lane);
             uint32_t begin = running + inclusive - count, end = begin + count;
             running += __shfl_sync(0xffffffffu, inclusive, 31);

@@ -1,0 +1,414 @@
+"""The divide-and-conquer walk over an atlas resident in HBM (pipeline/divide_and_conquer.py:931-1079, 1250-1309).
+
+The reference forces the whole cells x genes matrix to CSR once in the parent process (:1286) and every pile of every
+phase is ``ut.slice(adata, obs=pile mask)`` of it, handed to a forked worker (:1267, :1291).  Here the atlas is uploaded
+once (``Atlas``), every rank holds it in HBM, and a pile of any phase is a row gather on the device
+(``mcb_pile_create_from_atlas``): the host link carries the pile's index list, not its UMIs.  With several ranks each
+uploads a share of the rows and the shares are exchanged over NVLink (NCCL broadcasts), so the host link of every rank
+carries 1/N of the atlas once.
+
+Phases, as ``_compute_divide_and_conquer_subset`` sequences them (:947-1079):
+
+1. preliminary: ``random_piles`` (:947) -> per pile the k-NN graph and the candidate metacells
+   (``choose_seeds`` + ``optimize_partitions`` on the graph as it lies on the device);
+2. groups (:1016, ``_compute_metacell_groups`` :1153-1245): the UMIs of every preliminary metacell are summed
+   (``collect_metacells`` -> ``mcb_atlas_sum_groups``), the metacells become the "cells" of a grouping pile whose masses
+   are the metacells' cell counts and whose target mass is the pile size (:1188-1210), and its communities are the final
+   piles;
+3. final (:1047): the same per-pile path over the final piles.
+
+What this module does NOT do (outside the hot path): the split / merge rounds of
+``compute_candidate_metacells`` beyond the first optimisation, deviant detection and dissolving, the outlier levels
+(:1062-1079: they re-run the same phases on the cells left without a metacell), and the rare-gene-module piles.  A
+grouping of more metacells than fit one pile is done in random piles of metacells (the reference recurses the whole
+divide-and-conquer on them, :1216-1226).
+"""
+from __future__ import annotations
+
+import ctypes
+import time
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import scipy.sparse as sp
+
+from . import piles as pl
+from . import pipeline
+from . import tools as tl
+from ._lib import check, lib
+
+__all__ = ["Atlas", "compute_target_pile_size", "compute_piles_phase", "group_metacells_into_piles",
+           "divide_and_conquer_graphs", "metacells_of_phase"]
+
+# metacells/parameters.py
+MIN_TARGET_PILE_SIZE = 8000
+MAX_TARGET_PILE_SIZE = 24000
+TARGET_METACELLS_IN_PILE = 100
+PILES_KNN_K_SIZE_FACTOR = 3
+PILES_MIN_SPLIT_SIZE_FACTOR = 1.5
+PILES_MAX_MERGE_SIZE_FACTOR = 0.15
+
+
+def compute_target_pile_size(cell_umis: np.ndarray, *, target_metacell_size: int = pipeline.TARGET_METACELL_SIZE,
+                             target_metacell_umis: int = pipeline.TARGET_METACELL_UMIS,
+                             min_target_pile_size: int = MIN_TARGET_PILE_SIZE,
+                             max_target_pile_size: int = MAX_TARGET_PILE_SIZE,
+                             target_metacells_in_pile: int = TARGET_METACELLS_IN_PILE) -> int:
+    """pipeline/divide_and_conquer.py:141-199."""
+    assert 0 < min_target_pile_size <= max_target_pile_size
+    assert cell_umis.dtype == "float32"
+    by_cells = target_metacell_size * target_metacells_in_pile
+    mean_metacell_size = target_metacell_umis / np.mean(cell_umis)
+    by_umis = int(round(mean_metacell_size * target_metacells_in_pile))
+    return min(max(by_cells, by_umis, min_target_pile_size), max_target_pile_size)
+
+
+class Atlas:
+    """The cells x genes UMI matrix of a divide-and-conquer run, resident in HBM (``mcb_atlas`` of include/mcb200.h)."""
+
+    def __init__(self, handle: ctypes.c_void_p, shape: Tuple[int, int], keep=()):
+        self._handle = handle
+        self.shape = shape
+        self._keep = keep  # device tensors the atlas borrows
+        self._cell_umis: Optional[np.ndarray] = None
+
+    @classmethod
+    def from_host(cls, umis: sp.csr_matrix) -> "Atlas":
+        """Upload a scipy CSR matrix (float32 values; int32 or int64 structure) in one call."""
+        umis = sp.csr_matrix(umis)
+        data = np.ascontiguousarray(umis.data, dtype="float32")
+        indices = np.ascontiguousarray(umis.indices, dtype="int32")
+        indptr = np.ascontiguousarray(umis.indptr, dtype="int64")
+        handle = ctypes.c_void_p()
+        function = lib().mcb_atlas_create_host
+        function.restype = ctypes.c_int
+        check(function(ctypes.c_void_p(data.ctypes.data), ctypes.c_void_p(indices.ctypes.data),
+                       ctypes.c_void_p(indptr.ctypes.data), ctypes.c_int64(umis.shape[0]), ctypes.c_int64(umis.shape[1]),
+                       ctypes.byref(handle)))
+        return cls(handle, umis.shape)
+
+    @classmethod
+    def from_device(cls, data, indices, indptr_device, indptr_host: np.ndarray, genes: int) -> "Atlas":
+        """Borrow CUDA ``torch`` tensors (float32 values, int32 gene indices, int64 row pointers) that already hold the
+        atlas; ``indptr_host`` is the same row pointers as a numpy int64 array."""
+        indptr_host = np.ascontiguousarray(indptr_host, dtype="int64")
+        cells = len(indptr_host) - 1
+        handle = ctypes.c_void_p()
+        function = lib().mcb_atlas_create_dev
+        function.restype = ctypes.c_int
+        check(function(ctypes.c_void_p(data.data_ptr()), ctypes.c_void_p(indices.data_ptr()),
+                       ctypes.c_void_p(indptr_device.data_ptr()), ctypes.c_void_p(indptr_host.ctypes.data),
+                       ctypes.c_int64(cells), ctypes.c_int64(int(genes)), ctypes.byref(handle)))
+        return cls(handle, (cells, int(genes)), keep=(data, indices, indptr_device))
+
+    @property
+    def handle(self) -> ctypes.c_void_p:
+        return self._handle
+
+    @property
+    def cell_umis(self) -> np.ndarray:
+        """direct.py:214-218: the total UMIs of every cell (float32), summed on the device once."""
+        if self._cell_umis is None:
+            totals = np.empty(self.shape[0], dtype="float32")
+            function = lib().mcb_atlas_cell_totals
+            function.restype = ctypes.c_int
+            check(function(self._handle, ctypes.c_void_p(totals.ctypes.data)))
+            self._cell_umis = totals
+        return self._cell_umis
+
+    def pile(self, rows: np.ndarray) -> pipeline.Pile:
+        rows = np.asarray(rows, dtype="int64")
+        in_range = len(rows) > 0 and rows.min() >= 0 and rows.max() < self.shape[0]
+        largest = float(self.cell_umis[rows].max(initial=0)) if in_range else None  # a bad row is reported by the library
+        return pipeline.Pile.from_atlas(self._handle, rows, self.shape[1], max_cell_total=largest)
+
+    def sum_groups(self, group_of_cells: np.ndarray, groups: int):
+        """Per-group UMI totals, a CUDA float32 ``torch`` tensor [groups, genes] (``mcb_atlas_sum_groups``)."""
+        import torch
+
+        group_of_cells = np.ascontiguousarray(group_of_cells, dtype="int32")
+        assert len(group_of_cells) == self.shape[0]
+        sums = torch.empty((int(groups), self.shape[1]), dtype=torch.float32, device="cuda")
+        function = lib().mcb_atlas_sum_groups
+        function.restype = ctypes.c_int
+        check(function(self._handle, ctypes.c_void_p(group_of_cells.ctypes.data), ctypes.c_int64(int(groups)),
+                       ctypes.c_void_p(sums.data_ptr()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return sums
+
+    def close(self) -> None:
+        if getattr(self, "_handle", None):
+            lib().mcb_atlas_free(self._handle)
+            self._handle = None
+        self._keep = ()
+
+    def __del__(self):
+        self.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *_):
+        self.close()
+
+
+def _atlas_from_host_shares(cls, share_data, share_indices, share_indptr: np.ndarray, genes: int, *, rank: int,
+                            world_size: int, device=None, times: Optional[dict] = None) -> "Atlas":
+    """Every rank holds a contiguous share of the atlas' rows in (page-locked) host memory -- rank r the rows after
+    those of rank r - 1 -- uploads it, and the shares are exchanged between the GPUs (one ``torch.distributed``
+    broadcast per share and array: NCCL over NVLink), so that every rank ends with the whole atlas in HBM while its
+    host link carried only its share.  ``share_data`` / ``share_indices``: float32 / int32 ``torch`` CPU tensors or
+    numpy arrays of the share's non-zeros; ``share_indptr``: the share's own row pointers (starting at 0)."""
+    import torch
+    import torch.distributed as dist
+
+    started = time.perf_counter()
+    device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    share_indptr = np.ascontiguousarray(share_indptr, dtype="int64")
+    if world_size > 1:
+        every_indptr: List[Optional[np.ndarray]] = [None] * world_size
+        dist.all_gather_object(every_indptr, share_indptr)
+    else:
+        every_indptr = [share_indptr]
+    sizes = [np.diff(pointers) for pointers in every_indptr]  # type: ignore[arg-type]
+    indptr = np.zeros(sum(len(size) for size in sizes) + 1, dtype="int64")
+    np.cumsum(np.concatenate(sizes), out=indptr[1:])
+    edges = np.cumsum([0] + [int(pointers[-1]) for pointers in every_indptr])  # type: ignore[index]
+    nnz = int(indptr[-1])
+
+    def as_tensor(array, dtype):
+        return array if isinstance(array, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(array, dtype=dtype))
+
+    host_data, host_indices = as_tensor(share_data, "float32"), as_tensor(share_indices, "int32")
+    device_data = torch.empty(nnz, dtype=torch.float32, device=device)
+    device_indices = torch.empty(nnz, dtype=torch.int32, device=device)
+    device_indptr = torch.from_numpy(indptr).to(device)
+    first, count = int(edges[rank]), int(edges[rank + 1] - edges[rank])
+    block = 64 << 20  # elements per copy
+    for start in range(0, count, block):
+        stop = min(start + block, count)
+        device_data[first + start:first + stop].copy_(host_data[start:stop], non_blocking=True)
+        device_indices[first + start:first + stop].copy_(host_indices[start:stop], non_blocking=True)
+    torch.cuda.synchronize(device)
+    uploaded = time.perf_counter()
+    if world_size > 1:
+        for source in range(world_size):
+            if edges[source + 1] > edges[source]:
+                dist.broadcast(device_data[int(edges[source]):int(edges[source + 1])], src=source)
+                dist.broadcast(device_indices[int(edges[source]):int(edges[source + 1])], src=source)
+        torch.cuda.synchronize(device)
+    if times is not None:
+        times["upload_s"] = uploaded - started
+        times["exchange_s"] = time.perf_counter() - uploaded
+        times["h2d_bytes"] = count * 8 + len(indptr) * 8
+        times["exchanged_bytes"] = (nnz - count) * 8 if world_size > 1 else 0
+    return cls.from_device(device_data, device_indices, device_indptr, indptr, genes)
+
+
+Atlas.from_host_shares = classmethod(_atlas_from_host_shares)  # type: ignore[attr-defined]
+
+
+def _rows_of_piles(pile_of_cells: np.ndarray) -> List[np.ndarray]:
+    """The cells of every pile in ascending order (the order a boolean mask slices them in, :1267)."""
+    pile_of_cells = np.asarray(pile_of_cells)
+    order = np.argsort(pile_of_cells, kind="stable")
+    ordered = pile_of_cells[order]
+    first = int(np.searchsorted(ordered, 0))  # cells of pile -1 belong to no pile
+    piles_count = int(ordered[-1]) + 1 if len(ordered) > first else 0
+    edges = np.searchsorted(ordered, np.arange(piles_count + 1))
+    return [order[edges[pile]:edges[pile + 1]] for pile in range(piles_count)]
+
+
+def _samples_of(totals: np.ndarray) -> int:
+    """tools/downsample.py:84-93."""
+    return int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(totals, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
+                         np.quantile(totals, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
+
+
+def _gather_dictionaries(mine: Dict[int, dict], world_size: int) -> Dict[int, dict]:
+    if world_size == 1:
+        return mine
+    import torch.distributed as dist
+
+    everyone: List[Optional[Dict[int, dict]]] = [None] * world_size
+    dist.all_gather_object(everyone, mine)
+    merged: Dict[int, dict] = {}
+    for part in everyone:
+        merged.update(part)  # type: ignore[arg-type]
+    return merged
+
+
+def metacells_of_phase(cells_count: int, phase: List[dict]) -> Tuple[np.ndarray, int]:
+    """The candidate metacell of every atlas cell, numbered pile by pile (-1: the cell was in no pile), and their count."""
+    metacell_of_cells = np.full(cells_count, -1, dtype="int32")
+    count = 0
+    for pile in phase:
+        communities = pile["communities"]
+        metacell_of_cells[pile["cells"]] = communities + count
+        count += int(communities.max()) + 1
+    return metacell_of_cells, count
+
+
+def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 0, world_size: int = 1, features: int = 2000,
+                        random_seed: int = 123456, candidates: bool = True, workers: int = 2,
+                        masses: Optional[np.ndarray] = None, bounds=None, k_arguments: Optional[dict] = None,
+                        times: Optional[dict] = None) -> List[dict]:
+    """One phase of the walk (``_compute_metacells_of_piles``, :1250-1309) as far as this package goes: for every pile
+    of ``pile_of_cells`` (the pile index of every atlas cell, -1 = in no pile) the k-NN graph (downsample -> feature
+    genes -> log-fraction -> similarity -> balanced graph, direct.py:214-283) and, with ``candidates``, ``choose_seeds``
+    and the first ``optimize_partitions`` on the graph as it lies on the device.  The piles are dealt to the ranks
+    largest first (``piles.piles_of_rank``); a rank's ``workers`` host threads take its piles off one list, each pile on
+    its thread's own stream, then all its optimisations run side by side, one SM each.  Every pile gets the same
+    ``random_seed`` (:1274-1279).  ``masses``: the mass of every cell for the candidates (default: its UMIs, direct.py
+    ``cell_umis``).  Returns, on every rank, one dictionary per pile in pile order: ``cells`` (atlas rows), ``k``,
+    ``edges`` and, with ``candidates``, ``communities`` (int32 per pile cell), ``score``, ``seeds``."""
+    rows_of_piles = _rows_of_piles(pile_of_cells)
+    sizes = [len(rows) for rows in rows_of_piles]
+    mine = pl.piles_of_rank(sizes, rank, world_size)
+    mine.sort(key=lambda pile: (-sizes[pile], pile))  # a dynamic queue, largest first
+    cell_umis = atlas.cell_umis
+    masses = cell_umis if masses is None else np.ascontiguousarray(masses, dtype="float32")
+    bounds = bounds if bounds is not None else pipeline.metacell_bounds()
+    k_arguments = k_arguments or {}
+    pool = pipeline.worker_pool(max(1, int(workers)))
+    started = time.perf_counter()
+
+    def build(pile: int):
+        rows = rows_of_piles[pile]
+        samples = _samples_of(cell_umis[rows])
+        k = pipeline.knn_k_of_pile(len(rows), masses[rows], **k_arguments)
+        with atlas.pile(rows) as handle:
+            handle.downsample(samples, random_seed)
+            handle.select_top_genes(min(features, atlas.shape[1] - 1))
+            return pile, handle.knn_graph(None, k=min(k, len(rows) - 1))
+
+    results: Dict[int, dict] = {}
+    for pile in [pile for pile in mine if sizes[pile] < 3]:  # too small for a graph: one community
+        results[pile] = {"cells": rows_of_piles[pile], "k": 0, "edges": 0, "communities": np.zeros(sizes[pile], dtype="int32"),
+                         "score": 0.0, "seeds": 1}
+    graphs = list(pool.map(build, [pile for pile in mine if sizes[pile] >= 3]))
+    graphs_seconds = time.perf_counter() - started
+    try:
+        for pile, graph in graphs:
+            results[pile] = {"cells": rows_of_piles[pile], "k": graph.k, "edges": graph.nnz}
+        if candidates and graphs:
+            def seed_partition(entry):
+                pile, graph = entry
+                pile_masses = masses[rows_of_piles[pile]]
+                wanted = max(pipeline.seeds_count_for(float(sum(pile_masses)), len(pile_masses), bounds), 1)
+                return pile, graph.seed_partition(pile_masses, bounds, wanted, random_seed=random_seed)
+
+            side_by_side = pipeline.worker_pool(pipeline._side_by_side(None))
+            for pile, (communities, score, seeds) in side_by_side.map(seed_partition, graphs):
+                results[pile].update(communities=communities, score=score, seeds=seeds)
+    finally:
+        for _, graph in graphs:
+            graph.close()
+    if times is not None:
+        times["graphs_s"] = times.get("graphs_s", 0.0) + graphs_seconds
+        times["candidates_s"] = times.get("candidates_s", 0.0) + time.perf_counter() - started - graphs_seconds
+    merged = _gather_dictionaries(results, world_size)
+    assert sorted(merged) == list(range(len(rows_of_piles))), "some piles were not processed"
+    return [merged[pile] for pile in range(len(rows_of_piles))]
+
+
+def group_metacells_into_piles(atlas: Atlas, metacell_of_cells: np.ndarray, metacells_count: int, *, target_pile_size: int,
+                               features: int = 2000, random_seed: int = 123456, times: Optional[dict] = None) -> np.ndarray:
+    """``_compute_metacell_groups`` (:1153-1245): the final pile of every cell.  The UMIs of every metacell are summed on
+    the device (``collect_metacells``, pipeline/collect.py:162-201), the metacells are the cells of a grouping pile whose
+    masses are their cell counts, with target mass = the pile size, target size ``target_metacells_in_pile``,
+    ``piles_knn_k_size_factor`` and the piles' split / merge factors (:1188-1210), and the communities of its candidate
+    partition are the final piles.  Every rank computes the same grouping.  More metacells than fit one pile are grouped
+    in random piles of metacells, whose graphs are built one after the other and whose optimisations run side by side."""
+    import torch
+
+    started = time.perf_counter()
+    sums = atlas.sum_groups(metacell_of_cells, metacells_count)
+    metacell_sizes = np.bincount(metacell_of_cells[metacell_of_cells >= 0], minlength=metacells_count).astype("float32")
+    metacell_umis = sums.sum(dim=1).cpu().numpy().astype("float32")
+    bounds = pipeline.metacell_bounds(target_metacell_size=TARGET_METACELLS_IN_PILE, target_metacell_umis=target_pile_size,
+                                      min_split_size_factor=PILES_MIN_SPLIT_SIZE_FACTOR,
+                                      max_merge_size_factor=PILES_MAX_MERGE_SIZE_FACTOR)
+    k_arguments = dict(target_metacell_size=TARGET_METACELLS_IN_PILE, target_metacell_umis=target_pile_size,
+                       knn_k_size_factor=PILES_KNN_K_SIZE_FACTOR)
+    if metacells_count > MAX_TARGET_PILE_SIZE:
+        pile_of_metacells_first = pl.random_piles(metacells_count, MAX_TARGET_PILE_SIZE // 2, random_seed=random_seed)
+    else:
+        pile_of_metacells_first = np.zeros(metacells_count, dtype="int32")
+    group_of_metacells = np.full(metacells_count, -1, dtype="int32")
+    graphs = []
+    try:
+        for rows in _rows_of_piles(pile_of_metacells_first):
+            if len(rows) < 3:  # nothing to group
+                graphs.append((rows, None))
+                continue
+            block = sums if len(rows) == metacells_count else sums[torch.from_numpy(rows).to(sums.device)].contiguous()
+            with pipeline.Pile.from_dense_device(block.data_ptr(), len(rows), atlas.shape[1]) as pile:
+                pile.set_max_cell_total(float(metacell_umis[rows].max()))
+                pile.downsample(_samples_of(metacell_umis[rows]), random_seed)
+                pile.select_top_genes(min(features, atlas.shape[1] - 1))
+                k = min(pipeline.knn_k_of_pile(len(rows), metacell_sizes[rows], **k_arguments), len(rows) - 1)
+                graphs.append((rows, pile.knn_graph(None, k=k)))
+            del block
+
+        def seed_partition(entry):
+            rows, graph = entry
+            if graph is None:
+                return np.zeros(len(rows), dtype="int32")
+            masses = metacell_sizes[rows]
+            wanted = max(pipeline.seeds_count_for(float(sum(masses)), len(rows), bounds), 1)
+            return graph.seed_partition(masses, bounds, wanted, random_seed=random_seed)[0]
+
+        groups = 0
+        side_by_side = pipeline.worker_pool(pipeline._side_by_side(None))
+        for (rows, _), communities in zip(graphs, side_by_side.map(seed_partition, graphs)):
+            group_of_metacells[rows] = communities + groups
+            groups += int(communities.max()) + 1
+    finally:
+        for _, graph in graphs:
+            if graph is not None:
+                graph.close()
+    pile_of_cells = np.full(len(metacell_of_cells), -1, dtype="int32")
+    grouped = metacell_of_cells >= 0
+    pile_of_cells[grouped] = group_of_metacells[metacell_of_cells[grouped]]
+    # a community the first optimisation left far above the largest pile the path is built for is cut into random parts
+    # (the reference's split rounds, tools/candidates.py:410-530, bound it by the split factor)
+    sizes = np.bincount(pile_of_cells[grouped], minlength=groups)
+    for pile in np.flatnonzero(sizes > MAX_TARGET_PILE_SIZE):
+        cells = np.flatnonzero(pile_of_cells == pile)
+        parts = pl.random_piles(len(cells), target_pile_size, random_seed=random_seed)
+        extra = parts > 0
+        pile_of_cells[cells[extra]] = groups + parts[extra] - 1
+        groups += int(parts.max())
+    if times is not None:
+        times["groups_s"] = times.get("groups_s", 0.0) + time.perf_counter() - started
+    return pile_of_cells
+
+
+def divide_and_conquer_graphs(atlas: Atlas, *, rank: int = 0, world_size: int = 1, features: int = 2000,
+                              random_seed: int = 123456, workers: int = 2, target_pile_size: Optional[int] = None) -> dict:
+    """Preliminary phase -> groups -> final phase over a resident atlas (:947-1060).  Returns the piles and candidate
+    metacells of both phases and the wall time of every step (``times``; seconds on this rank)."""
+    times: dict = {}
+    cells = atlas.shape[0]
+    if target_pile_size is None:
+        target_pile_size = compute_target_pile_size(atlas.cell_umis)
+    preliminary_pile_of_cells = pl.random_piles(cells, target_pile_size, random_seed=random_seed).astype("int32")
+    phase_times: dict = {}
+    preliminary = compute_piles_phase(atlas, preliminary_pile_of_cells, rank=rank, world_size=world_size, features=features,
+                                      random_seed=random_seed, workers=workers, times=phase_times)
+    times["preliminary"] = phase_times
+    result = {"target_pile_size": int(target_pile_size), "preliminary_pile_of_cells": preliminary_pile_of_cells,
+              "preliminary": preliminary, "times": times}
+    if len(preliminary) == 1:  # a single pile is its own final phase (:966-981)
+        result["metacell_of_cells"], result["metacells"] = metacells_of_phase(cells, preliminary)
+        return result
+    metacell_of_cells, metacells_count = metacells_of_phase(cells, preliminary)
+    final_pile_of_cells = group_metacells_into_piles(atlas, metacell_of_cells, metacells_count, target_pile_size=target_pile_size,
+                                                     features=features, random_seed=random_seed, times=times)
+    phase_times = {}
+    final = compute_piles_phase(atlas, final_pile_of_cells, rank=rank, world_size=world_size, features=features,
+                                random_seed=random_seed, workers=workers, times=phase_times)
+    times["final"] = phase_times
+    result.update(preliminary_metacells=metacells_count, final_pile_of_cells=final_pile_of_cells, final=final)
+    result["metacell_of_cells"], result["metacells"] = metacells_of_phase(cells, final)
+    return result

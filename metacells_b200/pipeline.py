@@ -55,6 +55,38 @@ def _ptr(array: np.ndarray) -> ctypes.c_void_p:
     return ctypes.c_void_p(array.ctypes.data)
 
 
+_POOLS: dict = {}
+
+
+def worker_pool(workers: int):
+    """The host threads that drive piles side by side on the calling thread's device, kept for the life of the process:
+    every thread owns a CUDA stream, a page-locked staging slot and a cached log table in the library (runtime.cu), so
+    a fresh executor per call would leak them.  One pool per (device, size); ``map`` may be used from one caller at a
+    time."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    device = ctypes.c_int(0)
+    check(lib().mcb_current_device(ctypes.byref(device)))
+    key = (device.value, int(workers))
+    pool = _POOLS.get(key)
+    if pool is None:
+        def on_device(index=device.value) -> None:  # the current device is per thread
+            check(lib().mcb_set_device(ctypes.c_int(index)))
+
+        pool = _POOLS[key] = ThreadPoolExecutor(max_workers=int(workers), initializer=on_device,
+                                                thread_name_prefix=f"mcb-pile-{device.value}")
+    return pool
+
+
+def _side_by_side(workers: Optional[int]) -> int:
+    """How many one-SM optimisations run at once: one per SM unless the caller says otherwise."""
+    if workers is not None:
+        return max(1, int(workers))
+    count = ctypes.c_int(0)
+    check(lib().mcb_device_sm_count(ctypes.byref(count)))
+    return count.value
+
+
 class Pile:
     """A device-resident pile (cells x genes UMI CSR matrix)."""
 
@@ -85,6 +117,55 @@ class Pile:
             function.restype = ctypes.c_int
             check(function(self._handle, ctypes.c_uint64(int(max_cell_total))))
 
+    @classmethod
+    def _adopt(cls, handle: ctypes.c_void_p, shape: Tuple[int, int]) -> "Pile":
+        """A pile whose arrays live on the device only (gathered from an atlas, or made from a dense device matrix)."""
+        pile = cls.__new__(cls)
+        pile._data = pile._indices = pile._indptr = None
+        pile.shape = shape
+        pile._pinned = []
+        pile._handle = handle
+        pile.samples = None
+        return pile
+
+    @classmethod
+    def from_atlas(cls, atlas_handle: ctypes.c_void_p, rows: np.ndarray, genes: int,
+                   max_cell_total: Optional[float] = None) -> "Pile":
+        """The pile of the atlas rows ``rows`` (``ut.slice(adata, obs=...)`` of divide_and_conquer.py:1267), gathered on
+        the device (``mcb_pile_create_from_atlas``): only the row list crosses the host link."""
+        rows = np.ascontiguousarray(rows, dtype="int64")
+        handle = ctypes.c_void_p()
+        function = lib().mcb_pile_create_from_atlas
+        function.restype = ctypes.c_int
+        check(function(atlas_handle, _ptr(rows), ctypes.c_int64(len(rows)), ctypes.byref(handle)))
+        pile = cls._adopt(handle, (len(rows), int(genes)))
+        if max_cell_total is not None:
+            pile.set_max_cell_total(max_cell_total)
+        return pile
+
+    @classmethod
+    def from_dense_device(cls, pointer: int, cells: int, genes: int) -> "Pile":
+        """The pile of a dense float32 [cells, genes] device matrix (``mcb_pile_create_dense_dev``)."""
+        handle = ctypes.c_void_p()
+        function = lib().mcb_pile_create_dense_dev
+        function.restype = ctypes.c_int
+        check(function(ctypes.c_void_p(pointer), ctypes.c_int64(cells), ctypes.c_int64(genes), ctypes.byref(handle)))
+        return cls._adopt(handle, (int(cells), int(genes)))
+
+    def set_max_cell_total(self, max_cell_total: float) -> None:
+        """``mcb_pile_set_max_cell_total``: the largest total of a cell, when the caller has the totals."""
+        function = lib().mcb_pile_set_max_cell_total
+        function.restype = ctypes.c_int
+        check(function(self._handle, ctypes.c_uint64(int(max_cell_total))))
+
+    def _largest_count(self) -> int:
+        """An upper bound of the values the log table must cover: a downsampled cell holds at most ``samples`` UMIs."""
+        if self.samples is not None:
+            return int(self.samples)
+        if self._data is None:
+            raise ValueError("max_count is needed for a device pile that was not downsampled")
+        return int(self._data.max(initial=0))
+
     def wait_upload(self) -> None:
         """Returns when the pile's upload has arrived (``mcb_pile_wait_upload``)."""
         check(lib().mcb_pile_wait_upload(self._handle))
@@ -114,6 +195,8 @@ class Pile:
         self.samples = int(samples)
 
     def downsampled(self) -> sp.csr_matrix:
+        if self._data is None:
+            raise NotImplementedError("a pile gathered on the device keeps no host copy of its structure")
         data = np.empty(len(self._data), dtype="float32")
         function = lib().mcb_pile_read_downsampled
         function.restype = ctypes.c_int
@@ -152,7 +235,7 @@ class Pile:
         else:
             features = 0
         if max_count is None:
-            max_count = int(self.samples if self.samples is not None else self._data.max(initial=0))
+            max_count = self._largest_count()
         table = log_fraction_table(min(max_count, 1 << 20), regularization)
         if feature_genes is None:
             function = lib().mcb_pile_top_genes_count
@@ -177,7 +260,7 @@ class Pile:
         if feature_genes is not None:
             feature_genes = np.ascontiguousarray(feature_genes, dtype="int32")
         if max_count is None:
-            max_count = int(self.samples if self.samples is not None else self._data.max(initial=0))
+            max_count = self._largest_count()
         table = log_fraction_table(min(max_count, 1 << 20), regularization)
         handle = ctypes.c_void_p()
         outside = ctypes.c_int(0)
@@ -239,26 +322,18 @@ def compute_piles_knn_graphs(piles: Iterable[sp.csr_matrix], *, features: int = 
     ``workers + 1`` piles are taken from ``piles`` ahead of the one being yielded."""
     if workers > 1:
         from collections import deque
-        from concurrent.futures import ThreadPoolExecutor
-
-        device = ctypes.c_int(0)
-        check(lib().mcb_current_device(ctypes.byref(device)))
-
-        def on_device() -> None:  # the current device is per thread
-            check(lib().mcb_set_device(device))
-
         import threading
 
         upload_turn = threading.Lock()  # the threads take turns uploading: each upload under the others' kernels
-        with ThreadPoolExecutor(max_workers=int(workers), initializer=on_device) as pool:
-            in_flight: deque = deque()
-            for umis in piles:
-                in_flight.append(pool.submit(compute_pile_knn_graph, umis, features=features, random_seed=random_seed,
-                                             upload_turn=upload_turn))
-                if len(in_flight) > workers:
-                    yield in_flight.popleft().result()
-            while in_flight:
+        pool = worker_pool(int(workers))
+        in_flight: deque = deque()
+        for umis in piles:
+            in_flight.append(pool.submit(compute_pile_knn_graph, umis, features=features, random_seed=random_seed,
+                                         upload_turn=upload_turn))
+            if len(in_flight) > workers:
                 yield in_flight.popleft().result()
+        while in_flight:
+            yield in_flight.popleft().result()
         return
 
     def start(umis: sp.csr_matrix):
@@ -352,23 +427,11 @@ def compute_piles_seed_partitions(piles, *, workers: Optional[int] = None, **arg
     SM, at most one per pile) run at once, each on the stream of the host thread that drives it (the entry points
     release the GIL).  The reference runs its piles in forked processes, one core each
     (pipeline/divide_and_conquer.py:1291-1295).  Results are in the order of ``piles`` and do not depend on ``workers``."""
-    from concurrent.futures import ThreadPoolExecutor
-
     piles = list(piles)
     if not piles:
         return []
-    if workers is None:
-        count = ctypes.c_int(0)
-        check(lib().mcb_device_sm_count(ctypes.byref(count)))
-        workers = count.value
-    device = ctypes.c_int(0)
-    check(lib().mcb_current_device(ctypes.byref(device)))
-
-    def on_device() -> None:  # the current device is per thread
-        check(lib().mcb_set_device(device))
-
-    with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(piles))), initializer=on_device) as pool:
-        return list(pool.map(lambda pile: compute_pile_seed_partition(pile[0], pile[1], **arguments), piles))
+    pool = worker_pool(_side_by_side(workers))
+    return list(pool.map(lambda pile: compute_pile_seed_partition(pile[0], pile[1], **arguments), piles))
 
 
 def pile_knn_graph_on_device(umis: sp.csr_matrix, *, features: int = 2000, random_seed: int = 123456):
@@ -391,8 +454,6 @@ def compute_piles_candidates(piles: Iterable[sp.csr_matrix], *, features: int = 
     for ~10 ms) and then, for all piles side by side, the seeds and the first partition optimisation on the graphs as
     they lie on the device (``KnnGraph.seed_partition``: one SM, one host thread and stream per pile).  Returns a list of
     ``(community_of_nodes, score, seeds_count, k)``.  The graphs stay on the device in between (12 bytes per edge)."""
-    from concurrent.futures import ThreadPoolExecutor
-
     bounds = metacell_bounds(**bounds_arguments)
     graphs = []
     try:
@@ -400,15 +461,6 @@ def compute_piles_candidates(piles: Iterable[sp.csr_matrix], *, features: int = 
             graphs.append(pile_knn_graph_on_device(umis, features=features, random_seed=random_seed))
         if not graphs:
             return []
-        if workers is None:
-            count = ctypes.c_int(0)
-            check(lib().mcb_device_sm_count(ctypes.byref(count)))
-            workers = count.value
-        device = ctypes.c_int(0)
-        check(lib().mcb_current_device(ctypes.byref(device)))
-
-        def on_device() -> None:  # the current device is per thread
-            check(lib().mcb_set_device(device))
 
         def candidates(entry):
             graph, cell_umis = entry
@@ -416,8 +468,7 @@ def compute_piles_candidates(piles: Iterable[sp.csr_matrix], *, features: int = 
             communities, score, seeds = graph.seed_partition(cell_umis, bounds, wanted, random_seed=random_seed)
             return communities, score, seeds, graph.k
 
-        with ThreadPoolExecutor(max_workers=max(1, min(int(workers), len(graphs))), initializer=on_device) as pool:
-            return list(pool.map(candidates, graphs))
+        return list(worker_pool(_side_by_side(workers)).map(candidates, graphs))
     finally:
         for graph, _ in graphs:
             graph.close()

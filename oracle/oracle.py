@@ -511,3 +511,126 @@ def cpu_pile_knn_graph(umis: sp.csr_matrix, features: int, k: int, seed: int, re
     weights = weigh_edges(pruned)
     lap("weigh_edges", start)
     return weights
+
+
+# ---------------------------------------------------------------------------------------------
+# feature-gene selection (pipeline/select.py:145-220 over tools/high.py and utilities/computation.py)
+# ---------------------------------------------------------------------------------------------
+
+
+def high_topN_genes(downsampled: sp.spmatrix, topN: int, min_gene_topN: int, ref=None) -> np.ndarray:
+    """tools/high.py:121-124: ``rank_per(column_major, rank=max(n_obs - topN - 1, 1)) >= min_gene_topN``
+    (computation.py:1285-1293 -> rank_rows on the dense [genes, cells] view)."""
+    dense = np.ascontiguousarray(downsampled.toarray().transpose(), dtype="float32")
+    rank = max(downsampled.shape[0] - topN - 1, 1)
+    if ref is not None:
+        values = np.empty(dense.shape[0], dtype="float32")
+        ref.rank_rows_float32_t(dense, values, rank)
+    else:
+        values = rank_rows(dense, rank)
+    return values >= min_gene_topN
+
+
+def high_total_genes(downsampled: sp.spmatrix, min_gene_total: float) -> np.ndarray:
+    """tools/high.py:29-79: ``sum_per(column) >= min_gene_total``."""
+    return np.asarray(sp.csc_matrix(downsampled).sum(axis=0)).reshape(-1) >= min_gene_total
+
+
+def _variance_per_column(matrix: sp.csc_matrix) -> np.ndarray:
+    """utilities/computation.py:1526-1546 with sum_per / sum_squared_per (:1224-1268) on a CSC matrix."""
+    sums = np.asarray(matrix.sum(axis=0)).reshape(-1)
+    sums_squared = np.asarray(matrix.multiply(matrix).sum(axis=0)).reshape(-1)
+    size = matrix.shape[0]
+    result = np.square(sums).astype(float)
+    result /= -size
+    result += sums_squared
+    result /= size
+    result[result < 0] = 0
+    return result
+
+
+def relative_variance_per_column(matrix: sp.spmatrix, window_size: int = 100) -> np.ndarray:
+    """utilities/computation.py:1549-1595 (normalized_variance_per, relative_variance_per) and :1836-1897
+    (sliding_window_function, ``median``, ordered by the mean)."""
+    import pandas as pd
+
+    matrix = sp.csc_matrix(matrix)
+    variance = _variance_per_column(matrix)
+    mean = np.asarray(matrix.sum(axis=0)).reshape(-1) / matrix.shape[0]
+    zeros_mask = mean == 0
+    normalized = np.reciprocal(mean, where=~zeros_mask)
+    normalized[zeros_mask] = 0
+    normalized *= variance
+    normalized[zeros_mask] = 1.0
+    with np.errstate(divide="ignore"):
+        np.log2(normalized, out=normalized)
+    if window_size % 2 == 0:
+        window_size += 1
+    half = (window_size - 1) // 2
+    size = len(normalized)
+    if window_size >= size:
+        return normalized - np.full(size, np.median(normalized))
+    order = np.argsort(mean)
+    reverse = np.argsort(order)
+    extended = np.concatenate([order[np.arange(window_size - half, window_size)], order,
+                               order[np.arange(size - window_size, size - window_size + half)]])
+    rolled = pd.Series(normalized[extended]).rolling(window_size).median().values[window_size - 1:]
+    assert rolled.size == size
+    return normalized - rolled[reverse]
+
+
+def select_feature_genes(downsampled: sp.spmatrix, *, min_gene_relative_variance: Optional[float] = 0.1, min_genes: int = 100,
+                         min_gene_total: Optional[int] = 50, min_gene_top3: Optional[int] = 4,
+                         lateral_genes_mask: Optional[np.ndarray] = None, ref=None) -> np.ndarray:
+    """pipeline/select.py:145-220 (no ``select_gene`` override): the boolean ``selected_gene`` mask."""
+    genes = downsampled.shape[1]
+    masks = []
+    if min_gene_top3 is not None:
+        masks.append(high_topN_genes(downsampled, 3, min_gene_top3, ref=ref))
+    if min_gene_total is not None:
+        masks.append(high_total_genes(downsampled, min_gene_total))
+    relative = None
+    if min_gene_relative_variance is not None:
+        relative = relative_variance_per_column(downsampled)
+        masks.append(relative >= min_gene_relative_variance)
+    additional = [] if lateral_genes_mask is None else [~np.asarray(lateral_genes_mask, dtype=bool)]
+
+    def combine(some):
+        combined = np.ones(genes, dtype=bool)
+        for mask in some:
+            combined &= mask
+        return combined
+
+    candidates = combine(masks + additional)
+    if np.sum(candidates) >= min_genes:
+        return candidates
+    if min_gene_relative_variance is None:
+        raise ValueError(f"Failed to select {min_genes} genes")
+    valid = combine(masks[:-1] + additional)
+    is_valid_set = False
+    if np.sum(valid) <= min_genes:
+        masks.pop()
+    else:
+        while True:
+            high = min_gene_relative_variance
+            min_gene_relative_variance -= 1 / 8
+            masks[-1] = relative >= min_gene_relative_variance
+            valid = combine(masks + additional)
+            if np.sum(valid) >= min_genes:
+                is_valid_set = True
+                break
+        for _ in range(4):
+            mid = (high + min_gene_relative_variance) / 2.0
+            masks[-1] = relative >= mid
+            mid_mask = combine(masks + additional)
+            if np.sum(mid_mask) >= min_genes:
+                min_gene_relative_variance = mid
+                valid = mid_mask
+                is_valid_set = True
+            else:
+                high = mid
+                is_valid_set = False
+        # select.py:208-209: the last mask written (the mid one) stays unless the valid set is put back
+        if not is_valid_set:
+            masks[-1] = valid
+    return combine(masks + additional)
