@@ -120,6 +120,18 @@ int mcb_dev_pairs_correlate_dense_f32(const float* first, const float* second, i
 int mcb_host_rank_matrix_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending);
 int mcb_dev_rank_matrix_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, void* stream);
 
+/* mcb_dev_rank_matrix_f32 for callers that cannot allocate.  No counterpart in the reference: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same
+ * kernels and the same ranks as mcb_dev_rank_matrix_f32; the one piece of scratch (the list of rows handed from the
+ * bucket sort to the merge sort) lives in a file-scope device array of the library, so the call makes no cudaMalloc /
+ * cudaFree / pool allocation.  Limits: rows <= MCB_RANK_MATRIX_NOALLOC_MAX_ROWS, columns <=
+ * MCB_RANK_MATRIX_NOALLOC_MAX_COLUMNS; beyond them the call fails with MCB_ERR_ARG and a message.  Every GPU that loads
+ * the library holds the array (257 KiB) until exit.  All calls share it: calls that overlap on one GPU (two streams,
+ * two host threads) race; calls on one stream, one after the other, are fine (every call clears what it needs). */
+#define MCB_RANK_MATRIX_NOALLOC_MAX_ROWS 65536
+#define MCB_RANK_MATRIX_NOALLOC_MAX_COLUMNS 24576
+int mcb_dev_rank_matrix_noalloc_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, void* stream);
+
 /* rank_rows<float32>  (rank.cpp:5-36): output[row] = value of 0-based `rank` in ascending order. */
 int mcb_host_rank_rows_f32(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank);
 int mcb_dev_rank_rows_f32(const float* matrix, int64_t rows, int64_t columns, int64_t row_stride, float* output, int64_t rank,

@@ -937,3 +937,85 @@ int collect_top_launch(int64_t degree, const float* similarity, int64_t rows, in
 }
 
 }  // namespace mcb
+
+// ---- rank_matrix without any allocation ---------------------------------------------------------------------------------
+//
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same two kernels as
+// rank_matrix_launch (bucket sort; rows with wide groups of ties passed on to the merge sort), with the list of passed
+// rows in a file-scope device array instead of the stream-ordered pool.  Every GPU that loads the library holds the
+// array (257 KiB) until exit; every call shares it, so calls that overlap on the GPU race.
+
+#include <mutex>
+
+#include "../../include/mcb200.h"
+
+namespace mcb {
+namespace {
+
+constexpr int64_t NOALLOC_MAX_ROWS = MCB_RANK_MATRIX_NOALLOC_MAX_ROWS;
+constexpr int64_t NOALLOC_MAX_COLUMNS = MCB_RANK_MATRIX_NOALLOC_MAX_COLUMNS;
+static_assert(NOALLOC_MAX_COLUMNS == MS_THREADS * 24, "the widest row the shared-memory rank kernels take");
+
+// [0]: the count of passed rows (cleared by every call), [64 ...]: the rows.  In host code this name is a stand-in, not
+// a device address: the address comes from cudaGetSymbolAddress, once per device.
+static __device__ __align__(256) int rank_noalloc_scratch[64 + NOALLOC_MAX_ROWS];
+
+int rank_noalloc_scratch_address(int** address) {
+    constexpr int MAX_DEVICES = 64;
+    static std::mutex mutex;
+    static int* of_device[MAX_DEVICES] = {};
+    int device = 0;
+    MCB_CUDA(cudaGetDevice(&device));
+    MCB_REQUIRE(device >= 0 && device < MAX_DEVICES, "rank_matrix_noalloc: device %d is beyond the %d this build knows", device, MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(mutex);
+    if (of_device[device] == nullptr) {
+        void* pointer = nullptr;
+        MCB_CUDA(cudaGetSymbolAddress(&pointer, rank_noalloc_scratch));  // with `device` current: this device's copy
+        of_device[device] = static_cast<int*>(pointer);
+    }
+    *address = of_device[device];
+    return MCB_OK;
+}
+
+template <int ITEMS>
+int rank_matrix_noalloc_launch(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending, int* scratch,
+                               cudaStream_t stream) {
+    using Plan = BucketPlan<ITEMS>;
+    int* passed_count = scratch;
+    int* passed_rows = scratch + 64;
+    MCB_CUDA(cudaMemsetAsync(passed_count, 0, sizeof(int), stream));  // the array keeps the last call's contents
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(rank_matrix_bucket_kernel<ITEMS>), (size_t)Plan::SMEM));
+    rank_matrix_bucket_kernel<ITEMS><<<(unsigned)rows, MS_THREADS, Plan::SMEM, stream>>>(matrix, rows, (int)columns, row_stride,
+                                                                                        ascending, passed_rows, passed_count);
+    MCB_LAUNCH_CHECK();
+    const size_t smem_bytes = (size_t)(MS_THREADS * ITEMS + MS_THREADS * ITEMS / 16 + 1) * 8;
+    MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(rank_matrix_merge_kernel<ITEMS>), smem_bytes));
+    const int64_t grid = std::min<int64_t>(rows, (int64_t)sm_count() * 4);
+    rank_matrix_merge_kernel<ITEMS><<<(unsigned)grid, MS_THREADS, smem_bytes, stream>>>(matrix, rows, (int)columns, row_stride,
+                                                                                       ascending, passed_rows, passed_count);
+    MCB_LAUNCH_CHECK();
+    return MCB_OK;
+}
+
+}  // namespace
+}  // namespace mcb
+
+extern "C" int mcb_dev_rank_matrix_noalloc_f32(float* matrix, int64_t rows, int64_t columns, int64_t row_stride, int ascending,
+                                               void* stream) {
+    using namespace mcb;
+    MCB_REQUIRE(rows >= 0 && columns >= 0 && row_stride >= columns, "rank_matrix_noalloc: bad shape");
+    MCB_REQUIRE(rows <= NOALLOC_MAX_ROWS, "rank_matrix_noalloc: %lld rows; the static scratch holds at most %lld",
+                (long long)rows, (long long)NOALLOC_MAX_ROWS);
+    MCB_REQUIRE(columns <= NOALLOC_MAX_COLUMNS, "rank_matrix_noalloc: %lld columns; at most %lld (wider rows need a workspace)",
+                (long long)columns, (long long)NOALLOC_MAX_COLUMNS);
+    if (rows == 0 || columns == 0)
+        return MCB_OK;
+    int* scratch = nullptr;
+    MCB_TRY(rank_noalloc_scratch_address(&scratch));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (columns <= MS_THREADS * 4) return rank_matrix_noalloc_launch<4>(matrix, rows, columns, row_stride, ascending, scratch, s);
+    if (columns <= MS_THREADS * 8) return rank_matrix_noalloc_launch<8>(matrix, rows, columns, row_stride, ascending, scratch, s);
+    if (columns <= MS_THREADS * 16) return rank_matrix_noalloc_launch<16>(matrix, rows, columns, row_stride, ascending, scratch, s);
+    return rank_matrix_noalloc_launch<24>(matrix, rows, columns, row_stride, ascending, scratch, s);
+}
