@@ -26,6 +26,7 @@
 // neighbour instead of two dependent ones); the merged (union) neighbour list of every node, built
 // once (u, outgoing weight or 0, incoming weight or 0) in ascending u.
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -299,6 +300,7 @@ struct OptParams {
     double* masses;
     double* scores;
     int nodes, partitions, padded, warps;
+    int parallel_shuffle;  // the shared-memory plan has room for the raw generator stream (8 bytes per node)
     Bounds bounds;
     double cooldown_pass, cooldown_node;
     uint32_t seed;
@@ -317,6 +319,7 @@ struct Control {
     int mover_node, mover_from, mover_to;
     int error;
     long long cycles_neighbours, cycles_candidates;
+    long long cycles_fine[4];  // warp 0: the partition scan, gathers + re-scoring, the ordered sums, (unused)
     int flags[OPT_MAX_WARPS];
     int counts[OPT_MAX_WARPS];
     int scan[34];
@@ -341,6 +344,7 @@ struct WarpBuffers {
     uint16_t* list;  // the (aliased) candidate list, in partition order
     double* staging; // one chunk of neighbour diffs, 32 doubles
     long long* cycles;  // warp 0 only: {scan + neighbours, candidates}
+    long long* fine;    // warp 0 only: Control::cycles_fine
 };
 constexpr int EVAL_UNROLL = 4;
 
@@ -388,6 +392,113 @@ __device__ void shuffle_order(uint16_t* order, int nodes, uint32_t& rng) {
         const uint32_t j = uniform_int(rng, uint32_t(i));
         const uint16_t tmp = order[i]; order[i] = order[j]; order[j] = tmp;
     }
+}
+
+// x * y mod (2^31 - 1) for x, y < 2^31 - 1, by Mersenne folding.
+__device__ __forceinline__ uint32_t mulmod_mersenne(uint32_t x, uint32_t y) {
+    const uint64_t product = uint64_t(x) * uint64_t(y);
+    uint32_t folded = uint32_t(product & 2147483647u) + uint32_t(product >> 31);
+    folded = (folded & 2147483647u) + (folded >> 31);
+    return folded >= 2147483647u ? folded - 2147483647u : folded;
+}
+
+// The same std::shuffle by the whole CTA (nodes <= 46340: the two-swaps-per-draw branch; `raw` and `scal` are shared
+// memory of `nodes` and nodes / 2 + 2 words).  What is sequential in it is little: which raw generator values the
+// rejection loops of uniform_int_distribution consume, and the swaps.  So (1) every thread writes its share of the raw
+// stream x0 a^(n+1) (closed form; pow_thread = a^(tid+1), pow_block = a^blockDim) and the scaling of every draw;
+// (2) warp 0 pairs draws with raw values, 32 at a time, restarting behind the first rejected value; (3) every thread turns
+// its accepted values into the two swap targets; (4) one thread swaps.  Returns the new generator state to thread 0.
+__device__ uint32_t shuffle_order_parallel(uint16_t* order, int nodes, uint32_t state, uint32_t* raw, uint32_t* scal,
+                                           uint32_t pow_thread, uint32_t pow_block) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int special = (nodes & 1) == 0 ? 1 : 0;      // an even count starts with one draw from {0, 1}
+    const int draws = special + (nodes - 1 - special) / 2;
+    const int capacity = nodes;                         // raw values kept; more are generated one by one (never, in practice)
+    {
+        uint32_t current = mulmod_mersenne(state, pow_thread);
+        for (int n = tid; n < capacity; n += blockDim.x) {
+            raw[n] = current;
+            current = mulmod_mersenne(current, pow_block);
+        }
+        for (int d = tid; d < draws; d += blockDim.x) {
+            const uint32_t i = d < special ? 1u : uint32_t(2 * (d - special) + 1 + special);
+            const uint32_t wanted = d < special ? 2u : (i + 1u) * (i + 2u);
+            scal[d] = 2147483645u / wanted;
+        }
+    }
+    __syncthreads();
+    uint32_t last = state;
+    if (tid < 32) {  // (2)
+        int d0 = 0, n0 = 0;
+        while (d0 < draws) {
+            const int d = d0 + lane, n = n0 + lane;
+            bool have = d < draws, rejected = false;
+            uint32_t value = 0;
+            if (have && n < capacity) {
+                const uint32_t i = d < special ? 1u : uint32_t(2 * (d - special) + 1 + special);
+                const uint32_t wanted = d < special ? 2u : (i + 1u) * (i + 2u);
+                value = raw[n] - 1u;
+                rejected = value >= wanted * scal[d];
+            }
+            const unsigned beyond = __ballot_sync(FULL, have && n >= capacity);
+            const unsigned rejects = __ballot_sync(FULL, rejected);
+            const unsigned stop = beyond | rejects;
+            const int taken = stop ? __ffs(stop) - 1 : min(32, draws - d0);  // lanes below the first rejected / missing value
+            __syncwarp();
+            if (lane < taken) raw[d] = value;  // d <= n: the accepted values are compacted in place
+            __syncwarp();
+            if (taken > 0) last = __shfl_sync(FULL, value, taken - 1) + 1u;
+            d0 += taken;
+            n0 += taken;
+            if (stop && (rejects >> taken & 1u)) {  // the rejected value is consumed too
+                last = __shfl_sync(FULL, value, taken) + 1u;
+                n0 += 1;
+            } else if (stop) {  // out of precomputed values: this draw one value at a time, as the serial loop does
+                if (lane == 0) {
+                    const uint32_t i = d0 < special ? 1u : uint32_t(2 * (d0 - special) + 1 + special);
+                    const uint32_t wanted = d0 < special ? 2u : (i + 1u) * (i + 2u);
+                    const uint32_t past = wanted * scal[d0];
+                    uint32_t draw;
+                    do {
+                        draw = rng_next(last) - 1u;
+                    } while (draw >= past);
+                    raw[d0] = draw;
+                }
+                last = __shfl_sync(FULL, last, 0);
+                d0 += 1;
+                n0 = capacity;
+            }
+        }
+    }
+    __syncthreads();
+    for (int d = tid; d < draws; d += blockDim.x) {  // (3)
+        const uint32_t x = raw[d] / scal[d];
+        if (d < special) {
+            scal[d] = x;
+        } else {
+            const uint32_t i = uint32_t(2 * (d - special) + 1 + special);
+            const uint32_t first = x / (i + 2u), second = x - first * (i + 2u);
+            scal[d] = first | second << 16;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {  // (4) stl_algo.h:3771-3790
+        int i = 1;
+        if (special) {
+            const uint32_t j = scal[0];
+            const uint16_t tmp = order[i]; order[i] = order[j]; order[j] = tmp;
+            ++i;
+        }
+        for (int d = special; d < draws; ++d) {
+            const uint32_t packed = scal[d];
+            const uint32_t first = packed & 0xffffu, second = packed >> 16;
+            uint16_t tmp = order[i]; order[i] = order[first]; order[first] = tmp;
+            ++i;
+            tmp = order[i]; order[i] = order[second]; order[second] = tmp;
+            ++i;
+        }
+    }
+    return last;
 }
 
 // uniform_real_distribution<double>(0, high): generate_canonical<double, 53> (random.tcc:3349-3381), two draws.
@@ -444,6 +555,8 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
         }
     }
     __syncwarp();
+    long long lap = clock64();
+    if (B.fine && lane == 0) B.fine[0] += lap - entered;
 
     // :725-802: every neighbour (merged list, ascending) re-scored as if the node had left `current` / joined the
     // neighbour's partition; the cold diffs of one partition are added in neighbour order.  EVAL_UNROLL chunks of 32
@@ -491,14 +604,24 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
                 linked[j] = 0;
             }
         }
+        if (B.fine) {  // the re-scored terms are complete here (the sums below consume them)
+            const long long now = clock64();
+            if (lane == 0) B.fine[1] += now - lap + (long long)(diff[0] == 1e300) + (long long)(diff[EVAL_UNROLL - 1] == 1e300);
+            lap = now;
+        }
+        unsigned peers_of[EVAL_UNROLL];  // the groups of equal partitions of all four chunks first: independent of each other
+#pragma unroll
+        for (int j = 0; j < EVAL_UNROLL; ++j) peers_of[j] = __match_any_sync(FULL, q[j]);
 #pragma unroll
         for (int j = 0; j < EVAL_UNROLL; ++j) {
             if (start + j * 32 >= count) break;
-            const unsigned peers = __match_any_sync(FULL, q[j]);
+            const unsigned peers = peers_of[j];
             if (linked[j] != 0) atomicAdd(&B.linked[q[j]], linked[j]);  // integers: any order; rarely non-zero
             B.staging[lane] = diff[j];
             __syncwarp();
             if (q[j] >= 0 && lane == __ffs(peers) - 1) {  // the first lane of a partition adds its terms in lane order
+                // (32 predicated steps, unrolled: the loads of the terms issue ahead of the dependent adds; a loop over
+                // the set bits only was measured slower)
                 double chain = B.cold[q[j]];
 #pragma unroll 8
                 for (int source = 0; source < 32; ++source)
@@ -506,6 +629,11 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
                 B.cold[q[j]] = chain;
             }
             __syncwarp();
+        }
+        if (B.fine) {
+            const long long now = clock64();
+            if (lane == 0) B.fine[2] += now - lap;
+            lap = now;
         }
     }
 
@@ -532,20 +660,30 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
 
     // :880-1002; all three push_back sites feed the one aliased list.  First the partitions that pass the two
     // connectivity filters (:950-957; few: a node is linked to a handful of partitions), in partition order ...
+    // (four rounds of 32 partitions at a time: their loads and tests are independent, only the counts chain)
     int admissible = 0;
-    for (int first = 0; first < partitions; first += 32) {
-        const int p = first + lane;
-        bool passes = false;
-        if (p < partitions && p != current) {
-            const int linked = B.linked[p];
-            const int connectivity_diff = int16_t(linked & 0xffff);
-            const int disconnected_diff = (linked - connectivity_diff) >> 16;
-            passes = disconnected_diff + current_disconnected_diff <= 0 &&
-                     connectivity_diff + current_connectivity_diff >= min_connectivity_diff;
+    for (int first = 0; first < partitions; first += 128) {
+        bool passes[4];
+        unsigned mask[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = first + 32 * u + lane;
+            passes[u] = false;
+            if (p < partitions && p != current) {
+                const int linked = B.linked[p];
+                const int connectivity_diff = int16_t(linked & 0xffff);
+                const int disconnected_diff = (linked - connectivity_diff) >> 16;
+                passes[u] = disconnected_diff + current_disconnected_diff <= 0 &&
+                            connectivity_diff + current_connectivity_diff >= min_connectivity_diff;
+            }
         }
-        const unsigned mask = __ballot_sync(FULL, passes);
-        if (passes) B.list[admissible + __popc(mask & ((1u << lane) - 1u))] = uint16_t(p);
-        admissible += __popc(mask);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mask[u] = __ballot_sync(FULL, passes[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (passes[u]) B.list[admissible + __popc(mask[u] & ((1u << lane) - 1u))] = uint16_t(first + 32 * u + lane);
+            admissible += __popc(mask[u]);
+        }
     }
     __syncwarp();
     // ... then their total diffs (a log each), keeping those that are candidates (compacted in place, in order).
@@ -678,6 +816,7 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
     {
         unsigned char* mine = region + size_t(warp < P.warps ? warp : 0) * warp_buffer_bytes(P.padded);
         B.cycles = warp == 0 ? &control->cycles_neighbours : nullptr;
+        B.fine = warp == 0 ? control->cycles_fine : nullptr;
         B.staging = reinterpret_cast<double*>(mine);
         B.cold = B.staging + 32;
         B.total = B.cold + P.padded;
@@ -686,6 +825,20 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
     }
     uint16_t* staged_order = reinterpret_cast<uint16_t*>(region);
 
+    // a^(tid+1) and a^blockDim of std::minstd_rand, for the parallel shuffle
+    uint32_t pow_thread = 1, pow_block = 1;
+    {
+        uint32_t base = 48271u;
+        for (unsigned e = threadIdx.x + 1; e; e >>= 1) {
+            if (e & 1u) pow_thread = mulmod_mersenne(pow_thread, base);
+            base = mulmod_mersenne(base, base);
+        }
+        base = 48271u;
+        for (unsigned e = blockDim.x; e; e >>= 1) {
+            if (e & 1u) pow_block = mulmod_mersenne(pow_block, base);
+            base = mulmod_mersenne(base, base);
+        }
+    }
     stage_log_tables(staged);
     const LogTables t = log_tables(staged);
     for (int p = threadIdx.x; p < P.partitions; p += blockDim.x) {
@@ -702,6 +855,7 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
         control->error = 0;
         control->cycles_neighbours = 0;
         control->cycles_candidates = 0;
+        for (int i = 0; i < 4; ++i) control->cycles_fine[i] = 0;
     }
     __syncthreads();
     for (int p = threadIdx.x; p < P.partitions; p += blockDim.x) refresh_partition(S, p, P.bounds, t);
@@ -742,7 +896,20 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
         // visit (:485, a chain of products).
         for (int i = threadIdx.x; i < nodes; i += blockDim.x) staged_order[i] = uint16_t(P.order[i]);
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (P.parallel_shuffle) {
+            uint32_t* raw = reinterpret_cast<uint32_t*>(region + align_up(size_t(nodes) * 2, 16));
+            uint32_t* scal = raw + nodes;
+            const uint32_t rng = shuffle_order_parallel(staged_order, nodes, control->rng, raw, scal, pow_thread, pow_block);
+            if (threadIdx.x == 0) control->rng = rng;
+            if (threadIdx.x == 32) {  // beside thread 0's swaps: the temperature of every visit
+                double running = temperature;
+                for (int i = 0; i < nodes; ++i) {
+                    running = dmul(running, cooldown_rate);
+                    P.visit_temperature[i] = running;
+                }
+                control->temperature_end = running;
+            }
+        } else if (threadIdx.x == 0) {
             uint32_t rng = control->rng;
             shuffle_order(staged_order, nodes, rng);
             control->rng = rng;
@@ -785,6 +952,17 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
                 const int i = P.active[done + warp];
                 node = P.order[i];
                 visit = P.visit_temperature[i];
+                // the table row and the neighbour list of the node this warp is likely to evaluate next (the one P.warps
+                // visits on, unless a move restarts the batch earlier: then its rows are in the caches already), into L2
+                if (done + P.warps + warp < active_count) {
+                    const int next = P.order[P.active[done + P.warps + warp]];
+                    const char* row = reinterpret_cast<const char*>(P.table + int64_t(next) * P.partitions);
+                    for (int line = lane * 128; line < P.partitions * int(sizeof(Entry)); line += 32 * 128)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(row + line));
+                    const char* list = reinterpret_cast<const char*>(P.neighbours + int64_t(P.out_ptr[next]) + P.in_ptr[next]);
+                    for (int line = lane * 128; line < P.union_count[next] * int(sizeof(Neighbour)); line += 32 * 128)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(list + line));
+                }
                 const int candidates = evaluate_node(P, S, B, t, node, visit, lane);
                 if (lane == 0) {
                     control->flags[warp] = candidates > 0;
@@ -860,6 +1038,7 @@ __global__ void __launch_bounds__(OPT_THREADS, 1) optimize_partitions_kernel(Opt
             P.stats[4] = batches; P.stats[5] = control->error;
             P.stats[8] = cycles_setup; P.stats[9] = cycles_evaluate; P.stats[10] = cycles_choose; P.stats[11] = cycles_move;
             P.stats[12] = control->cycles_neighbours; P.stats[13] = control->cycles_candidates;
+            P.stats[6] = control->cycles_fine[0]; P.stats[7] = control->cycles_fine[1]; P.stats[14] = control->cycles_fine[2];
         }
     }
 }
@@ -913,7 +1092,11 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
     MCB_REQUIRE(fixed + warp_buffer_bytes(padded) <= shared_limit && fixed + size_t(n) * 2 <= shared_limit,
                 "optimize_partitions: %d partitions x %d nodes do not fit the shared-memory plan", partitions, n);
     const int warps = int(std::min<size_t>(OPT_MAX_WARPS, (shared_limit - fixed) / warp_buffer_bytes(padded)));
-    const size_t shared_bytes = fixed + std::max(size_t(warps) * warp_buffer_bytes(padded), size_t(n) * 2);
+    // the visiting order (2 bytes per node) and, when it fits, the raw generator stream and the scaling of every draw of
+    // the shuffle (shuffle_order_parallel: 4 + 2 bytes per node more)
+    const size_t shuffle_bytes = align_up(size_t(n) * 2, 16) + size_t(n) * 4 + (size_t(n) / 2 + 2) * 4;
+    const bool parallel_shuffle = n >= 64 && n <= 46340 && fixed + shuffle_bytes <= shared_limit && std::getenv("MCB_SERIAL_SHUFFLE") == nullptr;
+    const size_t shared_bytes = fixed + std::max(size_t(warps) * warp_buffer_bytes(padded), parallel_shuffle ? shuffle_bytes : size_t(n) * 2);
 
     Scratch table, self, neighbours, union_count, incoming_log2, sizes, masses, scores, temperatures, frozen,
         order, visit_temperature, active, result, stats_device;
@@ -985,6 +1168,7 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
         params.partitions = partitions;
         params.padded = padded;
         params.warps = warps;
+        params.parallel_shuffle = parallel_shuffle ? 1 : 0;
         params.bounds = bounds;
         params.cooldown_pass = cooldown_pass;
         params.cooldown_node = cooldown_node;

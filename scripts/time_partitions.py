@@ -44,6 +44,7 @@ for it in range(args.repeat):
     stats = xt.last_optimize_stats.copy()
     print("GPU optimize_partitions: %.3f s score %.17g passes %d visits %d moves %d skipped %d batches %d" % (elapsed, my_score, *stats[:5]), flush=True)
     print("   Mcycles: setup %.0f evaluate %.0f choose %.0f move %.0f | warp0 scan+neighbours %.0f candidates %.0f" % tuple(stats[8:14] / 1e6), flush=True)
+    print("   warp0 Mcycles: partition scan %.0f, gathers + re-scoring %.0f, ordered sums %.0f" % (stats[6] / 1e6, stats[7] / 1e6, stats[14] / 1e6), flush=True)
 if not args.no_cpu:
     theirs = initial.copy()
     start = time.perf_counter()
