@@ -39,7 +39,10 @@ def parse_args():
     parser.add_argument("--impl", default="b200", choices=["b200", "reference"])
     parser.add_argument("--cells", type=int, default=16000)
     parser.add_argument("--genes", type=int, default=27000)
-    parser.add_argument("--features", type=int, default=2000)
+    parser.add_argument("--features", type=lambda text: text if text == "select" else int(text), default="select",
+                        help='"select": the feature genes extract_selected_data of pipeline/select.py picks (high top-3, high total, '
+                             "high relative variance), in both arms; a number: that many genes of the largest downsampled totals "
+                             "(the stand-in of SURVEY.md 8d)")
     parser.add_argument("--cpu-cells", type=int, default=0,
                         help="cells of the pile the CPU legs (--impl reference, cpu_baseline) time; 0 = --cells, the same pile "
                              "as the GPU arm (the path is O(cells^2): any other value is not a like-for-like baseline)")
@@ -57,13 +60,15 @@ def parse_args():
 
 
 def workload_name(args, cells):
-    return (f"pile k-NN graph: {cells} cells x {args.genes} genes synthetic UMIs, {args.features} feature genes "
-            f"(downsample+log-fraction+correlate+rank+balance+prune_per)")
+    features = ("feature genes selected as pipeline/select.py does" if args.features == "select" else
+                f"{args.features} feature genes of the largest totals")
+    return (f"pile k-NN graph: {cells} cells x {args.genes} genes synthetic UMIs, {features} "
+            f"(downsample+select+log-fraction+correlate+rank+balance+prune_per)")
 
 
 def config_of(args, cells, genes, k, samples, nnz):
     """The workload description both arms print (the driver compares them)."""
-    return {"workload": workload_name(args, cells), "cells": int(cells), "genes": int(genes), "feature_genes": int(args.features),
+    return {"workload": workload_name(args, cells), "cells": int(cells), "genes": int(genes), "feature_genes": args.features,
             "k": int(k), "downsample_samples": int(samples), "umis_nnz": int(nnz),
             "l2": "inputs larger than L2 (CSR pile 0.45 GB, similarity and rank matrices 1 GB each per step)"}
 
@@ -216,9 +221,11 @@ def run_reference_arm(args):
         "ms_per_step": 1000.0 * elapsed / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "impl": "reference",
         "config": step.config, "timing": "host wall clock", "piles_per_step": 1, "graph_nnz": int(step.graph.nnz),
+        "feature_genes_selected": int(timings.get("feature_genes_count", 0)),
         "cpu_baseline": dict(info, value=value, unit=UNIT),
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "stage_seconds_per_step": {name: seconds / max(args.steps, 1) for name, seconds in timings.items()},
+        "stage_seconds_per_step": {name: seconds / max(args.steps, 1) for name, seconds in timings.items()
+                                   if name != "feature_genes_count"},
     }
     emit(line)
 
@@ -282,7 +289,7 @@ def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
 
-    from metacells_b200 import pipeline, tools as tl
+    from metacells_b200 import pipeline, select, tools as tl
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -316,18 +323,36 @@ def run_gpu_arm(args):
               "indptr": torch.empty(cells + 1, dtype=torch.int32).pin_memory()}
     stream = torch.cuda.current_stream(device)
 
+    select_genes = args.features == "select"
+    selected = {"genes": None}  # the feature genes of the last pile (page-lockable, kept alive for the asynchronous copy)
+
     def hot_path(pile, k=k, meanwhile=None):
         """The path on an existing pile handle; returns the graph handle.  `meanwhile` runs on the host after the
         first (asynchronous) launches: the pipelined legs start the next pile's upload there."""
         library.call("mcb_pile_set_max_cell_total", pile, ctypes.c_uint64(max_cell_total))
+        if select_genes:  # the downsample kernel adds up the per-gene statistics of pipeline/select.py
+            library.call("mcb_pile_want_gene_statistics", pile, ctypes.c_float(select.SELECT_MIN_GENE_TOP3))
         library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
-        # feature genes: the largest downsampled totals (stand-in for pipeline/select.py), selected on the device
-        library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)
-        if meanwhile is not None:
-            meanwhile()
+        if select_genes:
+            if meanwhile is not None:
+                meanwhile()
+            view = pipeline.Pile._adopt(pile, (cells, genes))  # the handle stays ours
+            view.gene_top_threshold = float(select.SELECT_MIN_GENE_TOP3)
+            try:
+                chosen = np.flatnonzero(select.select_feature_genes(view)).astype("int32")
+            finally:
+                view._handle = None
+            selected["genes"] = chosen
+            genes_pointer, genes_count = p(chosen.ctypes.data), len(chosen)
+        else:
+            # the genes of the largest downsampled totals (the stand-in of SURVEY.md 8d), selected on the device
+            library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)
+            if meanwhile is not None:
+                meanwhile()
+            genes_pointer, genes_count = None, args.features
         graph = ctypes.c_void_p()
         outside = ctypes.c_int(0)
-        library.call("mcb_pile_knn_graph", pile, None, ctypes.c_int64(args.features),
+        library.call("mcb_pile_knn_graph", pile, genes_pointer, ctypes.c_int64(genes_count),
                      p(table.ctypes.data), ctypes.c_int64(len(table)), ctypes.c_float(np.float32(1 / 7)), ctypes.c_int(1),
                      ctypes.c_int64(k), ctypes.c_double(brf), ctypes.c_double(idf), ctypes.c_double(odf), ctypes.c_int64(mod),
                      ctypes.byref(outside), ctypes.byref(graph))
@@ -567,10 +592,11 @@ def run_gpu_arm(args):
                 "peak_source": hbm_source, "algorithmic_bytes_per_launch": algorithmic_bytes, "ms_per_launch": ms}
 
     umma_ms = per_launch_ms("correlate_umma")
-    flops = float(cells) * cells * args.features  # algorithmic: 2 * g * N (N - 1) / 2 ~= N^2 g
+    features_count = len(selected["genes"]) if select_genes else args.features
+    flops = float(cells) * cells * features_count  # algorithmic: 2 * g * N (N - 1) / 2 ~= N^2 g
     achieved = flops / (umma_ms * 1e-3) / 1e12 if umma_ms else None
     correlate_line = {"bound": "tensor", "kernel": "correlate_umma_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                      "frac": achieved / peak if achieved else None, "traffic": ncu_traffic("correlate_umma", cells, args.features),
+                      "frac": achieved / peak if achieved else None, "traffic": ncu_traffic("correlate_umma", cells, features_count),
                       "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_correlate_umma.txt",
                       "peak_source": peak_source, "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms,
                       "tf32_peak_measured": tf32,
@@ -580,7 +606,7 @@ def run_gpu_arm(args):
                       "ncu_tensor_pipe_source": "sm__pipe_tensor_cycles_active of profiles/r01_ncu_full_correlate_umma.txt"}
     # SURVEY 8d's algorithmic bytes: ranks read and write the whole square matrix; the downsample reads and writes the
     # pile's values and reads the row pointers; balance reads every rank once (count and fill passes are one stage).
-    rank_line = hbm_line("rank_matrix_bucket_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, args.features),
+    rank_line = hbm_line("rank_matrix_bucket_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, 2000),
                          "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_rank_matrix_bucket_kernel.txt")
     downsample_line = hbm_line("downsample_warp_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, None, None)
     balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells, None, None)
@@ -592,6 +618,7 @@ def run_gpu_arm(args):
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": resident_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_of(args, cells, genes, k, samples, umis.nnz), "graph_nnz": int(nnz), "piles_per_step": world,
+        "feature_genes_selected": int(features_count),
         "clocks": clocks,
         "host": {"cpus_near_gpu": len(gpu_cpus) if gpu_cpus else None, "cpus": len(launcher_cpus)},
         "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
@@ -604,8 +631,8 @@ def run_gpu_arm(args):
                         "pile (chunks on a copy stream) and the read of the previous graph (mcb_graph_read_start) under the "
                         "kernels of the current pile; worker_threads_ms_per_step = `worker_threads` host threads, each pile on its "
                         "thread's own stream, nothing prefetched.  unpipelined_ms_per_step: one pile at a time",
-                "h2d_bytes_per_step": int(umis.data.nbytes + umis.indices.nbytes + umis.indptr.nbytes + table.nbytes + 4 * args.features),
-                "d2h_bytes_per_step": int(nnz * 8 + (cells + 1) * 4 + genes * 4)},
+                "h2d_bytes_per_step": int(umis.data.nbytes + umis.indices.nbytes + umis.indptr.nbytes + table.nbytes + 4 * features_count),
+                "d2h_bytes_per_step": int(nnz * 8 + (cells + 1) * 4 + genes * (12 if select_genes else 4))},
         "gpu_launches": int(launches),
         "roofline": dominant,
         "roofline_kernels": [line for line in candidates if line is not dominant],

@@ -237,6 +237,28 @@ int mcb_pile_gene_totals(mcb_pile* pile, float* totals);
 int mcb_pile_top_genes(mcb_pile* pile, int64_t count, int32_t* genes_host);
 int64_t mcb_pile_top_genes_count(const mcb_pile* pile); /* the length of the list on the device (0: none yet) */
 
+/* The O(non-zeros) part of the feature-gene selection (pipeline/select.py:145-220 over tools/high.py:29-135, 246-303):
+ * per gene of the downsampled pile the total (tools/high.py:73 sum_per), the sum of squares (computation.py:1526-1546
+ * variance_per -> sum_squared_per) and the number of cells holding at least `min_top_value` UMIs of it (the
+ * `rank_per(..., rank=n_obs - topN - 1) >= min_gene_topN` test of tools/high.py:121-124 is "at least topN + 1 cells hold
+ * >= min_gene_topN": no dense [genes, cells] matrix is ranked).  Ask before mcb_pile_downsample: its kernel adds them up
+ * where it writes every count (one 64-bit integer add per non-zero); read after.  totals float32[genes] (exact below
+ * 2^24), squares uint64[genes] (exact), top_counts int32[genes].  At most 65535 cells. */
+int mcb_pile_want_gene_statistics(mcb_pile* pile, float min_top_value);
+int mcb_pile_gene_statistics(mcb_pile* pile, float* totals, uint64_t* squares, int32_t* top_counts);
+/* The non-zero values of `count` genes of the (downsampled) pile in cell order, values[g * cells + k], sizes[g] of them:
+ * the columns of the CSC matrix the reference sums (computation.py:1224-1268 on `layout="column_major"`).  For the few
+ * genes whose float32 sums pass 2^24, where the order of numpy's pairwise summation shows: the host re-sums them with
+ * numpy itself. */
+int mcb_pile_gene_columns(mcb_pile* pile, const int32_t* genes, int64_t count, float* values, int32_t* sizes);
+
+/* medians[i] = the median of values[i .. i + window) for i = 0 .. count - window (odd window <= 127; host arrays): the
+ * `rolling(window).median()` of sliding_window_function (computation.py:1836-1897) over the genes ordered by their mean
+ * expression, of which relative_variance_per subtracts the result (computation.py:1590-1595).  The median of an odd
+ * window is one of its elements, so no arithmetic is involved; a window holding a NaN or an infinity yields NaN, as pandas'
+ * rolling median does (it takes infinities for missing values). */
+int mcb_host_sliding_median_f32(const float* values, int64_t count, int64_t window, float* medians);
+
 /* direct.py:242-249 -> computation.py:679-741 (log_data): the dense float32 [cells, features] operand of the similarity,
  * dense_host[c, f] = log_table[count of gene feature_genes[f] in cell c] (log_table[c] = np.log2(float32(c) +
  * regularization), made by numpy on the host, so the result is bit-identical to the reference's `data += 1/7;

@@ -14,7 +14,8 @@ namespace mcb {
 int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
-                           cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr);
+                           cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr,
+                           unsigned long long* column_stats = nullptr, float top_threshold = 0.0f);
 int column_totals_launch(const float* data, const int32_t* indices, int64_t nnz, int64_t columns, float* totals,
                          cudaStream_t stream);
 int log_fraction_dense_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t rows,
@@ -42,6 +43,10 @@ struct mcb_pile {
     Scratch downsampled;  // same sparsity structure as `data`
     bool has_downsampled = false;
     Scratch gene_totals;  // float32[genes]: per-gene totals of `downsampled`, added up by the downsample kernels
+    // uint64[genes], when mcb_pile_want_gene_statistics asked for them: sum of squares << 16 | cells >= gene_top_threshold
+    Scratch gene_stats;
+    bool want_gene_stats = false;
+    float gene_top_threshold = 0.0f;
     Scratch top_genes;    // int32[top_genes_count] ascending, set by mcb_pile_top_genes
     int64_t top_genes_count = 0;
     // A host pile is uploaded in row chunks on its own stream, so that the downsampling of the first chunks runs
@@ -215,10 +220,22 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
         MCB_TRY(pile->gene_totals.alloc((size_t)pile->genes * sizeof(float), pile->stream));
     MCB_CUDA(cudaMemsetAsync(pile->gene_totals.ptr, 0, (size_t)pile->genes * sizeof(float), pile->stream));
     float* totals = pile->gene_totals.as<float>();
+    unsigned long long* stats = nullptr;
+    if (pile->want_gene_stats) {
+        // a downsampled cell holds at most `samples` UMIs of a gene: the packed sum of squares keeps 48 bits
+        MCB_REQUIRE((long double)pile->cells * samples * samples < 281474976710656.0L,
+                    "pile: gene statistics of %lld cells downsampled to %d UMIs would overflow 48 bits", (long long)pile->cells, samples);
+        if (!pile->gene_stats.ptr)
+            MCB_TRY(pile->gene_stats.alloc((size_t)pile->genes * sizeof(unsigned long long), pile->stream));
+        MCB_CUDA(cudaMemsetAsync(pile->gene_stats.ptr, 0, (size_t)pile->genes * sizeof(unsigned long long), pile->stream));
+        stats = pile->gene_stats.as<unsigned long long>();
+    }
+    const float top_threshold = pile->gene_top_threshold;
     if (pile->chunk_ready.empty()) {
         MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples, 0, pile->cells, 0,
                                        pile->widest, random_seed, 1, pile->max_row_total,
-                                       pile->max_row_total ? pile->status.as<int>() : nullptr, pile->stream, pile->indices, totals));
+                                       pile->max_row_total ? pile->status.as<int>() : nullptr, pile->stream, pile->indices, totals,
+                                       stats, top_threshold));
     } else {
         // Every chunk as soon as it has arrived; with the largest cell total known nothing here waits on the device.
         // Chunks that have arrived already (a pile uploaded under the previous pile's kernels) go in one launch: a
@@ -231,7 +248,7 @@ int mcb_pile_downsample(mcb_pile* pile, int32_t samples, uint64_t random_seed) {
             MCB_TRY(downsample_rows_launch(pile->data, pile->downsampled.as<float>(), pile->indptr, nullptr, samples,
                                            pile->chunk_rows[c], pile->chunk_rows[last + 1], 0, pile->widest, random_seed, 1,
                                            pile->max_row_total, pile->max_row_total ? pile->status.as<int>() : nullptr,
-                                           pile->stream, pile->indices, totals));
+                                           pile->stream, pile->indices, totals, stats, top_threshold));
             c = last + 1;
         }
     }
@@ -517,6 +534,68 @@ __global__ void __launch_bounds__(256) dense_to_csr_kernel(const float* __restri
     }
 }
 
+// values[g * rows + row] = the (downsampled) count of gene genes[g] in cell `row`, 0 when the cell does not hold it: one
+// thread per (gene, cell), a binary search in the cell's sorted gene indices.  The host drops the zeros: what is left is the
+// column of the CSC matrix without explicit zeros (computation.py:892-899 eliminates them), in cell order.
+__global__ void __launch_bounds__(256) gene_columns_kernel(const float* __restrict__ data, const int32_t* __restrict__ indices,
+                                                          const int32_t* __restrict__ indptr, int64_t rows,
+                                                          const int32_t* __restrict__ genes, float* __restrict__ values) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    const int32_t gene = genes[blockIdx.y];
+    const int last = indptr[row + 1];
+    int low = indptr[row], high = last;  // the first element with index >= gene
+    while (low < high) {
+        const int middle = (low + high) >> 1;
+        if (indices[middle] < gene)
+            low = middle + 1;
+        else
+            high = middle;
+    }
+    values[(int64_t)blockIdx.y * rows + row] = (low < last && indices[low] == gene) ? data[low] : 0.0f;
+}
+
+// out[i] = the median of values[i .. i + window) for an odd window: the element with at most window / 2 smaller and more
+// than window / 2 not larger elements.  One warp per output, the window in registers (window <= 128).
+__global__ void __launch_bounds__(256) sliding_median_kernel(const float* __restrict__ values, int64_t outputs, int window,
+                                                            float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= outputs) return;
+    float mine[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) mine[u] = lane + 32 * u < window ? values[i + lane + 32 * u] : 0.0f;
+    // pandas' rolling functions take infinities for missing values (window._prep_values) and a window with a missing value
+    // has no median: NaN, as the reference gets (a gene that is constant over the cells has log2(0) = -inf)
+    bool finite = true;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) finite = finite && (lane + 32 * u >= window || isfinite(mine[u]));
+    if (!__all_sync(0xffffffffu, finite)) {
+        if (lane == 0) out[i] = __int_as_float(0x7fc00000);
+        return;
+    }
+    const int half = window / 2;
+    float median = 0.0f;
+    bool found = false;
+    for (int j = 0; j < window; ++j) {
+        const float candidate = __shfl_sync(0xffffffffu, mine[j >> 5], j & 31);
+        int smaller = 0, not_larger = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (lane + 32 * u < window) {
+                smaller += mine[u] < candidate ? 1 : 0;
+                not_larger += mine[u] <= candidate ? 1 : 0;
+            }
+        smaller = warp_reduce_sum(smaller);
+        not_larger = warp_reduce_sum(not_larger);
+        if (!found && smaller <= half && half < not_larger) {
+            median = candidate;
+            found = true;
+        }
+    }
+    if (lane == 0) out[i] = median;
+}
+
 int check_atlas_indptr(const int64_t* indptr, int64_t cells) {
     MCB_REQUIRE(indptr[0] == 0, "atlas: indptr[0] must be 0");
     for (int64_t c = 0; c < cells; ++c)
@@ -698,6 +777,81 @@ int mcb_pile_create_dense_dev(const float* dense, int64_t cells, int64_t genes, 
     pile->indices = pile->own_indices.as<int32_t>();
     pile->indptr = pile->own_indptr.as<int32_t>();
     *out = pile.release();
+    return MCB_OK;
+}
+
+int mcb_host_sliding_median_f32(const float* values, int64_t count, int64_t window, float* medians) {
+    MCB_REQUIRE(values && medians && window >= 1 && (window & 1) == 1 && window <= 127 && count >= window,
+                "sliding_median: needs an odd window of at most 127 and at least one whole window");
+    const int64_t outputs = count - window + 1;
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    Scratch d_values, d_out;
+    MCB_TRY(d_values.alloc((size_t)count * sizeof(float), stream));
+    MCB_TRY(d_out.alloc((size_t)outputs * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_values.ptr, values, (size_t)count * sizeof(float), cudaMemcpyHostToDevice, stream));
+    MCB_PROFILED("sliding_median", stream,
+                 sliding_median_kernel<<<(unsigned)ceil_div(outputs, 8), 256, 0, stream>>>(d_values.as<float>(), outputs, (int)window,
+                                                                                         d_out.as<float>()));
+    MCB_LAUNCH_CHECK();
+    MCB_TRY(copy_to_host(medians, d_out.ptr, (size_t)outputs * sizeof(float), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_pile_want_gene_statistics(mcb_pile* pile, float min_top_value) {
+    MCB_REQUIRE(pile != nullptr, "pile: null handle");
+    MCB_REQUIRE(!pile->has_downsampled, "pile: ask for the gene statistics before mcb_pile_downsample");
+    MCB_REQUIRE(pile->cells < 65536, "pile: gene statistics count cells in 16 bits (at most 65535 cells)");
+    pile->want_gene_stats = true;
+    pile->gene_top_threshold = min_top_value;
+    return MCB_OK;
+}
+
+int mcb_pile_gene_statistics(mcb_pile* pile, float* totals, uint64_t* squares, int32_t* top_counts) {
+    MCB_REQUIRE(pile != nullptr && totals && squares && top_counts, "pile: null argument");
+    MCB_REQUIRE(pile->has_downsampled && pile->gene_stats.ptr != nullptr,
+                "pile: no gene statistics (mcb_pile_want_gene_statistics, then mcb_pile_downsample)");
+    MCB_TRY(check_status(pile));
+    MCB_TRY(copy_to_host(totals, pile->gene_totals.ptr, (size_t)pile->genes * sizeof(float), pile->stream));
+    MCB_TRY(copy_to_host(squares, pile->gene_stats.ptr, (size_t)pile->genes * sizeof(uint64_t), pile->stream));
+    MCB_CUDA(cudaStreamSynchronize(pile->stream));
+    for (int64_t gene = 0; gene < pile->genes; ++gene) {
+        top_counts[gene] = (int32_t)(squares[gene] & 0xffffu);
+        squares[gene] >>= 16;
+    }
+    return MCB_OK;
+}
+
+int mcb_pile_gene_columns(mcb_pile* pile, const int32_t* genes, int64_t count, float* values, int32_t* sizes) {
+    MCB_REQUIRE(pile != nullptr && genes && values && sizes && count >= 0, "pile: bad arguments");
+    if (count == 0)
+        return MCB_OK;
+    for (int64_t g = 0; g < count; ++g)
+        MCB_REQUIRE(genes[g] >= 0 && genes[g] < pile->genes, "pile: gene %d is out of range", genes[g]);
+    cudaStream_t stream = pile->stream;
+    MCB_TRY(wait_for_upload(pile));
+    Scratch d_genes, d_values;
+    MCB_REQUIRE(count <= 65535, "pile: at most 65535 gene columns per call");
+    MCB_TRY(d_genes.alloc((size_t)count * sizeof(int32_t), stream));
+    MCB_TRY(d_values.alloc((size_t)count * pile->cells * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_genes.ptr, genes, (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    const float* source = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
+    const dim3 grid((unsigned)ceil_div(pile->cells, 256), (unsigned)count);
+    MCB_PROFILED("gene_columns", stream,
+                 gene_columns_kernel<<<grid, 256, 0, stream>>>(source, pile->indices, pile->indptr, pile->cells,
+                                                               d_genes.as<int32_t>(), d_values.as<float>()));
+    MCB_LAUNCH_CHECK();
+    MCB_TRY(copy_to_host(values, d_values.ptr, (size_t)count * pile->cells * sizeof(float), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    for (int64_t g = 0; g < count; ++g) {  // drop the zeros, keep the order
+        float* column = values + g * pile->cells;
+        int32_t kept = 0;
+        for (int64_t row = 0; row < pile->cells; ++row)
+            if (column[row] != 0.0f) column[kept++] = column[row];
+        std::fill(column + kept, column + pile->cells, 0.0f);
+        sizes[g] = kept;
+    }
     return MCB_OK;
 }
 

@@ -50,7 +50,20 @@ struct DownsampleParams {
     int* error_flag;
     const int32_t* indices;  // with column_totals: the column of every element of a compressed matrix
     float* column_totals;    // nullable: += every output value (integers far below 2^24: exact in any order)
+    // nullable, with column_totals: per column += value^2 << 16 | (value >= top_threshold), one 64-bit integer add per
+    // non-zero output: the exact sum of squares (below 2^48) and the count of elements at or above the threshold (below
+    // 2^16 rows) that the feature-gene statistics of pipeline/select.py start from
+    unsigned long long* column_stats;
+    float top_threshold;
 };
+
+__device__ __forceinline__ void add_column_statistics(const DownsampleParams& p, int32_t column, float value) {
+    atomicAdd(&p.column_totals[column], value);
+    if (p.column_stats) {
+        const unsigned long long count = (unsigned long long)value;
+        atomicAdd(&p.column_stats[column], (count * count) << 16 | (value >= p.top_threshold ? 1ull : 0ull));
+    }
+}
 
 __global__ void __launch_bounds__(DS_THREADS) downsample_kernel(DownsampleParams p) {
     extern __shared__ uint32_t smem[];
@@ -290,7 +303,7 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
                 const float kept = (double)samples < (double)in[0] ? (float)samples : in[0];
                 out[0] = kept;
                 if (columns_of_row && kept != 0.0f)
-                    atomicAdd(&p.column_totals[columns_of_row[0]], kept);
+                    add_column_statistics(p, columns_of_row[0], kept);
             }
             continue;
         }
@@ -312,7 +325,7 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
             if (columns_of_row)
                 for (int i = lane; i < n; i += 32)
                     if (in[i] != 0.0f)
-                        atomicAdd(&p.column_totals[columns_of_row[i]], in[i]);
+                        add_column_statistics(p, columns_of_row[i], in[i]);
             continue;
         }
         const int words = (int)((total64 + 31) >> 5);
@@ -444,7 +457,7 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
             if (i < n) {
                 out[i] = (float)drawn;
                 if (columns_of_row && drawn)
-                    atomicAdd(&p.column_totals[columns_of_row[i]], (float)drawn);
+                    add_column_statistics(p, columns_of_row[i], (float)drawn);
             }
         }
         __syncwarp();
@@ -459,7 +472,7 @@ __global__ void __launch_bounds__(256) add_column_totals_kernel(DownsampleParams
         return;
     for (int64_t e = p.indptr[row] + lane; e < p.indptr[row + 1]; e += 32)
         if (p.output[e] != 0.0f)
-            atomicAdd(&p.column_totals[p.indices[e]], p.output[e]);
+            add_column_statistics(p, p.indices[e], p.output[e]);
 }
 
 }  // namespace
@@ -469,7 +482,8 @@ __global__ void __launch_bounds__(256) add_column_totals_kernel(DownsampleParams
 int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
-                           cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr);
+                           cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr,
+                           unsigned long long* column_stats = nullptr, float top_threshold = 0.0f);
 
 int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                       int32_t samples_all, int64_t rows, int64_t columns, int64_t max_row_size, uint64_t seed,
@@ -481,7 +495,8 @@ int downsample_launch(const float* input, float* output, const int32_t* indptr, 
 int downsample_rows_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
-                           cudaStream_t stream, const int32_t* indices, float* column_totals) {
+                           cudaStream_t stream, const int32_t* indices, float* column_totals, unsigned long long* column_stats,
+                           float top_threshold) {
     const int64_t rows = last_row - first_row;
     if (rows <= 0)
         return MCB_OK;
@@ -501,6 +516,9 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
                 "downsample: column totals need a compressed matrix");
     p.indices = indices;
     p.column_totals = column_totals;
+    MCB_REQUIRE(column_stats == nullptr || column_totals != nullptr, "downsample: column statistics come with the column totals");
+    p.column_stats = column_stats;
+    p.top_threshold = top_threshold;
 
     Scratch workspace, flag, counters;
     MCB_TRY(flag.alloc(sizeof(int), stream));

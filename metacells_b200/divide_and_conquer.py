@@ -248,7 +248,7 @@ def metacells_of_phase(cells_count: int, phase: List[dict]) -> Tuple[np.ndarray,
     return metacell_of_cells, count
 
 
-def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 0, world_size: int = 1, features: int = 2000,
+def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 0, world_size: int = 1, features=2000,
                         random_seed: int = 123456, candidates: bool = True, workers: int = 2,
                         masses: Optional[np.ndarray] = None, bounds=None, k_arguments: Optional[dict] = None,
                         times: Optional[dict] = None) -> List[dict]:
@@ -277,9 +277,9 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
         samples = _samples_of(cell_umis[rows])
         k = pipeline.knn_k_of_pile(len(rows), masses[rows], **k_arguments)
         with atlas.pile(rows) as handle:
+            pipeline._start_selection(handle, features)
             handle.downsample(samples, random_seed)
-            handle.select_top_genes(min(features, atlas.shape[1] - 1))
-            return pile, handle.knn_graph(None, k=min(k, len(rows) - 1))
+            return pile, handle.knn_graph(pipeline._feature_genes_of(handle, features), k=min(k, len(rows) - 1))
 
     results: Dict[int, dict] = {}
     for pile in [pile for pile in mine if sizes[pile] < 3]:  # too small for a graph: one community
@@ -344,10 +344,10 @@ def group_metacells_into_piles(atlas: Atlas, metacell_of_cells: np.ndarray, meta
             block = sums if len(rows) == metacells_count else sums[torch.from_numpy(rows).to(sums.device)].contiguous()
             with pipeline.Pile.from_dense_device(block.data_ptr(), len(rows), atlas.shape[1]) as pile:
                 pile.set_max_cell_total(float(metacell_umis[rows].max()))
+                pipeline._start_selection(pile, features)
                 pile.downsample(_samples_of(metacell_umis[rows]), random_seed)
-                pile.select_top_genes(min(features, atlas.shape[1] - 1))
                 k = min(pipeline.knn_k_of_pile(len(rows), metacell_sizes[rows], **k_arguments), len(rows) - 1)
-                graphs.append((rows, pile.knn_graph(None, k=k)))
+                graphs.append((rows, pile.knn_graph(pipeline._feature_genes_of(pile, features), k=k)))
             del block
 
         def seed_partition(entry):

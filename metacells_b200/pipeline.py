@@ -112,6 +112,7 @@ class Pile:
         check(function(_ptr(self._data), _ptr(self._indices), _ptr(self._indptr), ctypes.c_int64(umis.shape[0]),
                        ctypes.c_int64(umis.shape[1]), ctypes.byref(self._handle)))
         self.samples: Optional[int] = None
+        self.gene_top_threshold: Optional[float] = None
         if max_cell_total is not None:
             function = lib().mcb_pile_set_max_cell_total
             function.restype = ctypes.c_int
@@ -126,6 +127,7 @@ class Pile:
         pile._pinned = []
         pile._handle = handle
         pile.samples = None
+        pile.gene_top_threshold = None
         return pile
 
     @classmethod
@@ -203,6 +205,35 @@ class Pile:
         check(function(self._handle, _ptr(data)))
         return sp.csr_matrix((data, self._indices.copy(), self._indptr.copy()), shape=self.shape)
 
+    def want_gene_statistics(self, min_top_value: float) -> None:
+        """Before ``downsample``: have its kernel add up the per-gene statistics the feature-gene selection starts from
+        (``mcb_pile_want_gene_statistics``); ``min_top_value`` is ``min_gene_top3`` of pipeline/select.py."""
+        function = lib().mcb_pile_want_gene_statistics
+        function.restype = ctypes.c_int
+        check(function(self._handle, ctypes.c_float(float(min_top_value))))
+        self.gene_top_threshold = float(min_top_value)
+
+    def gene_statistics(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+        """``(totals float32, sums of squares uint64, cells at or above the top value int32)`` per gene of the downsampled
+        pile (``mcb_pile_gene_statistics``)."""
+        genes = self.shape[1]
+        totals, squares, top = np.empty(genes, dtype="float32"), np.empty(genes, dtype="uint64"), np.empty(genes, dtype="int32")
+        function = lib().mcb_pile_gene_statistics
+        function.restype = ctypes.c_int
+        check(function(self._handle, _ptr(totals), _ptr(squares), _ptr(top)))
+        return totals, squares, top
+
+    def gene_columns(self, genes: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+        """The non-zero values of ``genes`` in cell order, ``(values float32 [len(genes), cells], sizes int32)``
+        (``mcb_pile_gene_columns``): row g holds ``sizes[g]`` values."""
+        genes = np.ascontiguousarray(genes, dtype="int32")
+        values = np.zeros((len(genes), self.shape[0]), dtype="float32")
+        sizes = np.zeros(len(genes), dtype="int32")
+        function = lib().mcb_pile_gene_columns
+        function.restype = ctypes.c_int
+        check(function(self._handle, _ptr(genes), ctypes.c_int64(len(genes)), _ptr(values), _ptr(sizes)))
+        return values, sizes
+
     def gene_totals(self) -> np.ndarray:
         totals = np.empty(self.shape[1], dtype="float32")
         function = lib().mcb_pile_gene_totals
@@ -277,7 +308,28 @@ class Pile:
         return graph
 
 
-def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature_genes: Optional[np.ndarray] = None,
+def _start_selection(pile: "Pile", features) -> None:
+    """Before ``pile.downsample``: the reference's gene selection needs the per-gene statistics the kernel adds up."""
+    if features == "select":
+        from . import select
+
+        pile.want_gene_statistics(select.SELECT_MIN_GENE_TOP3)
+
+
+def _feature_genes_of(pile: "Pile", features) -> Optional[np.ndarray]:
+    """The feature genes of a downsampled pile.  ``features == "select"``: ``extract_selected_data`` of pipeline/select.py
+    (``select.select_feature_genes``: high top-3, high total, high relative variance), returned as gene indices for
+    ``knn_graph``; an integer: the stand-in of SURVEY.md 8d, that many genes of the largest totals, selected on the device
+    (the list stays there: ``knn_graph(None, ...)``)."""
+    if features == "select":
+        from . import select
+
+        return np.flatnonzero(select.select_feature_genes(pile)).astype("int32")
+    pile.select_top_genes(min(int(features), pile.shape[1] - 1))
+    return None
+
+
+def compute_pile_knn_graph(umis: sp.csr_matrix, *, features=2000, feature_genes: Optional[np.ndarray] = None,
                            k: Optional[int] = None, random_seed: int = 123456, upload_turn=None) -> Tuple[sp.csr_matrix, dict]:
     """The k-NN graph part of ``compute_direct_metacells`` for one pile: downsample (tools/downsample.py),
     feature genes, log-fraction, ``abs_pearson`` similarity, ``compute_obs_obs_knn_graph``.
@@ -294,10 +346,14 @@ def compute_pile_knn_graph(umis: sp.csr_matrix, *, features: int = 2000, feature
             pile = Pile(umis, max_cell_total=float(cell_umis.max()))
             pile.wait_upload()
     with pile:
+        if feature_genes is None:
+            _start_selection(pile, features)
         pile.downsample(samples, random_seed)
-        selected_on_device = feature_genes is None
-        if selected_on_device:
-            feature_genes = pile.select_top_genes(features)
+        selected_on_device = feature_genes is None and features != "select"
+        if feature_genes is None:
+            feature_genes = _feature_genes_of(pile, features)
+            if feature_genes is None:
+                feature_genes = pile.select_top_genes(features)
         graph = pile.knn_graph(None if selected_on_device else feature_genes, k=k)
         try:
             weights, pruned = graph.to_scipy()
@@ -434,7 +490,7 @@ def compute_piles_seed_partitions(piles, *, workers: Optional[int] = None, **arg
     return list(pool.map(lambda pile: compute_pile_seed_partition(pile[0], pile[1], **arguments), piles))
 
 
-def pile_knn_graph_on_device(umis: sp.csr_matrix, *, features: int = 2000, random_seed: int = 123456):
+def pile_knn_graph_on_device(umis: sp.csr_matrix, *, features=2000, random_seed: int = 123456):
     """``compute_pile_knn_graph`` that leaves the graph on the device: ``(KnnGraph, cell_umis)``; the caller closes the
     graph."""
     cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
@@ -442,9 +498,9 @@ def pile_knn_graph_on_device(umis: sp.csr_matrix, *, features: int = 2000, rando
                             np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
     k = knn_k_of_pile(umis.shape[0], cell_umis)
     with Pile(umis, max_cell_total=float(cell_umis.max(initial=0))) as pile:
+        _start_selection(pile, features)
         pile.downsample(samples, random_seed)
-        pile.select_top_genes(features)
-        return pile.knn_graph(None, k=k), cell_umis
+        return pile.knn_graph(_feature_genes_of(pile, features), k=k), cell_umis
 
 
 def compute_piles_candidates(piles: Iterable[sp.csr_matrix], *, features: int = 2000, random_seed: int = 123456,

@@ -414,7 +414,7 @@ def load_ref():
 # ---------------------------------------------------------------------------------------------
 
 
-def cpu_pile_knn_graph(umis: sp.csr_matrix, features: int, k: int, seed: int, ref=None, timings: Optional[dict] = None):
+def cpu_pile_knn_graph(umis: sp.csr_matrix, features, k: int, seed: int, ref=None, timings: Optional[dict] = None):
     """downsample -> feature genes -> log-fraction -> abs_pearson similarity -> balanced k-NN graph,
     sequenced as pipeline/direct.py:214-283 does.  With ``ref`` (oracle/_ref, the unmodified reference
     natives, multi-threaded) every native call goes to the reference; otherwise to the C port of
@@ -437,8 +437,19 @@ def cpu_pile_knn_graph(umis: sp.csr_matrix, features: int, k: int, seed: int, re
     lap("downsample", start)
 
     start = time.perf_counter()
-    gene_totals = np.asarray(down.sum(axis=0)).reshape(-1)
-    genes = np.sort(np.argsort(-gene_totals, kind="stable")[:features])
+    if isinstance(features, str):  # "select": extract_selected_data of pipeline/select.py:145-220
+        assert features == "select"
+        stored = sp.csr_matrix(down, copy=True)
+        stored.eliminate_zeros()  # computation.py:892-899
+        genes = np.flatnonzero(select_feature_genes(stored, ref=ref))
+        del stored
+        lap("select_genes", start)
+        start = time.perf_counter()
+    else:  # the stand-in of SURVEY.md 8d: the genes of the largest downsampled totals
+        gene_totals = np.asarray(down.sum(axis=0)).reshape(-1)
+        genes = np.sort(np.argsort(-gene_totals, kind="stable")[:features])
+    if timings is not None:
+        timings["feature_genes_count"] = len(genes)
     dense = log_fraction(down[:, genes].toarray())
     lap("log_fraction", start)
 

@@ -5,13 +5,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np, torch
 import bench
-from metacells_b200 import pipeline, tools as tl
+from metacells_b200 import pipeline, select, tools as tl
 
 parser = argparse.ArgumentParser()
 parser.add_argument("--steps", type=int, default=3)
 parser.add_argument("--cells", type=int, default=16000)
 parser.add_argument("--genes", type=int, default=27000)
-parser.add_argument("--features", type=int, default=2000)
+parser.add_argument("--features", default="select", type=lambda t: t if t == "select" else int(t))
 args = parser.parse_args()
 library = bench.Library()
 umis, samples, k = bench.make_pile(args.cells, args.genes, bench.SEED)
@@ -25,10 +25,20 @@ for step in range(args.steps):
     library.call("mcb_pile_create_dev", p(resident["data"].data_ptr()), p(resident["indices"].data_ptr()), p(resident["indptr"].data_ptr()),
                  ctypes.c_int64(args.cells), ctypes.c_int64(args.genes), p(stream.cuda_stream), ctypes.byref(pile))
     library.call("mcb_pile_set_max_cell_total", pile, ctypes.c_uint64(bench.make_pile.max_cell_total))
+    if args.features == "select":
+        library.call("mcb_pile_want_gene_statistics", pile, ctypes.c_float(select.SELECT_MIN_GENE_TOP3))
     library.call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(bench.SEED))
-    library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)
+    if args.features == "select":
+        view = pipeline.Pile._adopt(pile, (args.cells, args.genes))
+        view.gene_top_threshold = float(select.SELECT_MIN_GENE_TOP3)
+        chosen = np.flatnonzero(select.select_feature_genes(view)).astype("int32")
+        view._handle = None
+        genes_pointer, genes_count = p(chosen.ctypes.data), len(chosen)
+    else:
+        library.call("mcb_pile_top_genes", pile, ctypes.c_int64(args.features), None)
+        genes_pointer, genes_count = None, args.features
     graph = ctypes.c_void_p()
-    library.call("mcb_pile_knn_graph", pile, None, ctypes.c_int64(args.features), p(table.ctypes.data), ctypes.c_int64(len(table)),
+    library.call("mcb_pile_knn_graph", pile, genes_pointer, ctypes.c_int64(genes_count), p(table.ctypes.data), ctypes.c_int64(len(table)),
                  ctypes.c_float(np.float32(1 / 7)), ctypes.c_int(1), ctypes.c_int64(k), ctypes.c_double(tl.KNN_BALANCED_RANKS_FACTOR),
                  ctypes.c_double(tl.KNN_INCOMING_DEGREE_FACTOR), ctypes.c_double(tl.KNN_OUTGOING_DEGREE_FACTOR),
                  ctypes.c_int64(tl.KNN_MIN_OUTGOING_DEGREE), None, ctypes.byref(graph))

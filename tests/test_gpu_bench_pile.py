@@ -124,10 +124,11 @@ def test_bench_pile_graph_matches_oracle_and_digest(bench_pile):
     assert digest == bench.graph_digest(expected_weights.data, expected_weights.indices, expected_weights.indptr)
     key = f"{CELLS}x{GENES}x{FEATURES}@{SEED}"
     if os.environ.get("MCB_WRITE_GOLDEN"):
-        golden = json.load(open(GOLDEN)) if os.path.exists(GOLDEN) else {}
+        written = os.path.join(os.path.dirname(GOLDEN), "..", "..", "gpurun_out", "bench_pile.json")
+        golden = json.load(open(written)) if os.path.exists(written) else (json.load(open(GOLDEN)) if os.path.exists(GOLDEN) else {})
         golden[key] = digest
-        os.makedirs(os.path.join(os.path.dirname(GOLDEN), "..", "..", "gpurun_out"), exist_ok=True)
-        with open(os.path.join(os.path.dirname(GOLDEN), "..", "..", "gpurun_out", "bench_pile.json"), "w") as handle:
+        os.makedirs(os.path.dirname(written), exist_ok=True)
+        with open(written, "w") as handle:
             json.dump(golden, handle, indent=1)
         return
     with open(GOLDEN) as handle:
@@ -311,3 +312,79 @@ def test_bench_pile_against_reference_pipeline(bench_pile, ref):
     print(f"bench pile vs the reference pipeline: {len(only_mine)} edges only here, {len(only_theirs)} only in the reference of "
           f"{len(their_keys)}, Jaccard {jaccard:.6f}; differing edges without a similarity within 2e-5 in either row: {far}")
     assert jaccard >= 0.97
+
+
+def test_bench_pile_with_selected_genes(ref):
+    """bench.py's default path (`--features select`): the same entry points with the feature genes of pipeline/select.py.
+    Genes `==` the oracle's selection (scipy sums + the reference's rank_rows on the dense [genes, cells] matrix), graph `==`
+    oracle.knn_graph on the similarity of those genes, digest pinned for bench.py."""
+    import torch
+
+    import bench
+    from metacells_b200 import _lib, pipeline, select, tools as tl
+
+    library = _lib.lib()
+
+    def call(name, *arguments):
+        function = getattr(library, name)
+        function.restype = ctypes.c_int
+        _lib.check(function(*arguments))
+
+    umis, samples, k = bench.make_pile(CELLS, GENES, SEED)
+    table = pipeline.log_fraction_table(samples)
+    pile = ctypes.c_void_p()
+    call("mcb_pile_create_host", _p(umis.data), _p(umis.indices), _p(umis.indptr), ctypes.c_int64(CELLS), ctypes.c_int64(GENES),
+         ctypes.byref(pile))
+    try:
+        call("mcb_pile_set_max_cell_total", pile, ctypes.c_uint64(bench.make_pile.max_cell_total))
+        call("mcb_pile_want_gene_statistics", pile, ctypes.c_float(select.SELECT_MIN_GENE_TOP3))
+        call("mcb_pile_downsample", pile, ctypes.c_int32(samples), ctypes.c_uint64(SEED))
+        view = pipeline.Pile._adopt(pile, (CELLS, GENES))
+        view.gene_top_threshold = float(select.SELECT_MIN_GENE_TOP3)
+        try:
+            genes = np.flatnonzero(select.select_feature_genes(view)).astype("int32")
+        finally:
+            view._handle = None
+        data = np.empty(umis.nnz, dtype="float32")
+        call("mcb_pile_read_downsampled", pile, _p(data))
+        stored = sp.csr_matrix((data, umis.indices, umis.indptr), shape=umis.shape)
+        stored.eliminate_zeros()
+        expected_genes = np.flatnonzero(oracle.select_feature_genes(stored, ref=ref)).astype("int32")
+        del stored
+        print(f"bench pile: {len(genes)} feature genes selected")
+        assert np.array_equal(genes, expected_genes)
+        similarity = torch.empty((CELLS, CELLS), dtype=torch.float32, device="cuda")
+        call("mcb_pile_similarity", pile, _p(genes), ctypes.c_int64(len(genes)), _p(table), ctypes.c_int64(len(table)),
+             ctypes.c_float(np.float32(1 / 7)), ctypes.c_int(1), ctypes.c_void_p(similarity.data_ptr()), None)
+        torch.cuda.synchronize()
+        host_similarity = similarity.cpu().numpy()
+        del similarity
+        graph = ctypes.c_void_p()
+        call("mcb_pile_knn_graph", pile, _p(genes), ctypes.c_int64(len(genes)), _p(table), ctypes.c_int64(len(table)),
+             ctypes.c_float(np.float32(1 / 7)), ctypes.c_int(1), ctypes.c_int64(k), ctypes.c_double(tl.KNN_BALANCED_RANKS_FACTOR),
+             ctypes.c_double(tl.KNN_INCOMING_DEGREE_FACTOR), ctypes.c_double(tl.KNN_OUTGOING_DEGREE_FACTOR),
+             ctypes.c_int64(tl.KNN_MIN_OUTGOING_DEGREE), None, ctypes.byref(graph))
+        handle = tl.KnnGraph(graph)
+        try:
+            weights, pruned = handle.to_scipy()
+        finally:
+            handle.close()
+    finally:
+        library.mcb_pile_free(pile)
+    expected_weights, expected_pruned, _, _ = oracle.knn_graph(host_similarity, k)
+    for mine, theirs in ((pruned, expected_pruned), (weights, expected_weights)):
+        assert np.array_equal(mine.indptr, theirs.indptr) and np.array_equal(mine.indices, theirs.indices)
+        assert np.array_equal(mine.data, theirs.data)
+    digest = bench.graph_digest(weights.data, weights.indices, weights.indptr)
+    key = f"{CELLS}x{GENES}xselect@{SEED}"
+    print(f"bench pile (selected genes): graph sha256 {digest}")
+    if os.environ.get("MCB_WRITE_GOLDEN"):
+        written = os.path.join(os.path.dirname(GOLDEN), "..", "..", "gpurun_out", "bench_pile.json")
+        golden = json.load(open(written)) if os.path.exists(written) else json.load(open(GOLDEN))
+        golden[key] = digest
+        os.makedirs(os.path.dirname(written), exist_ok=True)
+        with open(written, "w") as handle:
+            json.dump(golden, handle, indent=1)
+        return
+    with open(GOLDEN) as handle:
+        assert json.load(handle).get(key) == digest, "the digest of the bench pile's graph (selected genes) is not the pinned one"
