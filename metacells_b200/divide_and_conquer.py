@@ -344,10 +344,14 @@ def group_metacells_into_piles(atlas: Atlas, metacell_of_cells: np.ndarray, meta
             block = sums if len(rows) == metacells_count else sums[torch.from_numpy(rows).to(sums.device)].contiguous()
             with pipeline.Pile.from_dense_device(block.data_ptr(), len(rows), atlas.shape[1]) as pile:
                 pile.set_max_cell_total(float(metacell_umis[rows].max()))
-                pipeline._start_selection(pile, features)
-                pile.downsample(_samples_of(metacell_umis[rows]), random_seed)
+                samples = _samples_of(metacell_umis[rows])
+                chosen = features
+                if chosen == "select" and len(rows) * samples * samples >= 1 << 48:
+                    chosen = 2000  # the per-gene sums of squares of so deep a pile pass the 48 bits the kernel keeps
+                pipeline._start_selection(pile, chosen)
+                pile.downsample(samples, random_seed)
                 k = min(pipeline.knn_k_of_pile(len(rows), metacell_sizes[rows], **k_arguments), len(rows) - 1)
-                graphs.append((rows, pile.knn_graph(pipeline._feature_genes_of(pile, features), k=k)))
+                graphs.append((rows, pile.knn_graph(pipeline._feature_genes_of(pile, chosen), k=k)))
             del block
 
         def seed_partition(entry):
