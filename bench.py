@@ -53,6 +53,9 @@ def parse_args():
                         help="host threads of a rank that walk its piles end to end, each on a stream of its own")
     parser.add_argument("--atlas-extra", default="",
                         help="comma-separated cell counts of further atlases to walk (BASELINE.json configs C3 / C4: 500000,2000000)")
+    parser.add_argument("--oversized-cells", type=int, default=65536,
+                        help="N > 1 only: cells of the oversized pile whose similarity is sharded by row blocks over the ranks, "
+                             "the per-row top-150 gathered with one NCCL all-gather (0: skip)")
     parser.add_argument("--candidate-piles", type=int, default=16,
                         help="piles whose seeds and first partition optimisation run side by side after the k-NN steps "
                              "(N = 1 only; 0: skip)")
@@ -552,6 +555,10 @@ def run_gpu_arm(args):
         if extra:
             atlas["other_sizes"] = [time_atlas_walk(args, size, device, rank, world, barrier) for size in extra]
 
+    oversized = None
+    if world > 1 and args.oversized_cells > 0:
+        oversized = time_oversized(args, rank, world, device, barrier)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -640,6 +647,8 @@ def run_gpu_arm(args):
     }
     if atlas is not None:
         line["atlas"] = atlas
+    if oversized is not None:
+        line["oversized"] = oversized
     if world == 1 and args.candidate_piles > 0:
         line["candidates"] = time_candidates(args, umis)
     os.sched_setaffinity(0, launcher_cpus)  # the CPU baseline uses every core the launcher gave us
@@ -758,6 +767,36 @@ def time_atlas_walk(args, cells, device, rank, world, barrier):
                     "memory before the timed region); max over ranks, barrier on both sides; wall_s = atlas upload + exchange + "
                     "cell totals + preliminary phase + groups + final phase; candidates = choose_seeds + first "
                     "optimize_partitions of every pile, side by side, one SM each"}
+
+
+def time_oversized(args, rank, world, device, barrier, genes=2000, top=150):
+    """The one exchange step of the path: the similarity of a pile too large for one GPU's N x N matrices,
+    sharded by row blocks over the ranks (every rank holds the whole [cells, genes] operand and computes its rows on the
+    tensor cores), the `top` largest values of every row kept, and only those gathered: one NCCL all-gather of
+    cells x top indices and values.  Host array in, CSR out on every rank; the best of three, max over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    from metacells_b200 import tools as tl
+
+    cells = args.oversized_cells
+    rng = np.random.default_rng(SEED)
+    types = rng.normal(size=(64, genes)).astype("float32")
+    dense = np.log2(rng.poisson(np.exp(1.0 + 0.6 * types[rng.integers(0, 64, size=cells)])).astype("float32") + np.float32(1 / 7))
+    walls = []
+    for _ in range(3):
+        barrier()
+        start = time.perf_counter()
+        matrix = tl.compute_obs_obs_similarity_top(dense, top)
+        torch.cuda.synchronize(device)
+        elapsed = torch.tensor([time.perf_counter() - start], dtype=torch.float64, device=device)
+        dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
+        walls.append(float(elapsed.item()))
+    return {"metric": "oversized_pile_similarity_top_wall_time", "cells": int(cells), "genes": int(genes), "top": int(top),
+            "n_gpus": world, "wall_s": min(walls), "wall_s_of_runs": walls, "nnz": int(matrix.nnz),
+            "all_gather_bytes": int(cells) * top * 8, "rows_per_rank": int(-(-cells // world)),
+            "note": "tools.compute_obs_obs_similarity_top: H2D of the operand, row-block similarity (tcgen05) + per-row top-k per rank, "
+                    "one all-gather of indices and one of values over NVLink, CSR assembled on the host of every rank"}
 
 
 def time_candidates(args, umis):
