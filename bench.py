@@ -604,19 +604,23 @@ def run_gpu_arm(args):
     achieved = flops / (umma_ms * 1e-3) / 1e12 if umma_ms else None
     correlate_line = {"bound": "tensor", "kernel": "correlate_umma_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                       "frac": achieved / peak if achieved else None, "traffic": ncu_traffic("correlate_umma", cells, features_count),
-                      "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_correlate_umma.txt",
+                      "traffic_source": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_ncu_full_correlate_umma.txt (890 genes) / r01_ncu_full_correlate_umma.txt (2 000)",
                       "peak_source": peak_source, "algorithmic_flops_per_launch": flops, "ms_per_launch": umma_ms,
                       "tf32_peak_measured": tf32,
                       "frac_of_sustained": achieved / (tf32["sustained_tflops"] / 3.0) if achieved else None,
                       "frac_of_bf16_burst_over_6": achieved / (peaks["bf16_tflops"] / 6.0) if achieved and peaks.get("bf16_tflops") else None,
-                      "ncu_tensor_pipe_pct": 67.0,
-                      "ncu_tensor_pipe_source": "sm__pipe_tensor_cycles_active of profiles/r01_ncu_full_correlate_umma.txt"}
+                      "ncu_tensor_pipe_pct": {890: 63.4, 2000: 67.0}.get(features_count),
+                      "ncu_tensor_pipe_source": "tensor pipe, % of active cycles: profiles/r02_ncu_full_correlate_umma.txt (890 genes), "
+                                                "profiles/r01_ncu_full_correlate_umma.txt (2 000 genes)"}
     # SURVEY 8d's algorithmic bytes: ranks read and write the whole square matrix; the downsample reads and writes the
     # pile's values and reads the row pointers; balance reads every rank once (count and fill passes are one stage).
     rank_line = hbm_line("rank_matrix_bucket_kernel", ("rank_matrix",), 8.0 * cells * cells, ncu_traffic("rank_matrix", cells, 2000),
-                         "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_ncu_full_rank_matrix_bucket_kernel.txt")
-    downsample_line = hbm_line("downsample_warp_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, None, None)
-    balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells, None, None)
+                         "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_ncu_full_rank_matrix_bucket.txt")
+    downsample_line = hbm_line("downsample_warp_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, ncu_traffic("downsample", cells, 0),
+                               "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_ncu_full_downsample_warp.txt")
+    balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells,
+                            ncu_traffic("balance", cells, 0),
+                            "ncu --set full, both passes, profiles/r02_ncu_full_balance_kernels.txt")
     # the dominant kernel is the one with the largest share of the step
     candidates = [line for line in (rank_line, correlate_line, downsample_line, balance_line) if line["ms_per_launch"]]
     dominant = max(candidates, key=lambda line: line["ms_per_launch"]) if candidates else correlate_line
@@ -873,11 +877,17 @@ def measure_tf32_peak(device):
 
 
 def ncu_traffic(kernel, cells, features):
-    """DRAM bytes per launch of a kernel from the committed `ncu --set full` captures (profiles/); null for a
+    """DRAM bytes per launch of a kernel from the committed `ncu --set full` captures (profiles/r02_ncu_full_*.txt and the
+    table of profiles/README.md, round 2; correlate at 2 000 genes: profiles/r01_ncu_full_correlate_umma.txt); null for a
     workload that was not captured."""
-    if (cells, features) != (16000, 2000):
+    if cells != 16000:
         return None
-    return {"correlate_umma": 3.302457e9 + 1.005782e9, "rank_matrix": 1.024083e9 + 0.970209e9}.get(kernel)
+    table = {"rank_matrix": 1.025e9 + 0.969e9, "downsample": 0.690e9 + 0.206e9, "balance": 1.024e9 + 0.018e9 + 1.046e9 + 0.111e9}
+    if features == 2000:
+        table["correlate_umma"] = 3.302457e9 + 1.005782e9
+    elif features == 890:
+        table["correlate_umma"] = 0.998e9 + 0.994e9
+    return table.get(kernel)
 
 
 _RESULT_FD = None

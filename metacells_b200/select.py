@@ -81,7 +81,8 @@ def _sliding_median(values: np.ndarray, order_by: np.ndarray, window_size: int, 
     if window_size >= count:
         return np.full(count, np.median(values))
     order = np.argsort(order_by)
-    back = np.argsort(order)
+    back = np.empty(count, dtype=order.dtype)  # == np.argsort(order): the inverse of a permutation, by scatter
+    back[order] = np.arange(count, dtype=order.dtype)
     padded = np.concatenate([order[window_size - half:window_size], order, order[count - window_size:count - window_size + half]])
     medians = (window_medians or _device_window_medians)(values[padded], window_size)
     assert medians.size == count
@@ -107,7 +108,7 @@ def relative_variance_of_genes(sums: np.ndarray, sums_squared: np.ndarray, cells
     normalized[silent] = 1.0
     with np.errstate(divide="ignore"):
         np.log2(normalized, out=normalized)
-    return normalized - _sliding_median(normalized, sums / cells, window_size, window_medians)
+    return normalized - _sliding_median(normalized, mean, window_size, window_medians)
 
 
 def select_feature_genes(pile, *, min_gene_relative_variance: Optional[float] = SELECT_MIN_GENE_RELATIVE_VARIANCE,
