@@ -15,13 +15,14 @@ parser.add_argument("--genes", type=int, default=27000)
 parser.add_argument("--features", type=int, default=2000)
 parser.add_argument("--no-cpu", action="store_true")
 parser.add_argument("--repeat", type=int, default=2)
+parser.add_argument("--k", type=int, default=0, help="k of the k-NN graph (0: from the pile, direct.py:251-267)")
 args = parser.parse_args()
 SEED = 123456
 ref = oracle.load_ref()
 umis = synth_umis(args.cells, args.genes, seed=SEED)
 cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
 start = time.perf_counter()
-outgoing, details = pipeline.compute_pile_knn_graph(umis, features=args.features, random_seed=SEED)
+outgoing, details = pipeline.compute_pile_knn_graph(umis, features=args.features, random_seed=SEED, k=args.k or None)
 print("knn graph on the GPU: %.2f s, k=%d, nnz=%d" % (time.perf_counter() - start, details["k"], outgoing.nnz), flush=True)
 incoming = sp.csc_matrix(outgoing); incoming.sort_indices()
 graph = (outgoing.data, outgoing.indices, outgoing.indptr, incoming.data, incoming.indices, incoming.indptr)
