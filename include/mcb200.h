@@ -346,6 +346,43 @@ int mcb_graph_seed_partition(const mcb_graph* graph, const float* mass_of_nodes,
                              double cooldown_node, double cold_temperature, int32_t* partition_of_nodes, int64_t* seeds_count,
                              double* score);
 
+/* The whole loop of compute_candidate_metacells (tools/candidates.py:128-289) on a device-resident k-NN graph.  A
+ * session keeps what the loop's native calls share between them in HBM: the graph (borrowed: it must outlive the
+ * session), its incoming layout (:135) and the node masses (cell_umis, :145-149).  Only the community vector (int32 per
+ * node) and the hot mask travel per call.  Every call runs on the calling thread's own stream and returns when its
+ * results are on the host; sessions of different piles are driven side by side by as many host threads. */
+typedef struct mcb_candidates mcb_candidates;
+int mcb_candidates_create(const mcb_graph* graph, const float* mass_of_nodes, mcb_candidates** out);
+void mcb_candidates_free(mcb_candidates* session);
+/* _choose_seeds (tools/candidates.py:720-749 -> xt.choose_seeds): seed_of_nodes int32[nodes] (host) holds the communities
+ * already given (-1 = none) and receives a seed for every node; as mcb_host_choose_seeds. */
+int mcb_candidates_choose_seeds(mcb_candidates* session, uint64_t random_seed, int64_t max_seeds_count,
+                                float min_seed_size_quantile, float max_seed_size_quantile, int32_t* seed_of_nodes,
+                                int64_t* seeds_count);
+/* _optimize_partitions (tools/candidates.py:831-880 -> xt.optimize_partitions) with the hot-communities mask and the cold
+ * temperature of the round; as mcb_host_optimize_partitions (stats nullable). */
+int mcb_candidates_optimize_partitions(mcb_candidates* session, uint32_t random_seed, double low_mass, double target_mass,
+                                       double high_mass, double low_size, double target_size, double high_size,
+                                       double cooldown_pass, double cooldown_node, int32_t* partition_of_nodes,
+                                       const int8_t* hot_partitions_mask, int64_t mask_count, double cold_temperature,
+                                       int64_t* stats, double* score);
+/* The symmetric sub-graph of every listed community (tools/candidates.py:545-546: outgoing[mask, :][:, mask] plus its
+ * transpose): members int32[member_offsets[communities]] lists the nodes community by community (ascending inside one, as
+ * np.where gives them; a node at most once), member_offsets int64[communities + 1]; dense (host) receives the
+ * communities' [size, size] float32 blocks one after the other. */
+int mcb_candidates_community_weights(mcb_candidates* session, const int32_t* members, const int64_t* member_offsets,
+                                     int64_t communities, float* dense);
+/* ut.min_cut of every listed community's symmetric sub-graph (utilities/computation.py:2368-2449, called at
+ * tools/candidates.py:548), one CTA per community.  The reference hands the edges to igraph's Graph.mincut (absent from
+ * this image); here Stoer & Wagner's algorithm in float64 with stated tie rules (each phase starts at the lowest live
+ * vertex; the most tightly connected vertex next, the lowest index among equals; the first phase of the least weight
+ * wins; its last vertex's side is cut.partition[0]) -- the same minimal weight, but among cuts of equal weight igraph's
+ * choice is its own.  is_second int8[members]: 1 = the member is in cut.partition[1]; totals float64[communities, 3]: the
+ * weight inside the first side, inside the second side and across the cut, added in float32 in the order :2414-2426
+ * walks the edges (Python float += numpy float32 stays float32 under NumPy >= 2).  At most 4096 nodes in a community. */
+int mcb_candidates_min_cuts(mcb_candidates* session, const int32_t* members, const int64_t* member_offsets,
+                            int64_t communities, int8_t* is_second, double* totals);
+
 /* ---- partitions.cpp ----------------------------------------------------------------------------- */
 
 /* optimize_partitions (partitions.cpp:1234-1302; bound as xt.optimize_partitions, tools/candidates.py:853-873).

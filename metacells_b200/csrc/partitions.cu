@@ -301,7 +301,6 @@ struct OptParams {
     double* scores;
     int nodes, partitions, padded, warps;
     int parallel_shuffle;  // the shared-memory plan has room for the raw generator stream (8 bytes per node)
-    int partition_bits;    // bits of the largest partition index
     Bounds bounds;
     double cooldown_pass, cooldown_node;
     uint32_t seed;
@@ -610,19 +609,9 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
             if (lane == 0) B.fine[1] += now - lap + (long long)(diff[0] == 1e300) + (long long)(diff[EVAL_UNROLL - 1] == 1e300);
             lap = now;
         }
-        // The lanes of every chunk grouped by partition: a ballot per bit of the partition index (match.any takes time in
-        // proportion to the number of distinct keys: here up to 32).  Lanes past the end belong to no group.  The four
-        // chunks' ballots are independent of each other.
-        unsigned peers_of[EVAL_UNROLL];
+        unsigned peers_of[EVAL_UNROLL];  // the groups of equal partitions of all four chunks first: independent of each other
 #pragma unroll
-        for (int j = 0; j < EVAL_UNROLL; ++j) peers_of[j] = __ballot_sync(FULL, q[j] >= 0);
-        for (int bit = 0; bit < P.partition_bits; ++bit) {
-#pragma unroll
-            for (int j = 0; j < EVAL_UNROLL; ++j) {
-                const unsigned set = __ballot_sync(FULL, (q[j] >> bit & 1) != 0);
-                peers_of[j] &= (q[j] >> bit & 1) ? set : ~set;
-            }
-        }
+        for (int j = 0; j < EVAL_UNROLL; ++j) peers_of[j] = __match_any_sync(FULL, q[j]);
 #pragma unroll
         for (int j = 0; j < EVAL_UNROLL; ++j) {
             if (start + j * 32 >= count) break;
@@ -1180,8 +1169,6 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
         params.padded = padded;
         params.warps = warps;
         params.parallel_shuffle = parallel_shuffle ? 1 : 0;
-        params.partition_bits = 1;
-        while ((1 << params.partition_bits) < partitions) ++params.partition_bits;
         params.bounds = bounds;
         params.cooldown_pass = cooldown_pass;
         params.cooldown_node = cooldown_node;

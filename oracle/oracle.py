@@ -9,6 +9,7 @@ the tanaylab/metacells v0.9.5 tree).  Nothing under ``metacells_b200/`` may impo
 from __future__ import annotations
 
 import ctypes
+import math
 import os
 import subprocess
 from typing import Optional, Tuple
@@ -645,3 +646,259 @@ def select_feature_genes(downsampled: sp.spmatrix, *, min_gene_relative_variance
         if not is_valid_set:
             masks[-1] = valid
     return combine(masks + additional)
+
+
+# ---- the candidate-metacells loop (tools/candidates.py:32-289) ----------------------------------------------------------
+#
+# Host control flow of the reference restated around this file's choose_seeds / optimize_partitions (the C restatements
+# pinned against oracle/_ref).  ``ut.min_cut`` hands the community's edges to igraph's ``Graph.mincut``, which is NOT in
+# this image: ``stoer_wagner_min_cut`` below is the published algorithm igraph implements for undirected graphs, with this
+# file's own tie rules, so the CHOICE among several cuts of the same minimal weight is unpinned against igraph (the weight
+# of the cut, and so the strength test, is not affected when the minimal cut is unique).
+
+
+def stoer_wagner_min_cut(weights: np.ndarray) -> np.ndarray:
+    """The side (``True`` = ``cut.partition[1]``) of every vertex in a minimal cut of the undirected graph with the
+    symmetric dense ``weights`` (Stoer & Wagner 1997), in float64.  Every phase grows a set from the lowest live vertex
+    by the most tightly connected one (ties: the lowest index); the first phase with the least cut-of-the-phase wins and
+    the vertices merged into its last vertex are ``cut.partition[0]``."""
+    count = len(weights)
+    merged = np.array(weights, dtype="float64")
+    root = np.arange(count)
+    live = np.ones(count, dtype=bool)
+    best, side = np.inf, np.zeros(count, dtype=bool)
+    for phase in range(count - 1):
+        key = np.zeros(count)
+        free = live.copy()
+        last = previous = -1
+        last_key = 0.0
+        for _ in range(count - phase):
+            chosen = int(np.argmax(np.where(free, key, -1.0)))
+            previous, last, last_key = last, chosen, key[chosen]
+            free[chosen] = False
+            key[free] += merged[chosen, free]
+        if last_key < best:
+            best, side = last_key, root != last
+        others = live.copy()
+        others[[last, previous]] = False
+        merged[previous, others] += merged[last, others]
+        merged[others, previous] = merged[previous, others]
+        live[last] = False
+        root[root == last] = previous
+    return side
+
+
+def min_cut_strength(weights: np.ndarray, is_second: np.ndarray) -> Optional[float]:
+    """The strength ``ut.min_cut`` returns beside the cut (utilities/computation.py:2408-2449).  The three totals are
+    ``total += weight`` of numpy float32 scalars, which under NumPy >= 2 stays float32: sequential float32 sums, here as
+    the last entry of a float32 ``cumsum``, over the edges in the order :2389-2403 lists them."""
+    count = len(weights)
+    sources, targets = np.nonzero(np.tril(weights, -1) > 0)  # row-major: source ascending, target ascending below it
+    edge_weights = weights[sources, targets].astype("float32")
+    across = is_second[sources] != is_second[targets]
+    inside_second = is_second[sources] & is_second[targets]
+    inside_first = ~is_second[sources] & ~is_second[targets]
+
+    def total(mask):
+        return np.cumsum(edge_weights[mask], dtype="float32")[-1] if mask.any() else 0.0
+
+    cut_total, first_total, second_total = total(across), total(inside_first), total(inside_second)
+    second_size = int(is_second.sum())
+    first_size = count - second_size
+    if cut_total == 0:
+        return 0.0
+    if not (first_total > 0 and second_total > 0):
+        return None
+    cut_mean = cut_total / (first_size * second_size)
+    first_mean = first_total / ((first_size * (first_size - 1)) / 2)
+    second_mean = second_total / ((second_size * (second_size - 1)) / 2)
+    return cut_mean / math.sqrt(first_mean * second_mean)
+
+
+def _candidate_seeds_count(total_umis, total_size, low_umis, high_umis, low_size, high_size) -> int:
+    """tools/candidates.py:293-321."""
+    by_umis = (int(math.ceil(total_umis / high_umis)), int(math.ceil(total_umis / low_umis)))
+    by_size = (int(math.ceil(total_size / high_size)), int(math.ceil(total_size / low_size)))
+    if by_size[1] < by_umis[0]:
+        return int(round((by_size[1] + by_umis[0]) / 2))
+    if by_umis[1] < by_size[0]:
+        return int(round((by_umis[1] + by_size[0]) / 2))
+    return int(round((max(by_size[0], by_umis[0]) + min(by_size[1], by_umis[1])) / 2))
+
+
+def compute_candidate_metacells(outgoing: sp.csr_matrix, cell_umis: np.ndarray, *, random_seed: int,
+                                target_metacell_size: int = 48, min_metacell_size: int = 12, target_metacell_umis: int = 160000,
+                                min_seed_size_quantile: float = 0.85, max_seed_size_quantile: float = 0.95,
+                                cooldown_pass: float = 0.02, cooldown_node: float = 0.25, cooldown_phase: float = 0.75,
+                                increase_phase: float = 1.01, min_split_size_factor: float = 2.0,
+                                max_merge_size_factor: float = 0.5, max_split_min_cut_strength: float = 0.1,
+                                min_cut_seed_cells: int = 7, must_complete_cover: bool = False,
+                                trace: Optional[list] = None) -> np.ndarray:
+    """tools/candidates.py:121-289 with its helpers (:324-648) inlined as closures; the ``candidate`` of every cell."""
+    incoming = csr_to_csc(outgoing)
+    cells = outgoing.shape[0]
+    assert cell_umis.dtype == np.float32
+    lowest_size = min_metacell_size
+    low_umis = int(math.floor(target_metacell_umis * max_merge_size_factor))  # :152-159
+    high_umis = int(math.ceil(target_metacell_umis * min_split_size_factor)) - 1
+    low_size = max(min_metacell_size, int(math.floor(target_metacell_size * max_merge_size_factor)))
+    high_size = max(int(math.ceil(target_metacell_size * min_split_size_factor)) - 1, low_size + 1)
+    known_whole = set()
+
+    def seed(communities, max_seeds_count):  # :720-749
+        count = choose_seeds(outgoing, incoming, random_seed, max_seeds_count, min_seed_size_quantile, max_seed_size_quantile,
+                             communities)
+        assert communities.min() == 0
+        return count
+
+    def optimize(communities, hot, cold_temperature, size_limit):  # :831-880
+        hot_mask = np.zeros(max(communities.max() + 1, 2), dtype="int8")
+        hot_mask[hot] = 1
+        return optimize_partitions(outgoing, incoming, random_seed, cell_umis, low_umis, target_metacell_umis, high_umis,
+                                   low_size, target_metacell_size, size_limit, cooldown_pass, cooldown_node, communities,
+                                   hot_mask, cold_temperature)
+
+    def cut_one(communities, index, new_index):  # :533-589
+        mask = communities == index
+        if mask.sum() < 2:
+            return "unchanged"
+        sliced = outgoing[mask, :][:, mask]
+        weights = (sliced + sliced.T).toarray()
+        is_second = stoer_wagner_min_cut(weights)
+        strength = min_cut_strength(weights, is_second)
+        if strength is None or strength > max_split_min_cut_strength:
+            return "unchanged"
+        where = np.where(mask)[0]
+        sizes = (int((~is_second).sum()), int(is_second.sum()))
+        small = 0 if sizes[0] < sizes[1] else 1
+        if sizes[small] >= min_cut_seed_cells:
+            communities[where[is_second]] = new_index
+            return "split"
+        if must_complete_cover and strength > 0:
+            return "unchanged"
+        communities[where[is_second == bool(small)]] = -1
+        return "cut"
+
+    def split_or_cut(communities, size_limit):  # :410-530
+        count = communities.max() + 1
+        new_index = count
+        split = cut = 0
+        hot = []
+        for index in range(count):
+            mask = communities == index
+            size = np.sum(mask)
+            umis = np.sum(cell_umis[mask])
+            if not ((umis > high_umis and size >= 3 * low_size) or (size > size_limit and umis >= 3 * low_umis)):
+                continue
+            where = np.where(mask)[0]
+            parts = max(2, min(int(round(umis / target_metacell_umis)), int(round(size / target_metacell_size))))
+            while True:
+                assignment = np.random.randint(parts, size=len(where))
+                if all(np.any(assignment == part) for part in range(parts)):
+                    break
+            communities[where] = -1
+            for part in range(parts):
+                chosen = where[assignment == part]
+                chosen = chosen[np.random.randint(len(chosen))]
+                if part == 0:
+                    hot.append(index)
+                    communities[chosen] = index
+                else:
+                    hot.append(new_index)
+                    communities[chosen] = new_index
+                    new_index += 1
+                    split += 1
+        if split == 0:
+            for index in range(count):
+                key = tuple(np.where(communities == index)[0])
+                if key in known_whole:
+                    continue
+                action = cut_one(communities, index, new_index)
+                if action == "unchanged":
+                    known_whole.add(key)
+                    continue
+                hot.append(index)
+                if action == "split":
+                    hot.append(new_index)
+                    new_index += 1
+                    split += 1
+                else:
+                    cut += 1
+        return split, cut, hot
+
+    def reduce(communities, hot, cold_temperature):  # :324-407
+        np.random.seed(random_seed)
+        size_limit = high_size
+        while True:
+            score = optimize(communities, hot, cold_temperature, size_limit)
+            if trace is not None:
+                trace.append(("optimize", score, communities.copy()))
+            cold_temperature = cold_temperature * (1 - cooldown_phase)
+            size_limit *= increase_phase
+            split, cut, hot = split_or_cut(communities, size_limit)
+            if trace is not None:
+                trace.append(("split", split, cut, communities.copy()))
+            if split + cut == 0:
+                return cold_temperature, score
+            max_seeds_count = communities.max() + 1
+            if cut > 0:
+                hot.append(max_seeds_count)
+                max_seeds_count += 1
+            seed(communities, max_seeds_count)
+
+    def too_small(communities):  # :592-631
+        small, nodes, umis_of_small = set(), 0, 0
+        for index in range(communities.max() + 1):
+            mask = communities == index
+            size = np.sum(mask)
+            umis = np.sum(cell_umis[mask])
+            if size < lowest_size:
+                pass
+            elif size < low_size and 2 * umis < high_umis:
+                pass
+            elif umis < low_umis and 2 * size < high_size:
+                pass
+            else:
+                continue
+            small.add(index)
+            nodes += size
+            umis_of_small += umis
+        return small, nodes, umis_of_small
+
+    def cancel(communities, cancelled):  # :634-648
+        kept = 0
+        for index in range(communities.max() + 1):
+            if index in cancelled:
+                communities[communities == index] = -1
+                continue
+            if index > kept:
+                communities[communities == index] = kept
+            kept += 1
+        return kept
+
+    communities = np.full(cells, -1, dtype="int32")
+    seeds_count = seed(communities, _candidate_seeds_count(sum(cell_umis), cells, low_umis, high_umis, low_size, high_size))
+    if trace is not None:
+        trace.append(("seeds", seeds_count, communities.copy()))
+    np.random.seed(random_seed)
+    cold_temperature = 1 - cooldown_pass
+    old = (len(communities), 1e9)
+    old_communities = communities
+    hot = list(range(seeds_count))
+    while True:
+        cold_temperature, score = reduce(communities, hot, cold_temperature)
+        small, small_nodes, small_umis = too_small(communities)
+        if len(small) < 2:
+            break
+        if old <= (small_nodes, score):
+            communities = old_communities
+            break
+        old, old_communities = (small_nodes, score), communities.copy()
+        kept = cancel(communities, small)
+        extra = min(len(small) - 1, _candidate_seeds_count(small_umis, small_nodes, low_umis, high_umis, low_size, high_size))
+        seeds_count = seed(communities, kept + extra)
+        if trace is not None:
+            trace.append(("reseed", seeds_count, communities.copy()))
+        hot = list(range(kept, seeds_count))
+    assert np.all(communities >= 0)
+    return communities
