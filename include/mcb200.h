@@ -314,6 +314,50 @@ int mcb_pile_create_from_atlas(const mcb_atlas* atlas, const int64_t* rows, int6
  * of the grouping pile, divide_and_conquer.py:1153-1245): its non-zeros in column order, as scipy's csr_matrix(dense). */
 int mcb_pile_create_dense_dev(const float* dense, int64_t cells, int64_t genes, mcb_pile** out);
 
+/* ---- gaps.cpp ------------------------------------------------------------------------------------ */
+
+/* compute_cell_gaps (gaps.cpp:6-186; bound as xt.compute_cell_gaps, tools/deviants.py:309-326): per candidate metacell and
+ * gene, the cells are ordered by the gene's log fraction (the reference's own std::sort, whose order of equal values
+ * carries over from gene to gene, is reproduced) and the cells beyond a gap at either end of the order receive the gap's
+ * size in max_gap_per_cell (float32[cells], read and written: the maximum with what is there).  The two matrices are
+ * float32 [cells, genes], C contiguous; candidate_of_cells int32[cells]; deviant_per_cell / active_per_cell bool[cells];
+ * min_gap_per_gene float32[genes].  The reference's third matrix (the fractions) is only checked for its shape there and
+ * is not an argument here.  At most 8192 cells in a candidate, 65535 candidates. */
+int mcb_host_compute_cell_gaps(const float* umis_per_gene_per_cell, const float* log_fraction_per_gene_per_cell, int64_t cells,
+                               int64_t genes, const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell,
+                               const uint8_t* active_per_cell, const float* min_gap_per_gene, int64_t candidates_count,
+                               int64_t gap_skip_cells, int64_t max_deviant_cells_count, float max_deviant_cells_fraction,
+                               float min_compare_umis, float* max_gap_per_cell);
+/* As above with the two matrices on the device (the vectors stay host arrays); synchronises the stream. */
+int mcb_dev_compute_cell_gaps(const float* umis_per_gene_per_cell, const float* log_fraction_per_gene_per_cell, int64_t cells,
+                              int64_t genes, const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell,
+                              const uint8_t* active_per_cell, const float* min_gap_per_gene, int64_t candidates_count,
+                              int64_t gap_skip_cells, int64_t max_deviant_cells_count, float max_deviant_cells_fraction,
+                              float min_compare_umis, float* max_gap_per_cell, void* stream);
+
+/* The dense inputs of compute_cell_gaps for a pile, made on the device from its (not downsampled) UMIs
+ * (tools/deviants.py:270-292: to_numpy_matrix, the fractions umis / total, log2(fraction + regularization)).  The division
+ * and the addition are IEEE float32 operations; the logarithm is numpy's float32 log2, which is not correctly rounded, so
+ * the host supplies it: log_table float32 [cells, table_counts] holds log2(count / total + regularization) of every cell
+ * for the counts 0 .. table_counts - 1 (one vectorised numpy call), and the entries whose count the table does not hold
+ * are handed back (mcb_gap_inputs_exceptions / _read_exceptions: their fraction + regularization) and patched with the
+ * host's logarithms (mcb_gap_inputs_patch).  All host arrays. */
+typedef struct mcb_gap_inputs mcb_gap_inputs;
+int mcb_pile_gap_inputs_create(mcb_pile* pile, const float* total_umis_per_cell, const float* regularization_per_cell,
+                               const float* log_table, int64_t table_counts, mcb_gap_inputs** out);
+int64_t mcb_gap_inputs_exceptions(const mcb_gap_inputs* inputs);
+int mcb_gap_inputs_read_exceptions(const mcb_gap_inputs* inputs, float* values);
+int mcb_gap_inputs_patch(mcb_gap_inputs* inputs, const float* logs);
+/* The two matrices to host arrays of cells x genes floats (either may be null): for tests and small piles. */
+int mcb_gap_inputs_read(const mcb_gap_inputs* inputs, float* umis, float* log_fraction);
+int mcb_gap_inputs_device_arrays(const mcb_gap_inputs* inputs, const float** umis, const float** log_fraction);
+/* compute_cell_gaps on the resident matrices: one call per round of tools/deviants.py:299-356. */
+int mcb_gap_inputs_cell_gaps(const mcb_gap_inputs* inputs, const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell,
+                             const uint8_t* active_per_cell, const float* min_gap_per_gene, int64_t candidates_count,
+                             int64_t gap_skip_cells, int64_t max_deviant_cells_count, float max_deviant_cells_fraction,
+                             float min_compare_umis, float* max_gap_per_cell);
+void mcb_gap_inputs_free(mcb_gap_inputs* inputs);
+
 /* ---- choose_seeds.cpp --------------------------------------------------------------------------- */
 
 /* choose_seeds (choose_seeds.cpp:264-372; bound as xt.choose_seeds, tools/candidates.py:733-745).  The graph is

@@ -868,3 +868,218 @@ int mcb_pile_wait_upload(mcb_pile* pile) {
 void mcb_pile_free(mcb_pile* pile) { delete pile; }
 
 }  // extern "C"
+
+// ---- deviant cells: the dense inputs of compute_cell_gaps, built on the device (tools/deviants.py:270-292) ------------
+
+namespace mcb {
+int cell_gaps_launch(const float* umis, const float* log_fraction, int64_t cells, int64_t genes, int64_t stride,
+                     const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell, const uint8_t* active_per_cell,
+                     const float* min_gap_per_gene, int64_t candidates_count, int64_t gap_skip_cells,
+                     int64_t max_deviant_cells_count, float max_deviant_cells_fraction, float min_compare_umis,
+                     float* max_gap_per_cell, cudaStream_t stream);
+}
+
+struct mcb_gap_inputs {
+    int64_t cells = 0, genes = 0;
+    Scratch umis, log_fraction;       // float32 [cells, genes]
+    Scratch exception_at, exception_x;  // entries whose count is beyond the table: position in the matrix, fraction + regularization
+    int64_t exceptions = 0;
+};
+
+namespace {
+
+constexpr int64_t GAP_EXCEPTIONS_CAPACITY = 1 << 22;
+
+// One warp per cell: the row of log fractions starts as the cell's value of a zero count, then every stored count is
+// written to the dense UMIs and looked up in the cell's row of the table; counts the table does not hold (large, or not
+// whole numbers) are listed for the host, which takes their logarithm with numpy's own log2.
+__global__ void gap_inputs_kernel(const float* __restrict__ data, const int32_t* __restrict__ indices,
+                                  const int32_t* __restrict__ indptr, int64_t cells, int64_t genes,
+                                  const float* __restrict__ total_per_cell, const float* __restrict__ regularization_per_cell,
+                                  const float* __restrict__ table, int table_counts, float* __restrict__ umis,
+                                  float* __restrict__ log_fraction, int64_t* __restrict__ exception_at,
+                                  float* __restrict__ exception_x, unsigned long long* __restrict__ exceptions,
+                                  int64_t capacity) {
+    const int64_t cell = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (cell >= cells) return;
+    const float* row_table = table + cell * table_counts;
+    const float of_zero = row_table[0];
+    float* row_logs = log_fraction + cell * genes;
+    float* row_umis = umis + cell * genes;
+    for (int64_t gene = lane; gene < genes; gene += 32) {
+        row_logs[gene] = of_zero;
+        row_umis[gene] = 0.0f;
+    }
+    __syncwarp();
+    const float total = total_per_cell[cell], regularization = regularization_per_cell[cell];
+    for (int at = indptr[cell] + lane; at < indptr[cell + 1]; at += 32) {
+        const float value = data[at];
+        const int gene = indices[at];
+        row_umis[gene] = value;
+        const int whole = int(value);
+        if (value >= 0.0f && value < float(table_counts) && float(whole) == value) {
+            row_logs[gene] = row_table[whole];
+        } else {
+            const unsigned long long slot = atomicAdd(exceptions, 1ull);
+            if (slot < (unsigned long long)capacity) {
+                exception_at[slot] = cell * genes + gene;
+                exception_x[slot] = __fadd_rn(__fdiv_rn(value, total), regularization);
+            }
+        }
+    }
+}
+
+__global__ void gap_patch_kernel(const int64_t* __restrict__ exception_at, const float* __restrict__ logs, int64_t count,
+                                 float* __restrict__ log_fraction) {
+    const int64_t at = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (at < count) log_fraction[exception_at[at]] = logs[at];
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcb_pile_gap_inputs_create(mcb_pile* pile, const float* total_umis_per_cell, const float* regularization_per_cell,
+                               const float* log_table, int64_t table_counts, mcb_gap_inputs** out) {
+    MCB_REQUIRE(pile && total_umis_per_cell && regularization_per_cell && log_table && out, "gap_inputs: null argument");
+    MCB_REQUIRE(table_counts >= 1 && table_counts <= (1 << 20), "gap_inputs: table_counts out of range");
+    *out = nullptr;
+    cudaStream_t stream = pile->stream;
+    MCB_TRY(wait_for_upload(pile));
+    const int64_t cells = pile->cells, genes = pile->genes;
+    std::unique_ptr<mcb_gap_inputs> inputs(new mcb_gap_inputs());
+    inputs->cells = cells;
+    inputs->genes = genes;
+    MCB_TRY(inputs->umis.alloc(size_t(cells) * genes * sizeof(float), stream));
+    MCB_TRY(inputs->log_fraction.alloc(size_t(cells) * genes * sizeof(float), stream));
+    MCB_TRY(inputs->exception_at.alloc(size_t(GAP_EXCEPTIONS_CAPACITY) * sizeof(int64_t), stream));
+    MCB_TRY(inputs->exception_x.alloc(size_t(GAP_EXCEPTIONS_CAPACITY) * sizeof(float), stream));
+    Scratch d_totals, d_regularization, d_table, d_count;
+    MCB_TRY(d_totals.alloc(size_t(cells) * sizeof(float), stream));
+    MCB_TRY(d_regularization.alloc(size_t(cells) * sizeof(float), stream));
+    MCB_TRY(d_table.alloc(size_t(cells) * table_counts * sizeof(float), stream));
+    MCB_TRY(d_count.alloc(sizeof(unsigned long long), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_totals.ptr, total_umis_per_cell, size_t(cells) * sizeof(float), cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemcpyAsync(d_regularization.ptr, regularization_per_cell, size_t(cells) * sizeof(float),
+                             cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemcpyAsync(d_table.ptr, log_table, size_t(cells) * table_counts * sizeof(float), cudaMemcpyHostToDevice,
+                             stream));
+    MCB_CUDA(cudaMemsetAsync(d_count.ptr, 0, sizeof(unsigned long long), stream));
+    MCB_PROFILED("gap_inputs", stream,
+                 gap_inputs_kernel<<<unsigned(ceil_div(cells * 32, 256)), 256, 0, stream>>>(
+                     pile->data, pile->indices, pile->indptr, cells, genes, d_totals.as<float>(), d_regularization.as<float>(),
+                     d_table.as<float>(), int(table_counts), inputs->umis.as<float>(), inputs->log_fraction.as<float>(),
+                     inputs->exception_at.as<int64_t>(), inputs->exception_x.as<float>(), d_count.as<unsigned long long>(),
+                     GAP_EXCEPTIONS_CAPACITY));
+    MCB_LAUNCH_CHECK();
+    unsigned long long count = 0;
+    MCB_TRY(copy_to_host(&count, d_count.ptr, sizeof(count), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    MCB_REQUIRE(count <= (unsigned long long)GAP_EXCEPTIONS_CAPACITY,
+                "gap_inputs: %llu counts are beyond the table of %lld (raise table_counts)", count, (long long)table_counts);
+    inputs->exceptions = int64_t(count);
+    *out = inputs.release();
+    return MCB_OK;
+}
+
+int64_t mcb_gap_inputs_exceptions(const mcb_gap_inputs* inputs) { return inputs ? inputs->exceptions : 0; }
+
+int mcb_gap_inputs_read_exceptions(const mcb_gap_inputs* inputs, float* values) {
+    MCB_REQUIRE(inputs && (values || inputs->exceptions == 0), "gap_inputs: null argument");
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    MCB_TRY(copy_to_host(values, inputs->exception_x.ptr, size_t(inputs->exceptions) * sizeof(float), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_gap_inputs_patch(mcb_gap_inputs* inputs, const float* logs) {
+    MCB_REQUIRE(inputs && (logs || inputs->exceptions == 0), "gap_inputs: null argument");
+    if (inputs->exceptions == 0) return MCB_OK;
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    Scratch d_logs;
+    MCB_TRY(d_logs.alloc(size_t(inputs->exceptions) * sizeof(float), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_logs.ptr, logs, size_t(inputs->exceptions) * sizeof(float), cudaMemcpyHostToDevice, stream));
+    MCB_PROFILED("gap_patch", stream,
+                 gap_patch_kernel<<<unsigned(ceil_div(inputs->exceptions, 256)), 256, 0, stream>>>(
+                     inputs->exception_at.as<int64_t>(), d_logs.as<float>(), inputs->exceptions,
+                     inputs->log_fraction.as<float>()));
+    MCB_LAUNCH_CHECK();
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_gap_inputs_read(const mcb_gap_inputs* inputs, float* umis, float* log_fraction) {
+    MCB_REQUIRE(inputs != nullptr, "gap_inputs: null handle");
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    const size_t bytes = size_t(inputs->cells) * inputs->genes * sizeof(float);
+    if (umis) MCB_TRY(copy_to_host(umis, inputs->umis.ptr, bytes, stream));
+    if (log_fraction) MCB_TRY(copy_to_host(log_fraction, inputs->log_fraction.ptr, bytes, stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_gap_inputs_device_arrays(const mcb_gap_inputs* inputs, const float** umis, const float** log_fraction) {
+    MCB_REQUIRE(inputs != nullptr, "gap_inputs: null handle");
+    if (umis) *umis = inputs->umis.as<float>();
+    if (log_fraction) *log_fraction = inputs->log_fraction.as<float>();
+    return MCB_OK;
+}
+
+int mcb_gap_inputs_cell_gaps(const mcb_gap_inputs* inputs, const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell,
+                             const uint8_t* active_per_cell, const float* min_gap_per_gene, int64_t candidates_count,
+                             int64_t gap_skip_cells, int64_t max_deviant_cells_count, float max_deviant_cells_fraction,
+                             float min_compare_umis, float* max_gap_per_cell) {
+    MCB_REQUIRE(inputs && candidate_of_cells && deviant_per_cell && active_per_cell && min_gap_per_gene && max_gap_per_cell,
+                "compute_cell_gaps: null argument");
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    return cell_gaps_launch(inputs->umis.as<float>(), inputs->log_fraction.as<float>(), inputs->cells, inputs->genes,
+                            inputs->genes, candidate_of_cells, deviant_per_cell, active_per_cell, min_gap_per_gene,
+                            candidates_count, gap_skip_cells, max_deviant_cells_count, max_deviant_cells_fraction,
+                            min_compare_umis, max_gap_per_cell, stream);
+}
+
+void mcb_gap_inputs_free(mcb_gap_inputs* inputs) { delete inputs; }
+
+/* xt.compute_cell_gaps itself (gaps.cpp:6-186) on host arrays: the two dense matrices go up, the gaps come back.  The
+ * fraction matrix of the reference's signature is not read by the reference (only its shape is checked) and is left out. */
+int mcb_host_compute_cell_gaps(const float* umis_per_gene_per_cell, const float* log_fraction_per_gene_per_cell, int64_t cells,
+                               int64_t genes, const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell,
+                               const uint8_t* active_per_cell, const float* min_gap_per_gene, int64_t candidates_count,
+                               int64_t gap_skip_cells, int64_t max_deviant_cells_count, float max_deviant_cells_fraction,
+                               float min_compare_umis, float* max_gap_per_cell) {
+    MCB_REQUIRE(umis_per_gene_per_cell && log_fraction_per_gene_per_cell && candidate_of_cells && deviant_per_cell &&
+                    active_per_cell && min_gap_per_gene && max_gap_per_cell && cells > 0 && genes > 0,
+                "compute_cell_gaps: null argument or empty matrix");
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    Scratch d_umis, d_logs;
+    const size_t bytes = size_t(cells) * genes * sizeof(float);
+    MCB_TRY(d_umis.alloc(bytes, stream));
+    MCB_TRY(d_logs.alloc(bytes, stream));
+    MCB_CUDA(cudaMemcpyAsync(d_umis.ptr, umis_per_gene_per_cell, bytes, cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemcpyAsync(d_logs.ptr, log_fraction_per_gene_per_cell, bytes, cudaMemcpyHostToDevice, stream));
+    return cell_gaps_launch(d_umis.as<float>(), d_logs.as<float>(), cells, genes, genes, candidate_of_cells, deviant_per_cell,
+                            active_per_cell, min_gap_per_gene, candidates_count, gap_skip_cells, max_deviant_cells_count,
+                            max_deviant_cells_fraction, min_compare_umis, max_gap_per_cell, stream);
+}
+
+int mcb_dev_compute_cell_gaps(const float* umis_per_gene_per_cell, const float* log_fraction_per_gene_per_cell, int64_t cells,
+                              int64_t genes, const int32_t* candidate_of_cells, const uint8_t* deviant_per_cell,
+                              const uint8_t* active_per_cell, const float* min_gap_per_gene, int64_t candidates_count,
+                              int64_t gap_skip_cells, int64_t max_deviant_cells_count, float max_deviant_cells_fraction,
+                              float min_compare_umis, float* max_gap_per_cell, void* stream) {
+    MCB_REQUIRE(umis_per_gene_per_cell && log_fraction_per_gene_per_cell && candidate_of_cells && deviant_per_cell &&
+                    active_per_cell && min_gap_per_gene && max_gap_per_cell && cells > 0 && genes > 0,
+                "compute_cell_gaps: null argument or empty matrix");
+    return cell_gaps_launch(umis_per_gene_per_cell, log_fraction_per_gene_per_cell, cells, genes, genes, candidate_of_cells,
+                            deviant_per_cell, active_per_cell, min_gap_per_gene, candidates_count, gap_skip_cells,
+                            max_deviant_cells_count, max_deviant_cells_fraction, min_compare_umis, max_gap_per_cell,
+                            static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -259,6 +259,32 @@ def choose_seeds(outgoing_weights, outgoing_indices, outgoing_indptr, incoming_w
     return count.value
 
 
+def compute_cell_gaps(umis_per_gene_per_cell, fraction_per_gene_per_cell, log_fraction_per_gene_per_cell,
+                      candidate_index_per_cell, deviant_per_cell, active_per_cell, min_gap_per_gene, candidates_count,
+                      gap_skip_cells, max_deviant_cells_count, max_deviant_cells_fraction, min_compare_umis, max_gap_per_cell):
+    """gaps.cpp:6-186 (called at tools/deviants.py:309-326): ``max_gap_per_cell`` is updated in place.  The fractions
+    matrix is checked for its shape only, as in the reference."""
+    cells, genes = umis_per_gene_per_cell.shape
+    for name, matrix in (("fraction_per_gene_per_cell", fraction_per_gene_per_cell),
+                         ("log_fraction_per_gene_per_cell", log_fraction_per_gene_per_cell)):
+        if matrix.shape != (cells, genes):
+            raise ValueError(f"{name}: expected shape {(cells, genes)}, got {matrix.shape}")
+    for name, vector, size in (("candidate_index_per_cell", candidate_index_per_cell, cells),
+                               ("deviant_per_cell", deviant_per_cell, cells), ("active_per_cell", active_per_cell, cells),
+                               ("min_gap_per_gene", min_gap_per_gene, genes), ("max_gap_per_cell", max_gap_per_cell, cells)):
+        if len(vector) != size:
+            raise ValueError(f"{name}: expected {size} entries, got {len(vector)}")
+    if row_stride(umis_per_gene_per_cell) != genes or row_stride(log_fraction_per_gene_per_cell) != genes:
+        raise ValueError("compute_cell_gaps: the matrices must be C contiguous")
+    call("mcb_host_compute_cell_gaps", host_ptr(umis_per_gene_per_cell, "float32", "umis_per_gene_per_cell"),
+         host_ptr(log_fraction_per_gene_per_cell, "float32", "log_fraction_per_gene_per_cell"), ("i64", cells), ("i64", genes),
+         host_ptr(candidate_index_per_cell, "int32", "candidate_index_per_cell"),
+         host_ptr(deviant_per_cell, "bool", "deviant_per_cell"), host_ptr(active_per_cell, "bool", "active_per_cell"),
+         host_ptr(min_gap_per_gene, "float32", "min_gap_per_gene"), ("i64", int(candidates_count)),
+         ("i64", int(gap_skip_cells)), ("i64", int(max_deviant_cells_count)), ("f32", float(max_deviant_cells_fraction)),
+         ("f32", float(min_compare_umis)), host_ptr(max_gap_per_cell, "float32", "max_gap_per_cell", True))
+
+
 def glibc_log(values):
     """glibc's double ``log`` evaluated on the device (what the partition scores are built from)."""
     values = np.ascontiguousarray(values, dtype="float64")

@@ -168,6 +168,14 @@ class Pile:
             raise ValueError("max_count is needed for a device pile that was not downsampled")
         return int(self._data.max(initial=0))
 
+    def cell_totals(self) -> np.ndarray:
+        """The total UMIs of every cell (float32, ``umis.sum(axis=1)``), for a pile made from host arrays; a pile gathered
+        from an atlas takes them from ``Atlas.cell_umis``."""
+        if self._data is None:
+            raise ValueError("the pile has no host copy of its UMIs: pass the totals (Atlas.cell_umis()[rows])")
+        matrix = sp.csr_matrix((self._data, self._indices, self._indptr), shape=self.shape)
+        return np.asarray(matrix.sum(axis=1)).reshape(-1).astype("float32", copy=False)
+
     def wait_upload(self) -> None:
         """Returns when the pile's upload has arrived (``mcb_pile_wait_upload``)."""
         check(lib().mcb_pile_wait_upload(self._handle))

@@ -902,3 +902,68 @@ def compute_candidate_metacells(outgoing: sp.csr_matrix, cell_umis: np.ndarray, 
         hot = list(range(kept, seeds_count))
     assert np.all(communities >= 0)
     return communities
+
+
+# ---- deviant cells, "gaps" policy (tools/deviants.py:241-356 over gaps.cpp) ----------------------------------------------
+
+
+def gaps_deviant_cells(umis: sp.csr_matrix, candidates: np.ndarray, ref, *, noisy_genes_mask: Optional[np.ndarray] = None,
+                       min_gene_fold_factor: float = 3.0, gap_skip_cells: int = 1, min_noisy_gene_fold_factor: float = 2.0,
+                       max_cell_fraction: float = 0.25, max_gap_cells_count: int = 3, max_gap_cells_fraction: float = 0.1,
+                       cells_regularization_quantile: float = 0.25, min_compare_umis: int = 8,
+                       trace: Optional[list] = None) -> np.ndarray:
+    """``find_deviant_cells(policy="gaps")``: the dense matrices as the reference makes them (numpy, on the host) and the
+    reference's own ``compute_cell_gaps`` (``ref``: oracle/_ref, compiled from gaps.cpp).  ``gap_skip_cells`` is the
+    public parameter (the native call gets one more, tools/deviants.py:100)."""
+    gap_skip_cells += 1
+    cells_count, genes_count = umis.shape
+    if cells_count <= max_gap_cells_count:
+        return np.zeros(cells_count, dtype="bool")
+    min_gap_per_gene = np.full(genes_count, min_gene_fold_factor, dtype="float32")
+    if noisy_genes_mask is not None:
+        min_gap_per_gene[noisy_genes_mask] += min_noisy_gene_fold_factor
+    candidate_per_cell = np.asarray(candidates).astype("int32")
+    candidates_count = np.max(candidate_per_cell) + 1
+    umis_per_gene_per_cell = np.ascontiguousarray(umis.toarray(), dtype="float32")
+    regularization_per_cell = np.empty(cells_count, dtype="float32")
+    max_gap_per_cell = np.empty(cells_count, dtype="float32")
+    new_deviant_per_cell = np.empty(cells_count, dtype="bool")
+    deviant_per_cell = np.empty(cells_count, dtype="bool")
+    total_umis_per_cell = np.asarray(umis.sum(axis=1)).reshape(-1).copy()
+    assert total_umis_per_cell.dtype == np.float32
+    fraction_per_gene_per_cell = umis_per_gene_per_cell / total_umis_per_cell[:, np.newaxis]
+    for candidate_index in range(candidates_count):
+        mask_per_cell = candidate_per_cell == candidate_index
+        totals = total_umis_per_cell[mask_per_cell]
+        regularization = max(1.0, np.quantile(totals, cells_regularization_quantile))
+        regularization_per_cell[mask_per_cell] = 1.0 / np.maximum(totals, regularization)
+    log_fraction_per_gene_per_cell = np.log2(fraction_per_gene_per_cell + regularization_per_cell[:, np.newaxis])
+    assert log_fraction_per_gene_per_cell.dtype == np.float32
+    while True:
+        new_deviant_per_cell[:] = True
+        deviant_per_cell[:] = False
+        deviants_fraction = 0.0
+        while deviants_fraction <= max_cell_fraction:
+            max_gap_per_cell[:] = 0.0
+            ref.compute_cell_gaps(umis_per_gene_per_cell, fraction_per_gene_per_cell, log_fraction_per_gene_per_cell,
+                                  candidate_per_cell, deviant_per_cell, new_deviant_per_cell, min_gap_per_gene, candidates_count,
+                                  gap_skip_cells, max_gap_cells_count, max_gap_cells_fraction, float(min_compare_umis),
+                                  max_gap_per_cell)
+            if trace is not None:
+                trace.append(max_gap_per_cell.copy())
+            large_gap_count = np.sum(max_gap_per_cell > 0.0)
+            remaining_cell_fraction = 1 - max(max_cell_fraction - deviants_fraction, 0.0)
+            if large_gap_count / cells_count <= remaining_cell_fraction:
+                gap_threshold = 0.0
+            else:
+                gap_threshold = np.quantile(max_gap_per_cell, remaining_cell_fraction)
+            new_deviant_per_cell = (max_gap_per_cell > gap_threshold) & ~deviant_per_cell
+            new_deviants_count = np.sum(new_deviant_per_cell)
+            if new_deviants_count == 0:
+                break
+            deviants_fraction += new_deviants_count / cells_count
+            deviant_per_cell = deviant_per_cell | new_deviant_per_cell
+        if deviants_fraction <= max_cell_fraction:
+            return deviant_per_cell
+        min_gap_per_gene += 1 / 8
+        min_gene_fold_factor += 1 / 8

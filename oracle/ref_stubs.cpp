@@ -1,6 +1,6 @@
 // Test infrastructure (oracle build only).  The reference's module init
 // (/root/reference/metacells/extensions.cpp:64-83) registers 14 function groups; only the
-// hot-path groups are compiled into oracle/_ref.  The six groups that SURVEY.md §2.1 marks out
+// hot-path groups are compiled into oracle/_ref.  The five groups that SURVEY.md §2.1 marks out
 // of scope get empty registration functions here so the module links.
 #include "metacells/extensions.h"
 
@@ -8,7 +8,6 @@ namespace metacells {
 void register_auroc(pybind11::module&) {}
 void register_cover(pybind11::module&) {}
 void register_folds(pybind11::module&) {}
-void register_gaps(pybind11::module&) {}
 void register_logistics(pybind11::module&) {}
 void register_shuffle(pybind11::module&) {}
 }  // namespace metacells
