@@ -828,10 +828,29 @@ def time_candidates(args, umis):
             start = time.perf_counter()
             results = list(pool.map(candidates, range(args.candidate_piles)))
             together_s = time.perf_counter() - start
+        # the whole loop (tools/candidates.py:198-289: re-seeding, splits, minimal cuts) and the deviants pass that follows
+        # it in the pile (pipeline/direct.py:311-322), once each
+        from metacells_b200.candidates import compute_candidate_metacells
+        from metacells_b200.deviants import find_deviant_cells
+
+        rounds = []
+        start = time.perf_counter()
+        candidate = compute_candidate_metacells(graph, cell_umis, random_seed=SEED, trace=rounds)
+        loop_s = time.perf_counter() - start
+        with pipeline.Pile(umis) as pile:
+            gaps = []
+            start = time.perf_counter()
+            deviants = find_deviant_cells(pile, candidate, total_umis_per_cell=cell_umis, trace=gaps)
+            deviants_s = time.perf_counter() - start
     finally:
         graph.close()
     identical = all(np.array_equal(communities, other[0]) and score == other[1] for other in results)
-    return {"metric": "seeds_and_first_partition_optimisation_wall_time", "cells_per_pile": int(cells), "seeds": int(seeds),
+    whole = {"candidates_loop_s": loop_s, "optimisations": sum(step[0] == "optimize" for step in rounds),
+             "candidates": int(candidate.max()) + 1, "deviants_s": deviants_s, "deviants_rounds": len(gaps),
+             "deviant_cells": int(deviants.sum()),
+             "cpu_measured": "profiles/r02_candidates_deviants_16000.json: the oracle's loop 45.0 s (one thread, as the "
+                             "reference's natives are), the reference's compute_cell_gaps loop 3.1 s (16 threads); == both"}
+    return {"whole_loop_and_deviants": whole, "metric": "seeds_and_first_partition_optimisation_wall_time", "cells_per_pile": int(cells), "seeds": int(seeds),
             "one_pile_s": alone_s, "piles_side_by_side": int(args.candidate_piles), "side_by_side_s": together_s,
             "s_per_pile_side_by_side": together_s / args.candidate_piles, "identical_results": bool(identical),
             "note": "mcb_graph_seed_partition on the pile's k-NN graph as it lies on the device (incoming layout, choose_seeds, "

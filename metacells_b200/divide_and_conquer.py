@@ -249,9 +249,10 @@ def metacells_of_phase(cells_count: int, phase: List[dict]) -> Tuple[np.ndarray,
 
 
 def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 0, world_size: int = 1, features=2000,
-                        random_seed: int = 123456, candidates: bool = True, workers: int = 2,
+                        random_seed: int = 123456, candidates=True, workers: int = 2,
                         masses: Optional[np.ndarray] = None, bounds=None, k_arguments: Optional[dict] = None,
-                        times: Optional[dict] = None) -> List[dict]:
+                        times: Optional[dict] = None, deviants: bool = False,
+                        candidates_arguments: Optional[dict] = None) -> List[dict]:
     """One phase of the walk (``_compute_metacells_of_piles``, :1250-1309) as far as this package goes: for every pile
     of ``pile_of_cells`` (the pile index of every atlas cell, -1 = in no pile) the k-NN graph (downsample -> feature
     genes -> log-fraction -> similarity -> balanced graph, direct.py:214-283) and, with ``candidates``, ``choose_seeds``
@@ -259,8 +260,12 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
     largest first (``piles.piles_of_rank``); a rank's ``workers`` host threads take its piles off one list, each pile on
     its thread's own stream, then all its optimisations run side by side, one SM each.  Every pile gets the same
     ``random_seed`` (:1274-1279).  ``masses``: the mass of every cell for the candidates (default: its UMIs, direct.py
-    ``cell_umis``).  Returns, on every rank, one dictionary per pile in pile order: ``cells`` (atlas rows), ``k``,
-    ``edges`` and, with ``candidates``, ``communities`` (int32 per pile cell), ``score``, ``seeds``."""
+    ``cell_umis``).  ``candidates="loop"``: the whole ``compute_candidate_metacells`` loop instead of its opening
+    (``metacells_b200.candidates``, with ``candidates_arguments`` for its parameters in place of ``bounds``); ``deviants``:
+    then also ``find_deviant_cells`` on every pile (``metacells_b200.deviants``; two piles at a time: the dense matrices of a
+    16 000-cell pile take 3.5 GB).  Returns, on every rank, one dictionary per pile in pile order: ``cells`` (atlas rows),
+    ``k``, ``edges`` and, with ``candidates``, ``communities`` (int32 per pile cell), ``score``, ``seeds``, and with
+    ``deviants`` the boolean ``deviants`` mask."""
     rows_of_piles = _rows_of_piles(pile_of_cells)
     sizes = [len(rows) for rows in rows_of_piles]
     mine = pl.piles_of_rank(sizes, rank, world_size)
@@ -297,9 +302,29 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
                 wanted = max(pipeline.seeds_count_for(float(sum(pile_masses)), len(pile_masses), bounds), 1)
                 return pile, graph.seed_partition(pile_masses, bounds, wanted, random_seed=random_seed)
 
+            def whole_loop(entry):
+                from .candidates import compute_candidate_metacells
+
+                pile, graph = entry
+                communities = compute_candidate_metacells(graph, masses[rows_of_piles[pile]], random_seed=random_seed,
+                                                          **(candidates_arguments or {}))
+                return pile, (communities, None, int(communities.max()) + 1)
+
             side_by_side = pipeline.worker_pool(pipeline._side_by_side(None))
-            for pile, (communities, score, seeds) in side_by_side.map(seed_partition, graphs):
+            for pile, (communities, score, seeds) in side_by_side.map(whole_loop if candidates == "loop" else seed_partition,
+                                                                      graphs):
                 results[pile].update(communities=communities, score=score, seeds=seeds)
+            if deviants:
+                def deviants_of(entry):
+                    from .deviants import find_deviant_cells
+
+                    pile = entry[0]
+                    rows = rows_of_piles[pile]
+                    with atlas.pile(rows) as handle:
+                        return pile, find_deviant_cells(handle, results[pile]["communities"], total_umis_per_cell=cell_umis[rows])
+
+                for pile, mask in pool.map(deviants_of, graphs):
+                    results[pile]["deviants"] = mask
     finally:
         for _, graph in graphs:
             graph.close()

@@ -108,6 +108,33 @@ def test_phase_over_the_atlas_matches_pile_by_pile(small_atlas):
         assert result["seeds"] == expected[2] and result["k"] == expected[3]
 
 
+def test_phase_with_the_whole_loop_and_deviants(small_atlas):
+    """`candidates="loop", deviants=True`: every pile's candidates == the oracle's loop on the pile's graph, its deviants
+    == the reference's compute_cell_gaps driven by the oracle's restatement of the Python around it."""
+    from metacells_b200 import divide_and_conquer as dc, piles as pl, pipeline
+    from oracle import oracle
+
+    ref = oracle.load_ref()
+    if ref is None or not hasattr(ref, "compute_cell_gaps"):
+        pytest.skip("oracle/_ref (with gaps.cpp) is not built")
+    pile_of_cells = pl.random_piles(2600, 900, random_seed=123456).astype("int32")
+    arguments = dict(target_metacell_umis=int(48 * float(small_atlas.sum()) / 2600))
+    with dc.Atlas.from_host(small_atlas) as atlas:
+        phase = dc.compute_piles_phase(atlas, pile_of_cells, features=300, random_seed=123456, candidates="loop",
+                                       deviants=True, candidates_arguments=arguments)
+    for pile, result in enumerate(phase):
+        rows = np.flatnonzero(pile_of_cells == pile)
+        umis = small_atlas[rows]
+        graph, cell_umis = pipeline.pile_knn_graph_on_device(umis, features=300, random_seed=123456)
+        try:
+            outgoing, _ = graph.to_scipy()
+        finally:
+            graph.close()
+        expected = oracle.compute_candidate_metacells(outgoing, cell_umis, random_seed=123456, **arguments)
+        assert np.array_equal(result["communities"], expected)
+        assert np.array_equal(result["deviants"], oracle.gaps_deviant_cells(umis, expected, ref))
+
+
 def test_two_phase_walk(small_atlas):
     """Preliminary piles -> metacell groups -> final piles: every cell ends in exactly one final pile and one candidate
     metacell, cells of one preliminary metacell stay together, and the walk is reproducible."""
