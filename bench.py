@@ -283,9 +283,27 @@ def near_gpu_cpus(local_rank):
         words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
         cpus = {64 * index + bit for index, word in enumerate(words) for bit in range(64) if word >> bit & 1}
         cpus &= os.sched_getaffinity(0)
-        return cpus or None
+        if cpus and cpus != os.sched_getaffinity(0):
+            near_gpu_cpus.source = "nvml"
+            return cpus
+        # NVML names every core (round 1's 8-GPU box did): ask the PCI device for its NUMA node instead
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus[4:].lower()) as handle:
+            node = int(handle.read())
+        if node < 0:
+            return cpus or None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as handle:
+            listed = set()
+            for part in handle.read().strip().split(","):
+                first, _, last = part.partition("-")
+                listed.update(range(int(first), int(last or first) + 1))
+        listed &= os.sched_getaffinity(0)
+        near_gpu_cpus.source = "sysfs numa_node %d" % node
+        return listed or cpus or None
     except Exception:  # noqa: BLE001 (NVML missing or the attribute absent: stay where the launcher put us)
         return None
+
+
+near_gpu_cpus.source = "none"
 
 
 def run_gpu_arm(args):
@@ -631,7 +649,8 @@ def run_gpu_arm(args):
         "config": config_of(args, cells, genes, k, samples, umis.nnz), "graph_nnz": int(nnz), "piles_per_step": world,
         "feature_genes_selected": int(features_count),
         "clocks": clocks,
-        "host": {"cpus_near_gpu": len(gpu_cpus) if gpu_cpus else None, "cpus": len(launcher_cpus)},
+        "host": {"cpus_near_gpu": len(gpu_cpus) if gpu_cpus else None, "cpus": len(launcher_cpus),
+                 "affinity_source": near_gpu_cpus.source},
         "e2e": {"value": world * cells * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                 "unpipelined_ms_per_step": e2e_sequential_ms / args.steps,
                 "mode": e2e_mode, "graph_check": graph_check, "one_thread_prefetch_ms_per_step": e2e_prefetch_ms / args.steps,

@@ -314,6 +314,12 @@ int mcb_pile_create_from_atlas(const mcb_atlas* atlas, const int64_t* rows, int6
  * of the grouping pile, divide_and_conquer.py:1153-1245): its non-zeros in column order, as scipy's csr_matrix(dense). */
 int mcb_pile_create_dense_dev(const float* dense, int64_t cells, int64_t genes, mcb_pile** out);
 
+/* sums float64 [groups, genes] (host) = the per-gene UMIs of the pile's cells with group_of_cells[c] == g (host int32
+ * [cells]; negative: left out), of the pile's own (not downsampled) counts: the `data[cells, :].sum(axis=0)` and
+ * `sum_per(data, per="column")` of tools/dissolve.py:101-102, :187-189.  Exact integers, so a sum below 2^24 is the
+ * float32 value numpy computes in any order. */
+int mcb_pile_sum_groups(mcb_pile* pile, const int32_t* group_of_cells, int64_t groups, double* sums);
+
 /* ---- gaps.cpp ------------------------------------------------------------------------------------ */
 
 /* compute_cell_gaps (gaps.cpp:6-186; bound as xt.compute_cell_gaps, tools/deviants.py:309-326): per candidate metacell and

@@ -869,6 +869,52 @@ void mcb_pile_free(mcb_pile* pile) { delete pile; }
 
 }  // extern "C"
 
+// ---- dissolve: per-gene sums of groups of a pile's cells (tools/dissolve.py:101-102, :187-189) ---------------------------
+
+namespace {
+
+// One warp per cell; float64 atomics: sums of UMI counts are exact (below 2^53) in any order.
+__global__ void __launch_bounds__(256) pile_sum_groups_kernel(const float* __restrict__ data, const int32_t* __restrict__ indices,
+                                                             const int32_t* __restrict__ indptr, int64_t rows,
+                                                             const int32_t* __restrict__ group_of_row, int64_t genes,
+                                                             double* __restrict__ sums) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int32_t group = group_of_row[row];
+    if (group < 0) return;
+    double* target = sums + (int64_t)group * genes;
+    for (int e = indptr[row] + lane; e < indptr[row + 1]; e += 32) atomicAdd(&target[indices[e]], (double)data[e]);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcb_pile_sum_groups(mcb_pile* pile, const int32_t* group_of_cells, int64_t groups, double* sums) {
+    MCB_REQUIRE(pile != nullptr && group_of_cells && sums && groups >= 1, "pile: bad arguments");
+    for (int64_t cell = 0; cell < pile->cells; ++cell)
+        MCB_REQUIRE(group_of_cells[cell] < groups, "pile: cell %lld is in group %d of %lld", (long long)cell,
+                    group_of_cells[cell], (long long)groups);
+    cudaStream_t stream = pile->stream;
+    MCB_TRY(wait_for_upload(pile));
+    Scratch d_groups, d_sums;
+    MCB_TRY(d_groups.alloc((size_t)pile->cells * sizeof(int32_t), stream));
+    MCB_TRY(d_sums.alloc((size_t)groups * pile->genes * sizeof(double), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_groups.ptr, group_of_cells, (size_t)pile->cells * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemsetAsync(d_sums.ptr, 0, (size_t)groups * pile->genes * sizeof(double), stream));
+    MCB_PROFILED("pile_sum_groups", stream,
+                 pile_sum_groups_kernel<<<(unsigned)ceil_div(pile->cells, 8), 256, 0, stream>>>(
+                     pile->data, pile->indices, pile->indptr, pile->cells, d_groups.as<int32_t>(), pile->genes,
+                     d_sums.as<double>()));
+    MCB_LAUNCH_CHECK();
+    MCB_TRY(copy_to_host(sums, d_sums.ptr, (size_t)groups * pile->genes * sizeof(double), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+}  // extern "C"
+
 // ---- deviant cells: the dense inputs of compute_cell_gaps, built on the device (tools/deviants.py:270-292) ------------
 
 namespace mcb {

@@ -536,3 +536,42 @@ def compute_piles_candidates(piles: Iterable[sp.csr_matrix], *, features: int = 
     finally:
         for graph, _ in graphs:
             graph.close()
+
+
+def compute_direct_metacells(umis: sp.csr_matrix, *, features="select", random_seed: int = 123456,
+                             must_complete_cover: bool = False, candidates_arguments: Optional[dict] = None,
+                             deviants_arguments: Optional[dict] = None, dissolve_arguments: Optional[dict] = None,
+                             noisy_genes_mask: Optional[np.ndarray] = None) -> dict:
+    """One pile from its UMIs to its metacells, as ``compute_direct_metacells`` walks it (pipeline/direct.py:197-338):
+    downsample -> feature genes -> log fractions -> similarity -> k-NN graph -> ``compute_candidate_metacells`` ->
+    ``find_deviant_cells`` -> ``dissolve_metacells`` (the last two unless ``must_complete_cover``).  The pile is uploaded
+    once; the graph, the candidates session and the dense matrices of the deviants never leave the device.  Returns
+    ``metacell`` (int32 per cell, -1 = outlier), ``candidate``, ``deviant``, ``dissolved``, ``k`` and the graph's ``edges``."""
+    from .candidates import compute_candidate_metacells
+    from .deviants import find_deviant_cells
+    from .dissolve import dissolve_metacells
+
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    samples = int(round(min(max(tl.DOWNSAMPLE_MIN_SAMPLES, np.quantile(cell_umis, tl.DOWNSAMPLE_MIN_CELL_QUANTILE)),
+                            np.quantile(cell_umis, tl.DOWNSAMPLE_MAX_CELL_QUANTILE))))
+    k = knn_k_of_pile(umis.shape[0], cell_umis)
+    with Pile(umis, max_cell_total=float(cell_umis.max(initial=0))) as pile:
+        _start_selection(pile, features)
+        pile.downsample(samples, random_seed)
+        graph = pile.knn_graph(_feature_genes_of(pile, features), k=k)
+        try:
+            candidate = compute_candidate_metacells(graph, cell_umis, random_seed=random_seed,
+                                                    must_complete_cover=must_complete_cover, **(candidates_arguments or {}))
+            result = {"candidate": candidate, "k": graph.k, "edges": graph.nnz}
+        finally:
+            graph.close()
+        if must_complete_cover:  # direct.py:307-309
+            assert candidate.min() == 0
+            result.update(metacell=candidate, deviant=np.zeros(len(candidate), dtype="bool"),
+                          dissolved=np.zeros(len(candidate), dtype="bool"))
+            return result
+        deviant = find_deviant_cells(pile, candidate, total_umis_per_cell=cell_umis, noisy_genes_mask=noisy_genes_mask,
+                                     **(deviants_arguments or {}))
+        metacell, dissolved = dissolve_metacells(pile, candidate, deviant, cell_umis, **(dissolve_arguments or {}))
+    result.update(metacell=metacell, deviant=deviant, dissolved=dissolved)
+    return result

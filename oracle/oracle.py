@@ -967,3 +967,53 @@ def gaps_deviant_cells(umis: sp.csr_matrix, candidates: np.ndarray, ref, *, nois
             return deviant_per_cell
         min_gap_per_gene += 1 / 8
         min_gene_fold_factor += 1 / 8
+
+
+# ---- dissolve_metacells (tools/dissolve.py:81-223) -------------------------------------------------------------------------
+
+
+def dissolve_metacells(umis: sp.spmatrix, candidates: np.ndarray, deviants: Optional[np.ndarray], cell_umis: np.ndarray, *,
+                       target_metacell_size: int = 48, min_metacell_size: int = 12, target_metacell_umis: int = 160000,
+                       min_robust_size_factor: float = 0.5, min_convincing_gene_fold_factor: Optional[float] = 3.0):
+    """``(metacell, dissolved)`` per cell, with scipy on the column-major matrix as the reference has it."""
+    data = sp.csc_matrix(umis)
+    dissolved_of_cells = np.zeros(umis.shape[0], dtype="bool")
+    candidate_of_cells = np.copy(candidates)
+    if deviants is not None:
+        candidate_of_cells[deviants > 0] = -1
+
+    def compress(indices):  # utilities/computation.py:1936-1946
+        unique, consecutive = np.unique(indices, return_inverse=True)
+        consecutive += min(unique[0], 0)
+        return consecutive.astype(indices.dtype)
+
+    candidate_of_cells = compress(candidate_of_cells)
+    candidates_count = np.max(candidate_of_cells) + 1
+    total_per_gene = np.asarray(data.sum(axis=0)).reshape(-1)
+    assert total_per_gene.dtype == np.float32
+    fraction_of_genes = total_per_gene / total_per_gene.sum()
+    min_robust_size = int(math.floor(target_metacell_size * min_robust_size_factor))
+    min_robust_umis = int(math.floor(target_metacell_umis * min_robust_size_factor))
+    did_dissolve = False
+    for candidate_index in range(candidates_count):
+        cell_indices = np.where(candidate_of_cells == candidate_index)[0]
+        size = cell_indices.size
+        if size < min_metacell_size:
+            keep = False
+        elif size >= min_robust_size or np.sum(cell_umis[cell_indices]) >= min_robust_umis:
+            keep = True
+        elif min_convincing_gene_fold_factor is None:
+            keep = True
+        else:
+            data_of_genes = np.asarray(data[cell_indices, :].sum(axis=0)).reshape(-1)
+            expected_of_genes = fraction_of_genes * np.sum(data_of_genes)
+            expected_of_genes += 1
+            data_of_genes += 1
+            data_of_genes /= expected_of_genes
+            np.log2(data_of_genes, out=data_of_genes)
+            keep = bool(np.any(np.abs(data_of_genes) >= min_convincing_gene_fold_factor))
+        if not keep:
+            dissolved_of_cells[cell_indices] = True
+            candidate_of_cells[cell_indices] = -1
+            did_dissolve = True
+    return (compress(candidate_of_cells) if did_dissolve else candidate_of_cells), dissolved_of_cells

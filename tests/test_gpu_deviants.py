@@ -114,3 +114,46 @@ def test_find_deviant_cells_matches_oracle(ref, cells, genes, depth, moved, argu
         assert np.array_equal(my_gaps, their_gaps), (at, np.flatnonzero(my_gaps != their_gaps)[:10])
     assert np.array_equal(deviants, expected)
     assert expected.sum() > 0 and len(theirs) >= 2
+
+
+def test_dissolve_and_the_whole_pile_match_oracle(ref):
+    """`dissolve_metacells` on candidates with tiny, small-but-convincing and small-and-bland members == the oracle's scipy
+    restatement; then `compute_direct_metacells` (graph -> candidates -> deviants -> dissolve on one uploaded pile) == the
+    oracle's steps chained on the same graph."""
+    from metacells_b200.deviants import find_deviant_cells
+    from metacells_b200.dissolve import dissolve_metacells
+    from metacells_b200.pipeline import Pile, compute_direct_metacells, pile_knn_graph_on_device
+
+    cells, genes = 2000, 4000
+    umis = synth_umis(cells, genes, seed=7, depth_scale=3.0)
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    rng = np.random.default_rng(4)
+    candidates = typed_candidates(cells, genes, 7, 60, rng)
+    last = int(candidates.max())
+    candidates[rng.choice(cells, 5, replace=False)] = last + 1   # under the minimal size
+    candidates[np.flatnonzero(candidates == 3)[:20]] = last + 2  # 20 cells of one type: convincing genes
+    candidates[rng.choice(np.flatnonzero(candidates <= last), 18, replace=False)] = last + 3  # 18 random cells: bland
+    deviants = rng.random(cells) < 0.03
+    arguments = dict(target_metacell_umis=int(48 * cell_umis.mean()))
+    folds = dict(min_convincing_gene_fold_factor=3.5, **arguments)  # between the two small candidates' largest folds
+    with Pile(umis) as pile:
+        metacell, dissolved = dissolve_metacells(pile, candidates, deviants, cell_umis, **folds)
+        without_folds = dissolve_metacells(pile, candidates, None, cell_umis, min_convincing_gene_fold_factor=None, **arguments)
+    expected = oracle.dissolve_metacells(umis, candidates, deviants, cell_umis, **folds)
+    assert np.array_equal(metacell, expected[0]) and np.array_equal(dissolved, expected[1])
+    assert dissolved[(candidates == last + 1) & ~deviants].all() and dissolved[(candidates == last + 3) & ~deviants].all()
+    assert not dissolved[candidates == last + 2].any()
+    expected = oracle.dissolve_metacells(umis, candidates, None, cell_umis, min_convincing_gene_fold_factor=None, **arguments)
+    assert np.array_equal(without_folds[0], expected[0]) and np.array_equal(without_folds[1], expected[1])
+
+    whole = compute_direct_metacells(umis, features=1000, candidates_arguments=arguments, dissolve_arguments=arguments)
+    graph, _ = pile_knn_graph_on_device(umis, features=1000)
+    try:
+        outgoing, _ = graph.to_scipy()
+    finally:
+        graph.close()
+    candidate = oracle.compute_candidate_metacells(outgoing, cell_umis, random_seed=123456, **arguments)
+    deviant = oracle.gaps_deviant_cells(umis, candidate, ref)
+    metacell, dissolved = oracle.dissolve_metacells(umis, candidate, deviant, cell_umis, **arguments)
+    assert np.array_equal(whole["candidate"], candidate) and np.array_equal(whole["deviant"], deviant)
+    assert np.array_equal(whole["metacell"], metacell) and np.array_equal(whole["dissolved"], dissolved)
