@@ -12,6 +12,7 @@ parser.add_argument("--steps", type=int, default=3)
 parser.add_argument("--cells", type=int, default=16000)
 parser.add_argument("--genes", type=int, default=27000)
 parser.add_argument("--features", default="select", type=lambda t: t if t == "select" else int(t))
+parser.add_argument("--times", action="store_true", help="print the mean time of every kernel over the steps after the first two")
 args = parser.parse_args()
 library = bench.Library()
 umis, samples, k = bench.make_pile(args.cells, args.genes, bench.SEED)
@@ -21,6 +22,11 @@ resident = {name: torch.from_numpy(array).to(device) for name, array in (("data"
 stream = torch.cuda.current_stream(device)
 p = bench.p
 for step in range(args.steps):
+    if args.times and step == 2:
+        torch.cuda.synchronize()
+        library.call("mcb_profile_enable", ctypes.c_int(1))
+        library.call("mcb_profile_reset")
+        started = torch.cuda.Event(enable_timing=True); started.record(stream)
     pile = ctypes.c_void_p()
     library.call("mcb_pile_create_dev", p(resident["data"].data_ptr()), p(resident["indices"].data_ptr()), p(resident["indptr"].data_ptr()),
                  ctypes.c_int64(args.cells), ctypes.c_int64(args.genes), p(stream.cuda_stream), ctypes.byref(pile))
@@ -46,3 +52,14 @@ for step in range(args.steps):
     library.lib.mcb_graph_free(graph)
     library.lib.mcb_pile_free(pile)
 torch.cuda.synchronize()
+if args.times and args.steps > 2:
+    finished = torch.cuda.Event(enable_timing=True); finished.record(stream); torch.cuda.synchronize()
+    print("ms per step (events enabled): %.3f" % (started.elapsed_time(finished) / (args.steps - 2)))
+    buffer = ctypes.create_string_buffer(8192)
+    library.lib.mcb_profile_names(buffer, ctypes.c_longlong(8192))
+    for name in buffer.value.decode().split("\n"):
+        if name:
+            total, count = ctypes.c_double(0), ctypes.c_longlong(0)
+            library.lib.mcb_profile_read(name.encode(), ctypes.byref(total), ctypes.byref(count))
+            if count.value:
+                print("  %-28s %8.3f ms per step over %d launches" % (name, total.value / (args.steps - 2), count.value))
