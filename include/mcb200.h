@@ -258,6 +258,12 @@ int mcb_pile_gene_columns(mcb_pile* pile, const int32_t* genes, int64_t count, f
  * window is one of its elements, so no arithmetic is involved; a window holding a NaN or an infinity yields NaN, as pandas'
  * rolling median does (it takes infinities for missing values). */
 int mcb_host_sliding_median_f32(const float* values, int64_t count, int64_t window, float* medians);
+/* The whole of sliding_window_function(values, "median", window, order_by) (computation.py:1836-1897) but its argsort:
+ * `order` (int64[count], host) sorts the entries by `order_by`; medians[e] (float64[count], host) = the median of the
+ * `window` entries nearest to entry e in that order, the windows at both ends padded as the reference pads them
+ * (:1877-1883).  The gathers by `order`, the padding and the scatter back happen on the device. */
+int mcb_host_sliding_median_ordered_f32(const float* values, const int64_t* order, int64_t count, int64_t window,
+                                        double* medians);
 
 /* direct.py:242-249 -> computation.py:679-741 (log_data): the dense float32 [cells, features] operand of the similarity,
  * dense_host[c, f] = log_table[count of gene feature_genes[f] in cell c] (log_table[c] = np.log2(float32(c) +

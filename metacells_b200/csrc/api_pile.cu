@@ -576,7 +576,6 @@ __global__ void __launch_bounds__(256) sliding_median_kernel(const float* __rest
     }
     const int half = window / 2;
     float median = 0.0f;
-    bool found = false;
     for (int j = 0; j < window; ++j) {
         const float candidate = __shfl_sync(0xffffffffu, mine[j >> 5], j & 31);
         int smaller = 0, not_larger = 0;
@@ -588,12 +587,60 @@ __global__ void __launch_bounds__(256) sliding_median_kernel(const float* __rest
             }
         smaller = warp_reduce_sum(smaller);
         not_larger = warp_reduce_sum(not_larger);
-        if (!found && smaller <= half && half < not_larger) {
+        if (smaller <= half && half < not_larger) {  // the same for every lane: the counts are warp sums
             median = candidate;
-            found = true;
+            break;
         }
     }
     if (lane == 0) out[i] = median;
+}
+
+// The same medians for sliding_window_function(values, order_by=...) (utilities/computation.py:1836-1897) without the
+// host's gathers: `order` sorts the entries by `order_by`; the window of the entry at sorted place i covers the places
+// i - half .. i + half, the windows at both ends padded with the places the reference pads them with (:1877-1883); the
+// median goes to the entry's own index, as float64 (what `values - medians` needs).
+__global__ void __launch_bounds__(256) sliding_median_ordered_kernel(const float* __restrict__ values, const int64_t* __restrict__ order,
+                                                                    int64_t count, int window, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= count) return;
+    const int half = window / 2;
+    float mine[4];
+    bool finite = true;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int64_t padded = i + lane + 32 * u;  // place in [before | order | after]
+        mine[u] = 0.0f;
+        if (lane + 32 * u < window) {
+            const int64_t place = padded < half ? window - half + padded
+                                  : padded < half + count ? padded - half : count - window + (padded - half - count);
+            mine[u] = values[order[place]];
+            finite = finite && isfinite(mine[u]);
+        }
+    }
+    const int64_t target = order[i];
+    if (!__all_sync(0xffffffffu, finite)) {
+        if (lane == 0) out[target] = __longlong_as_double(0x7ff8000000000000ll);
+        return;
+    }
+    float median = 0.0f;
+    for (int j = 0; j < window; ++j) {
+        const float candidate = __shfl_sync(0xffffffffu, mine[j >> 5], j & 31);
+        int smaller = 0, not_larger = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (lane + 32 * u < window) {
+                smaller += mine[u] < candidate ? 1 : 0;
+                not_larger += mine[u] <= candidate ? 1 : 0;
+            }
+        smaller = warp_reduce_sum(smaller);
+        not_larger = warp_reduce_sum(not_larger);
+        if (smaller <= half && half < not_larger) {
+            median = candidate;
+            break;
+        }
+    }
+    if (lane == 0) out[target] = (double)median;
 }
 
 int check_atlas_indptr(const int64_t* indptr, int64_t cells) {
@@ -795,6 +842,27 @@ int mcb_host_sliding_median_f32(const float* values, int64_t count, int64_t wind
                                                                                          d_out.as<float>()));
     MCB_LAUNCH_CHECK();
     MCB_TRY(copy_to_host(medians, d_out.ptr, (size_t)outputs * sizeof(float), stream));
+    MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+int mcb_host_sliding_median_ordered_f32(const float* values, const int64_t* order, int64_t count, int64_t window,
+                                        double* medians) {
+    MCB_REQUIRE(values && order && medians && window >= 1 && (window & 1) == 1 && window <= 127 && count > window,
+                "sliding_median: needs an odd window of at most 127 and more entries than the window");
+    cudaStream_t stream = nullptr;
+    MCB_TRY(thread_stream(&stream));
+    Scratch d_values, d_order, d_out;
+    MCB_TRY(d_values.alloc((size_t)count * sizeof(float), stream));
+    MCB_TRY(d_order.alloc((size_t)count * sizeof(int64_t), stream));
+    MCB_TRY(d_out.alloc((size_t)count * sizeof(double), stream));
+    MCB_CUDA(cudaMemcpyAsync(d_values.ptr, values, (size_t)count * sizeof(float), cudaMemcpyHostToDevice, stream));
+    MCB_CUDA(cudaMemcpyAsync(d_order.ptr, order, (size_t)count * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    MCB_PROFILED("sliding_median", stream,
+                 sliding_median_ordered_kernel<<<(unsigned)ceil_div(count, 8), 256, 0, stream>>>(
+                     d_values.as<float>(), d_order.as<int64_t>(), count, (int)window, d_out.as<double>()));
+    MCB_LAUNCH_CHECK();
+    MCB_TRY(copy_to_host(medians, d_out.ptr, (size_t)count * sizeof(double), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
     return MCB_OK;
 }

@@ -69,7 +69,38 @@ def _device_window_medians(values: np.ndarray, window_size: int) -> np.ndarray:
     return medians.astype("float64")
 
 
-def _sliding_median(values: np.ndarray, order_by: np.ndarray, window_size: int, window_medians=None) -> np.ndarray:
+def _device_ordered_medians(values: np.ndarray, order: np.ndarray, window_size: int) -> np.ndarray:
+    """The medians of ``_sliding_median`` for a given ``order = argsort(order_by)``, in entry order (float64): the gathers,
+    the padding of the end windows and the way back all on the GPU (``mcb_host_sliding_median_ordered_f32``)."""
+    import ctypes
+
+    from ._lib import check, lib
+
+    values = np.ascontiguousarray(values, dtype="float32")
+    order = np.ascontiguousarray(order, dtype="int64")
+    medians = np.empty(len(values), dtype="float64")
+    function = lib().mcb_host_sliding_median_ordered_f32
+    function.restype = ctypes.c_int
+    check(function(ctypes.c_void_p(values.ctypes.data), ctypes.c_void_p(order.ctypes.data), ctypes.c_int64(len(values)),
+                   ctypes.c_int64(window_size), ctypes.c_void_p(medians.ctypes.data)))
+    return medians
+
+
+_sorter = None
+
+
+def _argsort_meanwhile(order_by: np.ndarray):
+    """``np.argsort(order_by)`` on a helper thread (numpy sorts without the interpreter lock): the variance arithmetic of
+    the caller runs beside it.  The order of equal keys is numpy's own and part of the result, so numpy does the sort."""
+    global _sorter
+    if _sorter is None:
+        from concurrent.futures import ThreadPoolExecutor
+
+        _sorter = ThreadPoolExecutor(max_workers=4, thread_name_prefix="mcb-argsort")
+    return _sorter.submit(np.argsort, order_by)
+
+
+def _sliding_median(values: np.ndarray, order_by: np.ndarray, window_size: int, window_medians=None, order=None) -> np.ndarray:
     """``sliding_window_function(values, function="median", window_size=..., order_by=...)`` (computation.py:1836-1897):
     the median of the ``window_size`` entries nearest in ``order_by``, the windows at both ends padded with the entries
     the reference pads them with.  ``window_medians(values, window_size)``: the medians of all whole windows (default: on
@@ -80,7 +111,12 @@ def _sliding_median(values: np.ndarray, order_by: np.ndarray, window_size: int, 
     count = len(values)
     if window_size >= count:
         return np.full(count, np.median(values))
-    order = np.argsort(order_by)
+    if order is None:
+        order = np.argsort(order_by)
+    elif hasattr(order, "result"):
+        order = order.result()
+    if window_medians is None and window_size <= 127:
+        return _device_ordered_medians(values, order, window_size)
     back = np.empty(count, dtype=order.dtype)  # == np.argsort(order): the inverse of a permutation, by scatter
     back[order] = np.arange(count, dtype=order.dtype)
     padded = np.concatenate([order[window_size - half:window_size], order, order[count - window_size:count - window_size + half]])
@@ -101,6 +137,7 @@ def relative_variance_of_genes(sums: np.ndarray, sums_squared: np.ndarray, cells
     variance /= cells
     variance[variance < 0] = 0
     mean = sums / cells
+    order = _argsort_meanwhile(mean) if len(mean) > max(window_size, 4096) else None
     silent = mean == 0
     normalized = np.reciprocal(mean, where=~silent)
     normalized[silent] = 0
@@ -108,7 +145,7 @@ def relative_variance_of_genes(sums: np.ndarray, sums_squared: np.ndarray, cells
     normalized[silent] = 1.0
     with np.errstate(divide="ignore"):
         np.log2(normalized, out=normalized)
-    return normalized - _sliding_median(normalized, mean, window_size, window_medians)
+    return normalized - _sliding_median(normalized, mean, window_size, window_medians, order)
 
 
 def select_feature_genes(pile, *, min_gene_relative_variance: Optional[float] = SELECT_MIN_GENE_RELATIVE_VARIANCE,

@@ -388,3 +388,34 @@ def test_bench_pile_with_selected_genes(ref):
         return
     with open(GOLDEN) as handle:
         assert json.load(handle).get(key) == digest, "the digest of the bench pile's graph (selected genes) is not the pinned one"
+
+
+def test_bench_pile_to_metacells(ref):
+    """The bench pile all the way (`pipeline.compute_direct_metacells`: graph -> the whole candidates loop -> deviant cells
+    -> dissolve on one uploaded pile) == the oracle's chain on the same graph: its restatement of tools/candidates.py around
+    the pinned natives, the REFERENCE's compute_cell_gaps under tools/deviants.py, scipy's dissolve.  (The oracle's loop
+    takes ~45 s of one host core at this size.)"""
+    import bench
+    from metacells_b200 import pipeline
+
+    if not hasattr(ref, "compute_cell_gaps"):
+        pytest.skip("oracle/_ref was built without gaps.cpp")
+    umis, _, _ = bench.make_pile(CELLS, GENES, SEED)
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    whole = pipeline.compute_direct_metacells(umis, features="select", random_seed=SEED)
+    graph, _ = pipeline.pile_knn_graph_on_device(umis, features="select", random_seed=SEED)
+    try:
+        outgoing, _ = graph.to_scipy()
+    finally:
+        graph.close()
+    with open(GOLDEN) as handle:
+        assert bench.graph_digest(outgoing.data, outgoing.indices, outgoing.indptr) == json.load(handle)[
+            f"{CELLS}x{GENES}xselect@{SEED}"], "not the graph bench.py times"
+    candidate = oracle.compute_candidate_metacells(outgoing, cell_umis, random_seed=SEED)
+    assert np.array_equal(whole["candidate"], candidate)
+    deviant = oracle.gaps_deviant_cells(umis, candidate, ref)
+    assert np.array_equal(whole["deviant"], deviant)
+    metacell, dissolved = oracle.dissolve_metacells(umis, candidate, deviant, cell_umis)
+    assert np.array_equal(whole["metacell"], metacell) and np.array_equal(whole["dissolved"], dissolved)
+    print(f"bench pile: {int(candidate.max()) + 1} candidates, {int(deviant.sum())} deviant cells, "
+          f"{int(dissolved.sum())} dissolved cells, {int(metacell.max()) + 1} metacells")

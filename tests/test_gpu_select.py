@@ -90,6 +90,26 @@ def test_sliding_median_matches_pandas():
     assert np.isnan(select._device_window_medians(np.array([1, -np.inf, 3], dtype="float32"), 3)).all()
 
 
+def test_ordered_sliding_median_matches_the_host_path():
+    """`mcb_host_sliding_median_ordered_f32` (gathers, end padding and the way back on the device) == the host's gathers
+    around pandas' rolling median, as sliding_window_function does them (computation.py:1866-1897), ties in the order
+    included."""
+    from test_select_host import pandas_window_medians
+
+    from metacells_b200 import select
+
+    rng = np.random.default_rng(12)
+    for count, window in ((27000, 101), (150, 101), (5000, 7), (1000, 127)):
+        values = rng.normal(size=count).astype("float32")
+        values[rng.choice(count, 3, replace=False)] = [-np.inf, np.inf, np.nan]
+        order_by = rng.integers(0, count // 4, size=count).astype("float32")  # many equal keys: numpy's order of them counts
+        expected = select._sliding_median(values, order_by, window, window_medians=pandas_window_medians)
+        mine = select._sliding_median(values, order_by, window)
+        assert mine.dtype == np.float64 and np.array_equal(mine, expected, equal_nan=True), (count, window)
+        ahead = select._sliding_median(values, order_by, window, order=select._argsort_meanwhile(order_by))
+        assert np.array_equal(ahead, expected, equal_nan=True)
+
+
 def test_pile_graph_on_selected_genes_matches_the_staged_path():
     """`features="select"` through the pile pipeline == selecting with the oracle and building the graph stage by stage."""
     from synth import synth_umis
