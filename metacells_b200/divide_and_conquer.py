@@ -290,7 +290,7 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
     for pile in [pile for pile in mine if sizes[pile] < 3]:  # too small for a graph: one community
         results[pile] = {"cells": rows_of_piles[pile], "k": 0, "edges": 0, "communities": np.zeros(sizes[pile], dtype="int32"),
                          "score": 0.0, "seeds": 1}
-    graphs = list(pool.map(build, [pile for pile in mine if sizes[pile] >= 3]))
+    graphs = list(pool.map(pl.retrying(build), [pile for pile in mine if sizes[pile] >= 3]))  # a failed pile is done again
     graphs_seconds = time.perf_counter() - started
     try:
         for pile, graph in graphs:

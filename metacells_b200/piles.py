@@ -14,7 +14,7 @@ from typing import Any, Callable, Dict, List, Optional, Sequence
 
 import numpy as np
 
-__all__ = ["random_piles", "piles_of_rank", "map_piles"]
+__all__ = ["random_piles", "piles_of_rank", "map_piles", "retrying"]
 
 
 def random_piles(elements_count: int, target_pile_size: int, *, random_seed: int) -> np.ndarray:
@@ -57,11 +57,33 @@ def piles_of_rank(pile_sizes: Sequence[int], rank: int, world_size: int) -> List
     return sorted(mine)
 
 
+def retrying(process: Callable[..., Any], attempts: int = 2) -> Callable[..., Any]:
+    """``process`` run again (up to ``attempts`` times in all) when it raises an ``McbError``: a pile is a pure function of
+    its cells and the seed, so a pile whose step failed on the device (an allocation under memory pressure from the piles
+    beside it, a transient launch failure) is simply done again; the last failure is raised.  Argument errors
+    (``ValueError``, ``AssertionError``...) are not retried."""
+    from ._lib import McbError
+
+    def process_again(*arguments, **keywords):
+        for attempt in range(attempts):
+            try:
+                return process(*arguments, **keywords)
+            except McbError:
+                if attempt + 1 == attempts:
+                    raise
+        raise AssertionError("unreachable")
+
+    return process_again
+
+
 def map_piles(pile_of_cells: np.ndarray, process_pile: Callable[[int, np.ndarray], Any], *, rank: int = 0,
-              world_size: int = 1, gather: Optional[Callable[[Dict[int, Any]], List[Dict[int, Any]]]] = None) -> List[Any]:
+              world_size: int = 1, gather: Optional[Callable[[Dict[int, Any]], List[Dict[int, Any]]]] = None,
+              attempts: int = 2) -> List[Any]:
     """Run ``process_pile(pile_index, cell_indices)`` for the piles of this rank and return the results of ALL
     piles in pile order on every rank.  ``gather`` exchanges the per-rank dictionaries; the default uses
-    ``torch.distributed.all_gather_object`` on the default process group (no exchange when ``world_size`` is 1)."""
+    ``torch.distributed.all_gather_object`` on the default process group (no exchange when ``world_size`` is 1).  A pile
+    whose processing raises an ``McbError`` is processed again (``attempts`` times in all, see ``retrying``)."""
+    process_pile = retrying(process_pile, attempts)
     pile_of_cells = np.asarray(pile_of_cells)
     piles_count = int(pile_of_cells.max()) + 1
     sizes = np.bincount(pile_of_cells, minlength=piles_count)

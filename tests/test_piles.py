@@ -97,3 +97,38 @@ def test_row_blocks_cover_the_matrix(rows, world):
     assert all(blocks[rank][1] == blocks[rank + 1][0] for rank in range(world - 1))
     widths = [last - first for first, last in blocks]
     assert max(widths) - min(widths) <= 1 and widths[0] == max(widths)
+
+
+def test_a_failed_pile_is_processed_again():
+    """A pile whose step raises McbError (a device-side failure) is run once more; the second failure is raised; errors of
+    the arguments are not retried."""
+    from metacells_b200 import piles as pl
+    from metacells_b200._lib import McbError
+
+    pile_of_cells = np.array([0, 1, 0, 2, 1, 2, 2], dtype="int32")
+    calls = []
+
+    def flaky(pile, cells):
+        calls.append(pile)
+        if pile == 1 and calls.count(1) == 1:
+            raise McbError("out of memory")
+        return int(cells.sum())
+
+    assert pl.map_piles(pile_of_cells, flaky) == [2, 5, 14]
+    assert calls.count(1) == 2 and calls.count(0) == 1
+
+    def broken(pile, cells):
+        calls.append(("broken", pile))
+        raise McbError("still out of memory")
+
+    with pytest.raises(McbError):
+        pl.map_piles(pile_of_cells, broken)
+    assert calls.count(("broken", 0)) == 2
+
+    def wrong(pile, cells):
+        calls.append(("wrong", pile))
+        raise ValueError("bad argument")
+
+    with pytest.raises(ValueError):
+        pl.map_piles(pile_of_cells, wrong)
+    assert calls.count(("wrong", 0)) == 1
