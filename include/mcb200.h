@@ -209,6 +209,16 @@ void mcb_graph_free(mcb_graph* graph);
 typedef struct mcb_pile mcb_pile;
 int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_t* indptr, int64_t cells, int64_t genes,
                          mcb_pile** out);
+/* The same pile from a COMPACT host copy: 16-bit gene indices (at most 65536 genes), 8-bit counts, 3 bytes per non-zero
+ * instead of 8 on the host link, which is what bounds the end-to-end step.  A count of 255 stands
+ * for "see the escape list": escape_at int64[escapes] (positions in the arrays, ascending) and escape_values
+ * float32[escapes] hold the counts of 255 and more (and any count that is not a whole number).  The chunks are widened on
+ * the device, on the copy stream, to the float32 / int32 arrays the path reads; every mcb_pile_* call then works as on a
+ * pile of mcb_pile_create_host, bit for bit.  No counterpart in the reference (its callers hold scipy CSR float32 /
+ * int32): for callers that keep an atlas compact on the host or on disk. */
+int mcb_pile_create_host_compact(const uint16_t* indices, const uint8_t* counts, const int32_t* indptr, int64_t cells,
+                                 int64_t genes, const int64_t* escape_at, const float* escape_values, int64_t escapes,
+                                 mcb_pile** out);
 /* Optional: the largest total of a cell (the pipeline has the totals on the host, tools/downsample.py:84-90).
  * Sizes the downsampling scratch without a pass over the data and a synchronisation; a cell above it is
  * reported by the next synchronising call on the pile. */

@@ -40,6 +40,7 @@ struct mcb_pile {
     const float* data = nullptr;
     const int32_t* indices = nullptr;
     const int32_t* indptr = nullptr;
+    Scratch compact_indices, compact_counts, escape_at, escape_values;  // the staging of mcb_pile_create_host_compact
     Scratch downsampled;  // same sparsity structure as `data`
     bool has_downsampled = false;
     Scratch gene_totals;  // float32[genes]: per-gene totals of `downsampled`, added up by the downsample kernels
@@ -162,6 +163,108 @@ int mcb_pile_create_host(const float* data, const int32_t* indices, const int32_
         cudaEvent_t ready;
         MCB_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
         MCB_CUDA(cudaEventRecord(ready, pile->copy_stream));
+        pile->chunk_ready.push_back(ready);
+        pile->chunk_rows.push_back(row);
+    }
+    pile->data = pile->own_data.as<float>();
+    pile->indices = pile->own_indices.as<int32_t>();
+    pile->indptr = pile->own_indptr.as<int32_t>();
+    *out = pile.release();
+    return MCB_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// A chunk of a compact pile (16-bit gene indices, 8-bit counts, 255 = the count is in the sorted escape list) widened to
+// the float32 / int32 arrays every kernel of the path reads.
+__global__ void __launch_bounds__(256) widen_compact_kernel(const uint16_t* __restrict__ indices16, const uint8_t* __restrict__ counts8,
+                                                           int64_t begin, int64_t end, const int64_t* __restrict__ escape_at,
+                                                           const float* __restrict__ escape_values, int64_t escapes,
+                                                           float* __restrict__ data, int32_t* __restrict__ indices) {
+    for (int64_t at = begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; at < end; at += (int64_t)gridDim.x * blockDim.x) {
+        indices[at] = (int32_t)indices16[at];
+        const uint8_t count = counts8[at];
+        float value = (float)count;
+        if (count == 255) {  // rare: a binary search for the entry's place in the escape list
+            int64_t low = 0, high = escapes;
+            while (low < high) {
+                const int64_t middle = (low + high) >> 1;
+                if (escape_at[middle] < at) low = middle + 1; else high = middle;
+            }
+            if (low < escapes && escape_at[low] == at) value = escape_values[low];
+        }
+        data[at] = value;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcb_pile_create_host_compact(const uint16_t* indices, const uint8_t* counts, const int32_t* indptr, int64_t cells,
+                                 int64_t genes, const int64_t* escape_at, const float* escape_values, int64_t escapes,
+                                 mcb_pile** out) {
+    MCB_REQUIRE(out && cells >= 1 && genes >= 1 && genes <= 65536, "pile: bad arguments (a compact pile has at most 65536 genes)");
+    MCB_REQUIRE(escapes >= 0 && (escapes == 0 || (escape_at && escape_values)), "pile: bad escape list");
+    for (int64_t e = 1; e < escapes; ++e)
+        MCB_REQUIRE(escape_at[e - 1] < escape_at[e], "pile: the escape list must be sorted by position");
+    std::unique_ptr<mcb_pile> pile(new mcb_pile());
+    pile->cells = cells;
+    pile->genes = genes;
+    MCB_TRY(finish_create(pile.get(), indptr));
+    MCB_TRY(thread_stream(&pile->stream));
+    cudaStream_t stream = pile->stream;
+    MCB_TRY(pile->own_data.alloc((size_t)pile->nnz * sizeof(float), stream));
+    MCB_TRY(pile->own_indices.alloc((size_t)pile->nnz * sizeof(int32_t), stream));
+    MCB_TRY(pile->own_indptr.alloc((size_t)(cells + 1) * sizeof(int32_t), stream));
+    MCB_TRY(pile->compact_indices.alloc((size_t)pile->nnz * sizeof(uint16_t), stream));
+    MCB_TRY(pile->compact_counts.alloc((size_t)pile->nnz, stream));
+    MCB_TRY(pile->escape_at.alloc((size_t)std::max<int64_t>(escapes, 1) * sizeof(int64_t), stream));
+    MCB_TRY(pile->escape_values.alloc((size_t)std::max<int64_t>(escapes, 1) * sizeof(float), stream));
+    MCB_TRY(pile->status.alloc(sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(pile->status.ptr, 0, sizeof(int), stream));
+    MCB_CUDA(cudaStreamCreateWithFlags(&pile->copy_stream, cudaStreamNonBlocking));
+    cudaEvent_t allocated;
+    MCB_CUDA(cudaEventCreateWithFlags(&allocated, cudaEventDisableTiming));
+    MCB_CUDA(cudaEventRecord(allocated, stream));
+    MCB_CUDA(cudaStreamWaitEvent(pile->copy_stream, allocated, 0));
+    cudaEventDestroy(allocated);
+    cudaStream_t copy = pile->copy_stream;
+    MCB_CUDA(cudaMemcpyAsync(pile->own_indptr.ptr, indptr, (size_t)(cells + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, copy));
+    if (escapes > 0) {
+        MCB_CUDA(cudaMemcpyAsync(pile->escape_at.ptr, escape_at, (size_t)escapes * sizeof(int64_t), cudaMemcpyHostToDevice, copy));
+        MCB_CUDA(cudaMemcpyAsync(pile->escape_values.ptr, escape_values, (size_t)escapes * sizeof(float), cudaMemcpyHostToDevice, copy));
+    }
+    int chunks = pile->nnz >= (8 << 20) ? 8 : 1;
+    if (const char* forced = getenv("MCB_PILE_CHUNKS"))  // developer aid
+        chunks = std::max(1, atoi(forced));
+    pile->chunk_rows.push_back(0);
+    for (int c = 1; c <= chunks; ++c) {
+        int64_t row = cells;
+        if (c < chunks) {
+            const int64_t want = pile->nnz / chunks * c;
+            row = std::lower_bound(indptr, indptr + cells + 1, (int32_t)want) - indptr;
+            row = std::min<int64_t>(std::max<int64_t>(row, pile->chunk_rows.back()), cells);
+        }
+        const int64_t begin = indptr[pile->chunk_rows.back()], end = indptr[row];
+        if (end > begin) {
+            MCB_CUDA(cudaMemcpyAsync(pile->compact_indices.as<uint16_t>() + begin, indices + begin,
+                                     (size_t)(end - begin) * sizeof(uint16_t), cudaMemcpyHostToDevice, copy));
+            MCB_CUDA(cudaMemcpyAsync(pile->compact_counts.as<uint8_t>() + begin, counts + begin, (size_t)(end - begin),
+                                     cudaMemcpyHostToDevice, copy));
+            const unsigned blocks = (unsigned)std::min<int64_t>(ceil_div(end - begin, 256 * 8), 148 * 8);
+            MCB_PROFILED("widen_compact", copy,
+                         widen_compact_kernel<<<blocks, 256, 0, copy>>>(
+                             pile->compact_indices.as<uint16_t>(), pile->compact_counts.as<uint8_t>(), begin, end,
+                             pile->escape_at.as<int64_t>(), pile->escape_values.as<float>(), escapes,
+                             pile->own_data.as<float>(), pile->own_indices.as<int32_t>()));
+            MCB_LAUNCH_CHECK();
+        }
+        cudaEvent_t ready;
+        MCB_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+        MCB_CUDA(cudaEventRecord(ready, copy));
         pile->chunk_ready.push_back(ready);
         pile->chunk_rows.push_back(row);
     }

@@ -87,6 +87,34 @@ def _side_by_side(workers: Optional[int]) -> int:
     return count.value
 
 
+class CompactPile:
+    """The compact host copy of a pile (``compact_csr``): ``indices`` uint16, ``counts`` uint8 (255: see the escapes),
+    ``indptr`` int32, ``escape_at`` int64 (ascending positions) and ``escape_values`` float32, ``shape``."""
+
+    def __init__(self, indices, counts, indptr, escape_at, escape_values, shape):
+        self.indices, self.counts, self.indptr = indices, counts, indptr
+        self.escape_at, self.escape_values, self.shape = escape_at, escape_values, shape
+
+    @property
+    def nbytes(self) -> int:
+        return sum(array.nbytes for array in (self.indices, self.counts, self.indptr, self.escape_at, self.escape_values))
+
+
+def compact_csr(umis: sp.csr_matrix) -> CompactPile:
+    """A UMI matrix (CSR, at most 65 536 genes) in the 3-bytes-per-non-zero form ``Pile.from_compact`` uploads: 16-bit gene
+    indices, 8-bit counts; counts of 255 and more, and counts that are not whole numbers, go to a list of escapes."""
+    umis = sp.csr_matrix(umis)
+    if umis.shape[1] > 65536:
+        raise ValueError("a compact pile has at most 65536 genes")
+    data = np.asarray(umis.data, dtype="float32")
+    escaped = ~((data >= 0) & (data < 255) & (data == np.floor(data)))
+    counts = np.where(escaped, 255, data).astype("uint8")
+    escape_at = np.flatnonzero(escaped).astype("int64")
+    return CompactPile(np.ascontiguousarray(umis.indices.astype("uint16")), np.ascontiguousarray(counts),
+                       np.ascontiguousarray(umis.indptr, dtype="int32"), escape_at,
+                       np.ascontiguousarray(data[escape_at], dtype="float32"), umis.shape)
+
+
 class Pile:
     """A device-resident pile (cells x genes UMI CSR matrix)."""
 
@@ -128,6 +156,21 @@ class Pile:
         pile._handle = handle
         pile.samples = None
         pile.gene_top_threshold = None
+        return pile
+
+    @classmethod
+    def from_compact(cls, compact: "CompactPile", *, max_cell_total: Optional[float] = None) -> "Pile":
+        """A pile uploaded from its compact host copy (``compact_csr``): 3 bytes per non-zero on the host link instead of
+        8 (``mcb_pile_create_host_compact``); on the device it is the pile ``Pile(umis)`` makes."""
+        pile = cls._adopt(ctypes.c_void_p(), compact.shape)
+        pile._compact = compact  # the arrays stay alive while the asynchronous upload runs
+        function = lib().mcb_pile_create_host_compact
+        function.restype = ctypes.c_int
+        check(function(_ptr(compact.indices), _ptr(compact.counts), _ptr(compact.indptr), ctypes.c_int64(compact.shape[0]),
+                       ctypes.c_int64(compact.shape[1]), _ptr(compact.escape_at), _ptr(compact.escape_values),
+                       ctypes.c_int64(len(compact.escape_at)), ctypes.byref(pile._handle)))
+        if max_cell_total is not None:
+            pile.set_max_cell_total(max_cell_total)
         return pile
 
     @classmethod
@@ -205,13 +248,16 @@ class Pile:
         self.samples = int(samples)
 
     def downsampled(self) -> sp.csr_matrix:
-        if self._data is None:
+        compact = getattr(self, "_compact", None)
+        if self._data is None and compact is None:
             raise NotImplementedError("a pile gathered on the device keeps no host copy of its structure")
-        data = np.empty(len(self._data), dtype="float32")
+        indices = self._indices.copy() if compact is None else compact.indices.astype("int32")
+        indptr = (self._indptr if compact is None else compact.indptr).copy()
+        data = np.empty(len(indices), dtype="float32")
         function = lib().mcb_pile_read_downsampled
         function.restype = ctypes.c_int
         check(function(self._handle, _ptr(data)))
-        return sp.csr_matrix((data, self._indices.copy(), self._indptr.copy()), shape=self.shape)
+        return sp.csr_matrix((data, indices, indptr), shape=self.shape)
 
     def want_gene_statistics(self, min_top_value: float) -> None:
         """Before ``downsample``: have its kernel add up the per-gene statistics the feature-gene selection starts from

@@ -1,0 +1,4 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_compact.py -x -q -m gpu > gpurun_out/r2y_t_compact.log 2>&1
+echo "rc $?" >> gpurun_out/r2y_t_compact.log
