@@ -107,6 +107,7 @@ static inline int copy_to_host(void* host, const void* device, size_t bytes, cud
 int sm_count();
 int allow_dynamic_shared(const void* kernel, size_t bytes);  // opt in to `bytes` of dynamic shared memory (only ever raised)
 int thread_stream(cudaStream_t* stream);  // the calling host thread's own stream on the current device
+int thread_side_stream(cudaStream_t* side, cudaEvent_t* fork, cudaEvent_t* join);  // that thread's second stream, with a fork and a join event
 // Developer aid: with MCB_TRACE=1 in the environment, synchronises `stream` and prints the host time
 // since the previous call on stderr.
 void trace_lap(const char* name, cudaStream_t stream);

@@ -527,13 +527,14 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     // (1)-(3) without the transposition (prune_mirror.cuh) when every band fits a warp's registers
     bool mirrored = outgoing_degree >= 1 && getenv("MCB_PRUNE_RELAYOUT") == nullptr;
     if (mirrored) {
-        Scratch cuts, padded_data, padded_indices, kept_sizes, overflow;
+        Scratch cuts, padded_data, padded_indices, kept_sizes, overflow, class_rows;
         MCB_TRY(cuts.alloc((size_t)n * sizeof(RowCut), stream));
         MCB_TRY(padded_data.alloc((size_t)n * outgoing_degree * sizeof(float), stream));
         MCB_TRY(padded_indices.alloc((size_t)n * outgoing_degree * sizeof(int32_t), stream));
         MCB_TRY(kept_sizes.alloc((size_t)n * sizeof(int32_t), stream));
-        MCB_TRY(overflow.alloc(sizeof(int), stream));
-        MCB_CUDA(cudaMemsetAsync(overflow.ptr, 0, sizeof(int), stream));
+        MCB_TRY(overflow.alloc(4 * sizeof(int), stream));  // [0]: the overflow flag, [1..3]: the sizes of the band classes
+        MCB_CUDA(cudaMemsetAsync(overflow.ptr, 0, 4 * sizeof(int), stream));
+        MCB_TRY(class_rows.alloc((size_t)3 * n * sizeof(int32_t), stream));
         MirrorParams mp{};
         mp.data = balanced.data.as<float>();
         mp.indices = balanced.indices.as<int32_t>();
@@ -551,22 +552,35 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
         mp.padded_indices = padded_indices.as<int32_t>();
         mp.sizes = kept_sizes.as<int32_t>();
         mp.overflow = overflow.as<int>();
+        mp.class_rows = class_rows.as<int32_t>();
+        mp.class_counts = overflow.as<int>() + 1;
         const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n * 32, 256), (int64_t)sm_count() * 8);
         MCB_PROFILED("row_cuts", stream, row_cuts_kernel<<<grid, 256, 0, stream>>>(mp));
         MCB_LAUNCH_CHECK();
         const unsigned narrow_grid = (unsigned)std::min<int64_t>(ceil_div(n * 32, 128), (int64_t)sm_count() * 16);
+        // The few bands wider than 2048 entries (the hub cells of a pile) take one warp each for a long time: they start
+        // first, on the thread's second stream, and the two classes that hold the rows run beside them.
+        cudaStream_t side = nullptr;
+        cudaEvent_t fork = nullptr, join = nullptr;
+        const bool hubs = balanced.widest > 32 * MP_MAX_ROUNDS;
+        if (hubs) {
+            MCB_TRY(thread_side_stream(&side, &fork, &join));
+            MCB_CUDA(cudaEventRecord(fork, stream));
+            MCB_CUDA(cudaStreamWaitEvent(side, fork, 0));
+            const size_t cache_bytes = (size_t)4 * MP_CACHE * sizeof(uint32_t);
+            MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(mirror_prune_kernel<0>), cache_bytes));
+            const unsigned hub_grid = (unsigned)std::min<int64_t>(narrow_grid, sm_count());
+            MCB_PROFILED("mirror_prune_widest", side, mirror_prune_kernel<0><<<hub_grid, 128, cache_bytes, side>>>(mp));
+            MCB_LAUNCH_CHECK();
+            MCB_CUDA(cudaEventRecord(join, side));
+        }
         MCB_PROFILED("mirror_prune", stream, mirror_prune_kernel<32><<<narrow_grid, 128, 0, stream>>>(mp));
         MCB_LAUNCH_CHECK();
         if (balanced.widest > 32 * 32) {
             MCB_PROFILED("mirror_prune_wide", stream, mirror_prune_kernel<MP_MAX_ROUNDS><<<narrow_grid, 128, 0, stream>>>(mp));
             MCB_LAUNCH_CHECK();
         }
-        if (balanced.widest > 32 * MP_MAX_ROUNDS) {
-            const size_t cache_bytes = (size_t)4 * MP_CACHE * sizeof(uint32_t);
-            MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(mirror_prune_kernel<0>), cache_bytes));
-            MCB_PROFILED("mirror_prune_widest", stream, mirror_prune_kernel<0><<<narrow_grid, 128, cache_bytes, stream>>>(mp));
-            MCB_LAUNCH_CHECK();
-        }
+        if (hubs) MCB_CUDA(cudaStreamWaitEvent(stream, join, 0));
         MCB_TRY(out_indptr.alloc((size_t)(n + 1) * sizeof(int32_t), stream));
         MCB_TRY(exclusive_scan_i32(kept_sizes.as<int32_t>(), out_indptr.as<int32_t>(), n, nullptr, stream));
         int32_t kept_nnz = 0, overflowed = 0;

@@ -49,6 +49,8 @@ struct MirrorParams {
     int32_t* padded_indices;
     int32_t* sizes;
     int* overflow;  // set when a lane would have to hold two foreign preserved entries of one row
+    int32_t* class_rows;  // [3, n]: the rows of every band-width class (up to 1024 / up to 2048 / wider), in any order
+    int* class_counts;    // [3], filled by row_cuts_kernel
 };
 
 constexpr int MP_MAX_ROUNDS = 64;  // bands of up to 2048 entries
@@ -153,6 +155,10 @@ __global__ void __launch_bounds__(256) row_cuts_kernel(MirrorParams p) {
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < p.n; row += warps) {
         const int lo = p.indptr[row], n = p.indptr[row + 1] - lo;
+        if (lane == 0) {  // the row joins the list of its class: mirror_prune_kernel<...> then walks lists without gaps
+            const int band_class = n <= 32 * 32 ? 0 : (n <= 32 * MP_MAX_ROUNDS ? 1 : 2);
+            p.class_rows[band_class * p.n + atomicAdd(&p.class_counts[band_class], 1)] = (int32_t)row;
+        }
         if (n <= p.incoming_degree) {  // prune_per.cpp:24-28: the band is kept as it is
             if (lane == 0) {
                 RowCut cut;
@@ -457,17 +463,20 @@ template <int ROUNDS>
 __global__ void __launch_bounds__(128, ROUNDS == 32 ? 4 : (ROUNDS == 0 ? 1 : 3)) mirror_prune_kernel(MirrorParams p) {
     extern __shared__ uint32_t mp_cache[];
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < p.n; row += warps) {
+    constexpr int BAND_CLASS = ROUNDS == 32 ? 0 : (ROUNDS == MP_MAX_ROUNDS ? 1 : 2);
+    const int32_t* rows = p.class_rows + BAND_CLASS * p.n;
+    const int count = p.class_counts[BAND_CLASS];
+    // the warps of the first CTAs take one row of the class each: every resident warp works, whatever share of the
+    // rows the class holds
+    for (int64_t at = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; at < count; at += warps) {
+        const int64_t row = rows[at];
         const int lo = p.indptr[row], n = p.indptr[row + 1] - lo;
-        if (ROUNDS == 32) {
-            if (n <= 32 * 32)
-                mirror_prune_in_warp<32>(p, row, lo, n);
-        } else if (ROUNDS == MP_MAX_ROUNDS) {
-            if (n > 32 * 32 && n <= 32 * MP_MAX_ROUNDS)
-                mirror_prune_in_warp<MP_MAX_ROUNDS>(p, row, lo, n);
-        } else if (n > 32 * MP_MAX_ROUNDS) {
+        if (ROUNDS == 32)
+            mirror_prune_in_warp<32>(p, row, lo, n);
+        else if (ROUNDS == MP_MAX_ROUNDS)
+            mirror_prune_in_warp<MP_MAX_ROUNDS>(p, row, lo, n);
+        else
             mirror_prune_streamed(p, row, lo, n, n <= MP_CACHE ? mp_cache + (threadIdx.x >> 5) * MP_CACHE : nullptr);
-        }
     }
 }
 

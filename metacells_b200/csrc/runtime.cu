@@ -142,6 +142,28 @@ int thread_stream(cudaStream_t* stream) {
     return MCB_OK;
 }
 
+// A second stream of the calling host thread with a fork and a join event: a short kernel that would otherwise be a
+// latency tail of its own runs beside the kernels that follow it on the main stream.
+int thread_side_stream(cudaStream_t* side, cudaEvent_t* fork, cudaEvent_t* join) {
+    struct Side {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t fork = nullptr, join = nullptr;
+    };
+    static thread_local Side sides[64];
+    int device = 0;
+    MCB_CUDA(cudaGetDevice(&device));
+    Side& mine = sides[device & 63];
+    if (mine.stream == nullptr) {
+        MCB_CUDA(cudaStreamCreateWithFlags(&mine.stream, cudaStreamNonBlocking));
+        MCB_CUDA(cudaEventCreateWithFlags(&mine.fork, cudaEventDisableTiming));
+        MCB_CUDA(cudaEventCreateWithFlags(&mine.join, cudaEventDisableTiming));
+    }
+    *side = mine.stream;
+    *fork = mine.fork;
+    *join = mine.join;
+    return MCB_OK;
+}
+
 void trace_lap(const char* name, cudaStream_t stream) {
     static const char* mode = getenv("MCB_TRACE");  // "host": the host's own time between laps, no synchronisation
     if (mode == nullptr)
