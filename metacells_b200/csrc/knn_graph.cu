@@ -69,6 +69,12 @@ struct BalanceParams {
     int32_t* out_indices;
     const int32_t* best_index;     // pass 3: the preserved column of every row
     float keep_product;            // the largest float32 r_ij * r_ji whose balanced rank passes the threshold (0: none)
+    // One pass over the ranks instead of two: the count pass also parks what it found -- per (row, column tile) the 64-bit
+    // mask of the entries that pass and, packed at the start of the tile's 64 slots, their values -- and
+    // balance_scatter_kernel places them once the offsets are known (null: balance_kernel<true> reads the ranks again).
+    unsigned long long* masks;     // [n, tiles]
+    float* staged;                 // [n, tiles, BT]
+    const float* best_value;       // scatter: the value of the preserved entry of every row, raised to 1
 };
 
 __device__ __forceinline__ void tile_of_block(int block, int* tile_i, int* tile_j) {
@@ -155,7 +161,17 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                 for (int half = 0; half < 2; ++half)
                     if (passes[half]) best = max(best, pack_tile_best(balanced_t_of_product(product[half]), lane + 32 * half));
                 best = __reduce_max_sync(0xffffffffu, best);
-                const int count = __popc(__ballot_sync(0xffffffffu, kept[0])) + __popc(__ballot_sync(0xffffffffu, kept[1]));
+                const uint32_t mask0 = __ballot_sync(0xffffffffu, kept[0]), mask1 = __ballot_sync(0xffffffffu, kept[1]);
+                const int count = __popc(mask0) + __popc(mask1);
+                if (p.staged != nullptr) {
+                    float* slots = p.staged + (row * p.tiles + column_tile) * BT;
+#pragma unroll
+                    for (int half = 0; half < 2; ++half)
+                        if (kept[half])
+                            slots[(half ? __popc(mask0) : 0) + __popc((half ? mask1 : mask0) & lower_lanes)] =
+                                __fadd_rn(balanced_t_of_product(product[half]), p.shift);
+                    if (lane == 0) p.masks[row * p.tiles + column_tile] = (unsigned long long)mask0 | ((unsigned long long)mask1 << 32);
+                }
                 if (lane == 0) {
                     p.counts[row * p.tiles + column_tile] = count;
                     if (best != 0) {
@@ -182,6 +198,52 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                         p.out_indices[at] = (int32_t)column;
                     }
             }
+        }
+    }
+}
+
+// The fill pass without the ranks: one warp per row, one lane per column tile; the entries the count pass parked go to
+// their places in column order, the preserved entry raised to 1 where it is among them and inserted where the threshold
+// had dropped it (balance_rows_kernel counted it in).
+__global__ void __launch_bounds__(256) balance_scatter_kernel(BalanceParams p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= p.n)
+        return;
+    const int64_t preserved = p.best_index[row];
+    const int preserved_tile = (int)(preserved / BT), preserved_bit = (int)(preserved % BT);
+    const float preserved_value = p.best_value[row];
+    const int64_t first = p.indptr[row];
+    for (int base = 0; base < p.tiles; base += 32) {
+        const int tile = base + lane;
+        if (tile >= p.tiles)
+            continue;
+        unsigned long long mask = p.masks[row * p.tiles + tile];
+        const float* slots = p.staged + (row * p.tiles + tile) * BT;
+        int64_t at = first + p.counts[row * p.tiles + tile];
+        const int64_t column0 = (int64_t)tile * BT;
+        const bool holds_preserved = tile == preserved_tile;
+        bool pending = holds_preserved && !(mask >> preserved_bit & 1ull);  // the threshold dropped the preserved entry
+        int slot = 0;
+        while (mask != 0) {
+            const int bit = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            if (pending && bit > preserved_bit) {
+                p.out_data[at] = preserved_value;
+                p.out_indices[at] = (int32_t)preserved;
+                ++at;
+                pending = false;
+            }
+            float value = slots[slot++];
+            if (holds_preserved && bit == preserved_bit)
+                value = fmaxf(value, 1.0f);  // knn_graph.py:331
+            p.out_data[at] = value;
+            p.out_indices[at] = (int32_t)(column0 + bit);
+            ++at;
+        }
+        if (pending) {
+            p.out_data[at] = preserved_value;
+            p.out_indices[at] = (int32_t)preserved;
         }
     }
 }
@@ -474,6 +536,14 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     MCB_REQUIRE(n < (1 << 20), "balance_ranks: %lld rows are more than the packed row maximum holds", (long long)n);
     p.counts = counts.as<int32_t>();
     p.row_best = row_best.as<unsigned long long>();
+    Scratch masks, staged;
+    const size_t staged_bytes = (size_t)n * tiles * BT * sizeof(float);
+    if (staged_bytes <= ((size_t)8 << 30) && getenv("MCB_BALANCE_TWO_PASSES") == nullptr) {
+        MCB_TRY(masks.alloc((size_t)n * tiles * sizeof(unsigned long long), stream));
+        MCB_TRY(staged.alloc(staged_bytes, stream));
+        p.masks = masks.as<unsigned long long>();
+        p.staged = staged.as<float>();
+    }
     MCB_PROFILED("balance_count", stream, balance_kernel<false><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p));
     MCB_LAUNCH_CHECK();
     MCB_PROFILED("balance_best", stream, balance_best_kernel<<<(unsigned)n, 256, 0, stream>>>(p));
@@ -493,7 +563,11 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     p.out_data = out->data.as<float>();
     p.out_indices = out->indices.as<int32_t>();
     p.best_index = out->best_index.as<int32_t>();
-    MCB_PROFILED("balance_fill", stream, balance_kernel<true><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p));
+    p.best_value = out->best_value.as<float>();
+    if (p.staged != nullptr)
+        MCB_PROFILED("balance_fill", stream, balance_scatter_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(p));
+    else
+        MCB_PROFILED("balance_fill", stream, balance_kernel<true><<<(unsigned)blocks, BAL_THREADS, 0, stream>>>(p));
     MCB_LAUNCH_CHECK();
     return MCB_OK;
 }
