@@ -702,9 +702,10 @@ def run_gpu_arm(args):
                          "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_ncu_full_rank_matrix_bucket.txt")
     downsample_line = hbm_line("downsample_warp_kernel", ("downsample",), 8.0 * umis.nnz + 8.0 * cells + 4, ncu_traffic("downsample", cells, 0),
                                "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_ncu_full_downsample_warp.txt")
-    balance_line = hbm_line("balance_count_kernel + balance_fill_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells,
+    balance_line = hbm_line("balance_kernel<count> + balance_scatter_kernel", ("balance_count", "balance_fill"), 4.0 * cells * cells,
                             ncu_traffic("balance", cells, 0),
-                            "ncu --set full, both passes, profiles/r02_ncu_full_balance_kernels.txt")
+                            "ncu --set full, count pass (reads the ranks once, parks masks + values) + scatter, "
+                            "profiles/r02b_ncu_table_step.md")
     # the dominant kernel is the one with the largest share of the step
     candidates = [line for line in (rank_line, correlate_line, downsample_line, balance_line) if line["ms_per_launch"]]
     dominant = max(candidates, key=lambda line: line["ms_per_launch"]) if candidates else correlate_line
@@ -993,7 +994,7 @@ def ncu_traffic(kernel, cells, features):
     workload that was not captured."""
     if cells != 16000:
         return None
-    table = {"rank_matrix": 1.025e9 + 0.969e9, "downsample": 0.690e9 + 0.206e9, "balance": 1.024e9 + 0.018e9 + 1.046e9 + 0.111e9}
+    table = {"rank_matrix": 1.025e9 + 0.969e9, "downsample": 0.690e9 + 0.206e9, "balance": 1.151e9 + 0.179e9 + 0.565e9 + 0.117e9}
     if features == 2000:
         table["correlate_umma"] = 3.302457e9 + 1.005782e9
     elif features == 890:
