@@ -56,12 +56,15 @@ __global__ void __launch_bounds__(32) cell_gaps_kernel(GapParams P) {
     const int64_t first_member = P.member_offsets[candidate];
     const int count = int(P.member_offsets[candidate + 1] - first_member);
     const int32_t* members = P.members + first_member;
-    float* key = reinterpret_cast<float*>(shared);  // the gene's log fraction of every cell of the candidate
-    float* count_of = key + count;                  // its UMIs
-    float* gap_of = count_of + count;               // the cell's largest gap so far
-    uint16_t* order = reinterpret_cast<uint16_t*>(gap_of + count);  // cell_index_of_position, as slots of `members`
+    // cell_index_of_position, as slots of `members`, each with the bits of its key above it: the sort compares and moves
+    // whole entries (the same comparisons and moves as the reference's sort of indices through a comparator that looks the
+    // keys up), one shared-memory load per operand instead of two dependent ones
+    unsigned long long* order = reinterpret_cast<unsigned long long*>(shared);
+    float* key = reinterpret_cast<float*>(order + count);  // the gene's log fraction of every cell of the candidate
+    float* count_of = key + count;                         // its UMIs
+    float* gap_of = count_of + count;                      // the cell's largest gap so far
     for (int slot = lane; slot < count; slot += 32) {
-        order[slot] = uint16_t(slot);
+        order[slot] = (unsigned long long)slot;
         gap_of[slot] = P.max_gap_per_cell[members[slot]];
     }
     const int positions = P.positions_limit[candidate];
@@ -79,35 +82,48 @@ __global__ void __launch_bounds__(32) cell_gaps_kernel(GapParams P) {
                 count_of[slot] = P.umis[at];
             }
             __syncwarp();
+            for (int place = lane; place < count; place += 32) {
+                const unsigned slot = (unsigned)(order[place] & 0xffffu);
+                order[place] = ((unsigned long long)__float_as_uint(key[slot]) << 32) | slot;
+            }
+            __syncwarp();
             if (lane != 0) continue;
-            serial_sort(order, count, [&](uint16_t left, uint16_t right) { return key[left] < key[right]; });
+            serial_sort(order, count, [](unsigned long long left, unsigned long long right) {
+                return __uint_as_float((unsigned)(left >> 32)) < __uint_as_float((unsigned)(right >> 32));
+            });
             const float min_gap = P.min_gap_per_gene[gene];
             for (int position = 0; position < positions; ++position) {  // gaps.cpp:106-137: the low end
-                const int first = order[position], second = order[position + skip];
+                const int first = (int)(order[position] & 0xffffu), second = (int)(order[position + skip] & 0xffffu);
                 if (double(__fadd_rn(count_of[first], count_of[second])) + 1e-6 < double(P.min_compare_umis)) continue;
                 const float full_gap = __fsub_rn(__fsub_rn(key[second], key[first]), min_gap);
                 if (full_gap < 0.0f) continue;
                 int stop = position + 1;
                 if (skip > 1) {
                     const float start_gap =
-                        float(2.0 * double(__fsub_rn(key[order[position + 1]], key[first])) - double(min_gap));
+                        float(2.0 * double(__fsub_rn(key[order[position + 1] & 0xffffu], key[first])) - double(min_gap));
                     if (start_gap < full_gap) stop += 1;
                 }
-                for (int at = 0; at <= stop; ++at) gap_of[order[at]] = fmaxf(gap_of[order[at]], full_gap);
+                for (int at = 0; at <= stop; ++at) {
+                    const int slot = (int)(order[at] & 0xffffu);
+                    gap_of[slot] = fmaxf(gap_of[slot], full_gap);
+                }
             }
             for (int offset = 0; offset < positions; ++offset) {  // gaps.cpp:139-178: the high end
                 const int position = count - 1 - offset - skip;
-                const int first = order[position], second = order[position + skip];
+                const int first = (int)(order[position] & 0xffffu), second = (int)(order[position + skip] & 0xffffu);
                 if (__fadd_rn(count_of[first], count_of[second]) < P.min_compare_umis) continue;
                 const float full_gap = __fsub_rn(__fsub_rn(key[second], key[first]), min_gap);
                 if (full_gap <= 0.0f) continue;
                 int start = position + 1;
                 if (skip > 1) {
                     const float start_gap =
-                        float(2.0 * double(__fsub_rn(key[order[position + 1]], key[first])) - double(min_gap));
+                        float(2.0 * double(__fsub_rn(key[order[position + 1] & 0xffffu], key[first])) - double(min_gap));
                     if (start_gap < full_gap) start += 1;
                 }
-                for (int at = start; at < count; ++at) gap_of[order[at]] = fmaxf(gap_of[order[at]], full_gap);
+                for (int at = start; at < count; ++at) {
+                    const int slot = (int)(order[at] & 0xffffu);
+                    gap_of[slot] = fmaxf(gap_of[slot], full_gap);
+                }
             }
         }
     }
@@ -176,7 +192,7 @@ int cell_gaps_launch(const float* umis, const float* log_fraction, int64_t cells
     GapParams params{umis, log_fraction, stride, genes, d_members.as<int32_t>(), d_offsets.as<int64_t>(),
                      d_limits.as<int32_t>(), d_flags.as<uint8_t>(), d_min_gap.as<float>(), int(gap_skip_cells),
                      min_compare_umis, d_max_gap.as<float>()};
-    const size_t shared_bytes = (largest * 14 + 15) / 16 * 16;
+    const size_t shared_bytes = (largest * 20 + 15) / 16 * 16;
     MCB_TRY(allow_dynamic_shared(reinterpret_cast<const void*>(cell_gaps_kernel), shared_bytes));
     MCB_PROFILED("cell_gaps", stream, cell_gaps_kernel<<<unsigned(listed), 32, shared_bytes, stream>>>(params));
     MCB_LAUNCH_CHECK();

@@ -272,7 +272,8 @@ __global__ void __launch_bounds__(256) balance_best_kernel(BalanceParams p) {
 // threshold dropped it, turns the counts into exclusive offsets and writes the row's size.
 __global__ void __launch_bounds__(256) balance_rows_kernel(BalanceParams p, int32_t* __restrict__ row_sizes,
                                                           int32_t* __restrict__ best_index, float* __restrict__ best_value,
-                                                          float* __restrict__ best_raw, int32_t* __restrict__ widest) {
+                                                          float* __restrict__ best_raw, int32_t* __restrict__ widest,
+                                                          int32_t* __restrict__ class_rows, int* __restrict__ class_counts) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= p.n)
@@ -300,6 +301,9 @@ __global__ void __launch_bounds__(256) balance_rows_kernel(BalanceParams p, int3
         best_value[row] = fmaxf(value, 1.0f);
         best_raw[row] = value;
         atomicMax(widest, running);
+        // the row joins the list of its band-width class: the pruning kernels walk lists without gaps, in any order
+        const int band_class = running <= 32 * 32 ? 0 : (running <= 32 * MP_MAX_ROUNDS ? 1 : 2);
+        class_rows[band_class * p.n + atomicAdd(&class_counts[band_class], 1)] = (int32_t)row;
     }
 }
 
@@ -478,6 +482,7 @@ int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint
 // The balanced-rank CSR of knn_graph.py:300-340 plus the preserved edge of every row.
 struct BalancedRanks {
     Scratch data, indices, indptr, best_index, best_value, best_raw;  // best_raw: the preserved value before max(., 1)
+    Scratch class_rows, class_counts;  // the rows by band-width class (prune_mirror.cuh): int32 [3, n] and int [4] ([3]: a flag)
     int64_t nnz = 0;
     int64_t widest = 0;  // the longest row
 };
@@ -548,8 +553,12 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
     MCB_LAUNCH_CHECK();
     MCB_PROFILED("balance_best", stream, balance_best_kernel<<<(unsigned)n, 256, 0, stream>>>(p));
     MCB_LAUNCH_CHECK();
+    MCB_TRY(out->class_rows.alloc((size_t)3 * n * sizeof(int32_t), stream));
+    MCB_TRY(out->class_counts.alloc(4 * sizeof(int), stream));
+    MCB_CUDA(cudaMemsetAsync(out->class_counts.ptr, 0, 4 * sizeof(int), stream));
     MCB_PROFILED("balance_rows", stream, balance_rows_kernel<<<(unsigned)ceil_div(n, 8), 256, 0, stream>>>(p, row_sizes.as<int32_t>(), out->best_index.as<int32_t>(),
-                                                                     out->best_value.as<float>(), out->best_raw.as<float>(), widest.as<int32_t>()));
+                                                                     out->best_value.as<float>(), out->best_raw.as<float>(), widest.as<int32_t>(),
+                                                                     out->class_rows.as<int32_t>(), out->class_counts.as<int>()));
     MCB_LAUNCH_CHECK();
     MCB_TRY(exclusive_scan_i32(row_sizes.as<int32_t>(), out->indptr.as<int32_t>(), n, nullptr, stream));
     int32_t nnz = 0, widest_host = 0;
@@ -601,14 +610,12 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
     // (1)-(3) without the transposition (prune_mirror.cuh) when every band fits a warp's registers
     bool mirrored = outgoing_degree >= 1 && getenv("MCB_PRUNE_RELAYOUT") == nullptr;
     if (mirrored) {
-        Scratch cuts, padded_data, padded_indices, kept_sizes, overflow, class_rows;
+        Scratch cuts, padded_data, padded_indices, kept_sizes;
         MCB_TRY(cuts.alloc((size_t)n * sizeof(RowCut), stream));
         MCB_TRY(padded_data.alloc((size_t)n * outgoing_degree * sizeof(float), stream));
         MCB_TRY(padded_indices.alloc((size_t)n * outgoing_degree * sizeof(int32_t), stream));
         MCB_TRY(kept_sizes.alloc((size_t)n * sizeof(int32_t), stream));
-        MCB_TRY(overflow.alloc(4 * sizeof(int), stream));  // [0]: the overflow flag, [1..3]: the sizes of the band classes
-        MCB_CUDA(cudaMemsetAsync(overflow.ptr, 0, 4 * sizeof(int), stream));
-        MCB_TRY(class_rows.alloc((size_t)3 * n * sizeof(int32_t), stream));
+
         MirrorParams mp{};
         mp.data = balanced.data.as<float>();
         mp.indices = balanced.indices.as<int32_t>();
@@ -625,20 +632,32 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
         mp.padded_data = padded_data.as<float>();
         mp.padded_indices = padded_indices.as<int32_t>();
         mp.sizes = kept_sizes.as<int32_t>();
-        mp.overflow = overflow.as<int>();
-        mp.class_rows = class_rows.as<int32_t>();
-        mp.class_counts = overflow.as<int>() + 1;
+        mp.overflow = balanced.class_counts.as<int>() + 3;
+        mp.class_rows = balanced.class_rows.as<int32_t>();
+        mp.class_counts = balanced.class_counts.as<int>();
         const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n * 32, 256), (int64_t)sm_count() * 8);
-        MCB_PROFILED("row_cuts", stream, row_cuts_kernel<<<grid, 256, 0, stream>>>(mp));
-        MCB_LAUNCH_CHECK();
         const unsigned narrow_grid = (unsigned)std::min<int64_t>(ceil_div(n * 32, 128), (int64_t)sm_count() * 16);
-        // The few bands wider than 2048 entries (the hub cells of a pile) take one warp each for a long time: they start
-        // first, on the thread's second stream, and the two classes that hold the rows run beside them.
+        // The few bands wider than 2048 entries (the hub cells of a pile) take one warp each for a long time: in both
+        // steps they start first, on the thread's second stream, and the two classes that hold the rows run beside them.
         cudaStream_t side = nullptr;
         cudaEvent_t fork = nullptr, join = nullptr;
         const bool hubs = balanced.widest > 32 * MP_MAX_ROUNDS;
         if (hubs) {
             MCB_TRY(thread_side_stream(&side, &fork, &join));
+            MCB_CUDA(cudaEventRecord(fork, stream));
+            MCB_CUDA(cudaStreamWaitEvent(side, fork, 0));
+            MCB_PROFILED("row_cuts_widest", side, row_cuts_kernel<0><<<(unsigned)std::min<int64_t>(grid, sm_count()), 256, 0, side>>>(mp));
+            MCB_LAUNCH_CHECK();
+            MCB_CUDA(cudaEventRecord(join, side));
+        }
+        MCB_PROFILED("row_cuts", stream, row_cuts_kernel<32><<<grid, 256, 0, stream>>>(mp));
+        MCB_LAUNCH_CHECK();
+        if (balanced.widest > 32 * 32) {
+            MCB_PROFILED("row_cuts_wide", stream, row_cuts_kernel<MP_MAX_ROUNDS><<<grid, 256, 0, stream>>>(mp));
+            MCB_LAUNCH_CHECK();
+        }
+        if (hubs) {  // every cut is there before any row is pruned
+            MCB_CUDA(cudaStreamWaitEvent(stream, join, 0));
             MCB_CUDA(cudaEventRecord(fork, stream));
             MCB_CUDA(cudaStreamWaitEvent(side, fork, 0));
             const size_t cache_bytes = (size_t)4 * MP_CACHE * sizeof(uint32_t);
@@ -659,7 +678,7 @@ int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incomin
         MCB_TRY(exclusive_scan_i32(kept_sizes.as<int32_t>(), out_indptr.as<int32_t>(), n, nullptr, stream));
         int32_t kept_nnz = 0, overflowed = 0;
         MCB_TRY(read_i32(out_indptr.as<int32_t>() + n, &kept_nnz, stream));
-        MCB_TRY(read_i32(overflow.as<int32_t>(), &overflowed, stream));
+        MCB_TRY(read_i32(balanced.class_counts.as<int32_t>() + 3, &overflowed, stream));
         if (overflowed) {
             mirrored = false;  // a row with more than 32 foreign preserved entries: the general path
         } else {

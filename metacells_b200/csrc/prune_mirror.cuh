@@ -50,7 +50,7 @@ struct MirrorParams {
     int32_t* sizes;
     int* overflow;  // set when a lane would have to hold two foreign preserved entries of one row
     int32_t* class_rows;  // [3, n]: the rows of every band-width class (up to 1024 / up to 2048 / wider), in any order
-    int* class_counts;    // [3], filled by row_cuts_kernel
+    int* class_counts;    // [3], filled where the rows' sizes are computed (balance_rows_kernel)
 };
 
 constexpr int MP_MAX_ROUNDS = 64;  // bands of up to 2048 entries
@@ -150,15 +150,18 @@ __device__ void row_cut_streamed(const MirrorParams& p, int64_t row, int lo, int
     }
 }
 
+// Three launches by band width, as mirror_prune_kernel below: ROUNDS = 32 (up to 1024 entries), MP_MAX_ROUNDS (up to 2048),
+// 0 (wider: streamed), each over the list of the rows of its class.
+template <int ROUNDS>
 __global__ void __launch_bounds__(256) row_cuts_kernel(MirrorParams p) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < p.n; row += warps) {
+    constexpr int BAND_CLASS = ROUNDS == 32 ? 0 : (ROUNDS == MP_MAX_ROUNDS ? 1 : 2);
+    const int32_t* rows = p.class_rows + BAND_CLASS * p.n;
+    const int count = p.class_counts[BAND_CLASS];
+    for (int64_t at = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; at < count; at += warps) {
+        const int64_t row = rows[at];
         const int lo = p.indptr[row], n = p.indptr[row + 1] - lo;
-        if (lane == 0) {  // the row joins the list of its class: mirror_prune_kernel<...> then walks lists without gaps
-            const int band_class = n <= 32 * 32 ? 0 : (n <= 32 * MP_MAX_ROUNDS ? 1 : 2);
-            p.class_rows[band_class * p.n + atomicAdd(&p.class_counts[band_class], 1)] = (int32_t)row;
-        }
         if (n <= p.incoming_degree) {  // prune_per.cpp:24-28: the band is kept as it is
             if (lane == 0) {
                 RowCut cut;
@@ -168,9 +171,9 @@ __global__ void __launch_bounds__(256) row_cuts_kernel(MirrorParams p) {
                 cut.unused = 0;
                 p.cuts[row] = cut;
             }
-        } else if (n <= 32 * 32) {
+        } else if (ROUNDS == 32) {
             row_cut_in_warp<32>(p, row, lo, n);
-        } else if (n <= 32 * MP_MAX_ROUNDS) {
+        } else if (ROUNDS == MP_MAX_ROUNDS) {
             row_cut_in_warp<MP_MAX_ROUNDS>(p, row, lo, n);
         } else {
             row_cut_streamed(p, row, lo, n);

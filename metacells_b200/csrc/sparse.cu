@@ -22,27 +22,31 @@ constexpr int SP_THREADS = 256;
 
 // ---- exclusive scan of int32 (single CTA; the arrays here have one entry per band) -------------
 
+constexpr int SCAN_ITEMS = 16;  // consecutive elements per thread: 16 384 per round of the one CTA (a pile's rows: one round)
+
 __global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int32_t* __restrict__ input, int32_t* __restrict__ output,
                                                              int64_t count, int32_t* __restrict__ total_out) {
     // output[0] = 0, output[i + 1] = input[0] + ... + input[i]; output has count + 1 entries.
     __shared__ int scratch[34];
-    __shared__ int carry;
-    if (threadIdx.x == 0) {
-        carry = 0;
+    int carry = 0;  // the same in every thread
+    if (threadIdx.x == 0)
         output[0] = 0;
-    }
-    __syncthreads();
-    for (int64_t base = 0; base < count; base += 1024) {
-        const int64_t i = base + threadIdx.x;
-        const int value = i < count ? input[i] : 0;
+    for (int64_t base = 0; base < count; base += 1024 * SCAN_ITEMS) {
+        const int64_t first = base + (int64_t)threadIdx.x * SCAN_ITEMS;
+        int values[SCAN_ITEMS], sum = 0;
+#pragma unroll
+        for (int r = 0; r < SCAN_ITEMS; ++r) values[r] = first + r < count ? input[first + r] : 0;
+#pragma unroll
+        for (int r = 0; r < SCAN_ITEMS; ++r) sum += values[r];
         int total;
-        const int before = block_exclusive_scan(value, scratch, &total);
-        if (i < count)
-            output[i + 1] = carry + before + value;
-        __syncthreads();
-        if (threadIdx.x == 0)
-            carry += total;
-        __syncthreads();
+        int running = carry + block_exclusive_scan(sum, scratch, &total);
+#pragma unroll
+        for (int r = 0; r < SCAN_ITEMS; ++r) {
+            running += values[r];
+            if (first + r < count)
+                output[first + r + 1] = running;
+        }
+        carry += total;
     }
     if (threadIdx.x == 0 && total_out)
         *total_out = carry;
