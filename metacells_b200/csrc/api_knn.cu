@@ -5,6 +5,7 @@
 #include <utility>
 
 #include "common.cuh"
+#include "knn_graph.cuh"
 #include "../../include/mcb200.h"
 
 namespace mcb {
@@ -21,19 +22,6 @@ int sort_compressed_indices_launch(float* data, int32_t* indices, const int32_t*
                                    cudaStream_t stream);
 int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint32_t* known_min);
 
-struct BalancedRanks {
-    Scratch data, indices, indptr, best_index, best_value, best_raw;  // best_raw: the preserved value before max(., 1)
-    int64_t nnz = 0;
-    int64_t widest = 0;  // the longest row
-};
-struct PrunedRanks {
-    Scratch data, indices, indptr;
-    int64_t nnz = 0;
-    int32_t min_degree = 0;
-};
-int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRanks* out, cudaStream_t stream);
-int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incoming_degree, int64_t outgoing_degree,
-                       PrunedRanks* out, cudaStream_t stream);
 int weigh_edges_launch(const float* data, const int32_t* indptr, int64_t n, float* weights, int32_t* min_degree_host,
                        cudaStream_t stream);
 }  // namespace mcb

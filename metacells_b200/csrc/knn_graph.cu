@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "select.cuh"
 #include "prune_mirror.cuh"
+#include "knn_graph.cuh"
 
 namespace mcb {
 
@@ -479,14 +480,6 @@ int rank_outgoing_launch(float* work, int64_t n, cudaStream_t stream, const uint
     return rank_matrix_launch(work, n, n, n, 0, stream);
 }
 
-// The balanced-rank CSR of knn_graph.py:300-340 plus the preserved edge of every row.
-struct BalancedRanks {
-    Scratch data, indices, indptr, best_index, best_value, best_raw;  // best_raw: the preserved value before max(., 1)
-    Scratch class_rows, class_counts;  // the rows by band-width class (prune_mirror.cuh): int32 [3, n] and int [4] ([3]: a flag)
-    int64_t nnz = 0;
-    int64_t widest = 0;  // the longest row
-};
-
 // The largest float32 product whose balanced rank passes `2^21 - sqrt(product) + shift > 0`, through the same float32
 // steps as the kernels (and numpy): the steps are monotone, so a bisection over the bit patterns finds it.  Products are
 // at least 1 (ranks start at 1); 0 means that nothing passes.
@@ -582,12 +575,6 @@ int balance_ranks_launch(const float* ranks, int64_t n, float shift, BalancedRan
 }
 
 // knn_graph.py:343-392 (_prune_ranks) after the balanced CSR exists.
-struct PrunedRanks {
-    Scratch data, indices, indptr;
-    int64_t nnz = 0;
-    int32_t min_degree = 0;
-};
-
 int prune_ranks_launch(const BalancedRanks& balanced, int64_t n, int64_t incoming_degree, int64_t outgoing_degree,
                        PrunedRanks* out, cudaStream_t stream) {
     // (4) knn_graph.py:383-388: maximum with the preserved edges and their transpose
