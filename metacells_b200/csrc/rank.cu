@@ -309,16 +309,14 @@ __global__ void __launch_bounds__(MS_THREADS, 1) rank_matrix_bucket_kernel(float
     int2* coarse = reinterpret_cast<int2*>(rm_smem + Plan::BASE_BYTES + Plan::KEYS_BYTES + Plan::POSITIONS_BYTES + Plan::SCRATCH_BYTES);
     float* extremes = reinterpret_cast<float*>(scratch + 40);  // three values per warp
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    float v[ITEMS];  // the row being ranked; reloaded with the next row while the ranks of this one are counted
-    if (blockIdx.x < rows) {
+    float v[ITEMS];  // the row being ranked (the grid has a CTA per row up to 2^20 rows: the loop is for more)
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        float* values = matrix + row * row_stride;
 #pragma unroll
         for (int r = 0; r < ITEMS; ++r) {
             const int i = r * MS_THREADS + tid;
-            v[r] = i < columns ? matrix[blockIdx.x * row_stride + i] : 0.0f;
+            v[r] = i < columns ? values[i] : 0.0f;
         }
-    }
-    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
-        float* values = matrix + row * row_stride;
         // 1. largest, smallest and second smallest value of the row
         float largest = -INFINITY, least = INFINITY, second = INFINITY;
 #pragma unroll
@@ -436,14 +434,13 @@ __global__ void __launch_bounds__(MS_THREADS, 1) rank_matrix_bucket_kernel(float
             int4* base4 = reinterpret_cast<int4*>(base) + tid * (Plan::PER_THREAD / 4);
 #pragma unroll
             for (int q = 0; q < Plan::PER_THREAD / 4; ++q) {
-                int4 four;
-                four.x = before, before += counts[4 * q];
-                four.y = before, before += counts[4 * q + 1];
-                four.z = before, before += counts[4 * q + 2];
-                four.w = before, before += counts[4 * q + 3];
+                int4 four;  // the bucket's place in the sorted order, its size above it (the row has at most 24 576 elements)
+                four.x = before | (counts[4 * q] << 16), before += counts[4 * q];
+                four.y = before | (counts[4 * q + 1] << 16), before += counts[4 * q + 1];
+                four.z = before | (counts[4 * q + 2] << 16), before += counts[4 * q + 2];
+                four.w = before | (counts[4 * q + 3] << 16), before += counts[4 * q + 3];
                 base4[q] = four;
             }
-            if (tid == 0) base[Plan::BINS] = total;
         }
         __syncthreads();
         // 4. scatter
@@ -451,29 +448,20 @@ __global__ void __launch_bounds__(MS_THREADS, 1) rank_matrix_bucket_kernel(float
         for (int r = 0; r < ITEMS; ++r) {
             const int i = r * MS_THREADS + tid;
             if (i < columns) {
-                const int at = base[placed[r] & 0xffffu] + (int)(placed[r] >> 16);
+                const int at = (base[placed[r] & 0xffffu] & 0xffff) + (int)(placed[r] >> 16);
                 keys[at] = sort_key(v[r], ascending != 0);
                 positions[at] = (uint16_t)i;
             }
         }
         __syncthreads();
-        // the next row's loads fly while this row's ranks are counted
-        if (row + gridDim.x < rows) {
-            const float* next = matrix + (row + gridDim.x) * row_stride;
-#pragma unroll
-            for (int r = 0; r < ITEMS; ++r) {
-                const int i = r * MS_THREADS + tid;
-                v[r] = i < columns ? next[i] : 0.0f;
-            }
-        }
         // 5. rank = elements of earlier buckets + members of the own bucket that sort before
 #pragma unroll
         for (int r = 0; r < ITEMS; ++r) {
             const int i = r * MS_THREADS + tid;
             if (i < columns) {
-                const int bin = (int)(placed[r] & 0xffffu);
-                const int first = base[bin], last = base[bin + 1];
-                const uint32_t key = keys[first + (int)(placed[r] >> 16)];
+                const int packed = base[placed[r] & 0xffffu];
+                const int first = packed & 0xffff, last = first + (packed >> 16);
+                const uint32_t key = sort_key(v[r], ascending != 0);
                 // four members at a time, the ones past the end of the bucket masked (the buffer is padded): most
                 // buckets take one round, and the four loads are independent
                 int smaller = 0, not_larger = 0;
