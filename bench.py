@@ -51,6 +51,9 @@ def parse_args():
                         help="cells of the divide-and-conquer atlas whose piles are timed after the per-pile steps (0: skip)")
     parser.add_argument("--e2e-workers", type=int, default=2,
                         help="host threads of a rank that walk its piles end to end, each on a stream of its own")
+    parser.add_argument("--atlas-pile-steps", default="opening", choices=["opening", "direct"],
+                        help="what the atlas walk does to a pile after its graph: seeds + first optimisation, or all of "
+                             "compute_direct_metacells (candidates loop, deviants, dissolve)")
     parser.add_argument("--atlas-extra", default="",
                         help="comma-separated cell counts of further atlases to walk (BASELINE.json configs C3 / C4: 500000,2000000)")
     parser.add_argument("--oversized-cells", type=int, default=65536,
@@ -832,7 +835,7 @@ def time_atlas_walk(args, cells, device, rank, world, barrier):
         barrier()
         resident_s = time.perf_counter() - started
         walk = dc.divide_and_conquer_graphs(atlas, rank=rank, world_size=world, features=args.features, random_seed=SEED,
-                                            workers=max(1, args.e2e_workers))
+                                            workers=max(1, args.e2e_workers), pile_steps=args.atlas_pile_steps)
         barrier()
         wall_s = time.perf_counter() - started
     finally:
@@ -860,6 +863,8 @@ def time_atlas_walk(args, cells, device, rank, world, barrier):
             "graph_edges": int(sum(pile["edges"] for pile in walk["preliminary"]) + sum(pile["edges"] for pile in walk.get("final", []))),
             "h2d_bytes_this_rank": int(upload["h2d_bytes"]), "nvlink_bytes_this_rank": int(upload["exchanged_bytes"]),
             "target_pile_size": walk["target_pile_size"], "generate_s_untimed": generate_s,
+            "pile_steps": args.atlas_pile_steps,
+            "outlier_cells": int((walk["metacell_of_cells"] < 0).sum()),
             "data": "synthetic, distinct cells (tests/synth.py's model, generated per rank on the GPU, moved to page-locked host "
                     "memory before the timed region); max over ranks, barrier on both sides; wall_s = atlas upload + exchange + "
                     "cell totals + preliminary phase + groups + final phase; candidates = choose_seeds + first "

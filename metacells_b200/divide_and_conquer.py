@@ -242,8 +242,8 @@ def metacells_of_phase(cells_count: int, phase: List[dict]) -> Tuple[np.ndarray,
     metacell_of_cells = np.full(cells_count, -1, dtype="int32")
     count = 0
     for pile in phase:
-        communities = pile["communities"]
-        metacell_of_cells[pile["cells"]] = communities + count
+        communities = pile.get("metacells", pile["communities"])  # "metacells": after deviants and dissolve (-1 = outlier)
+        metacell_of_cells[pile["cells"]] = np.where(communities >= 0, communities + count, -1)
         count += int(communities.max()) + 1
     return metacell_of_cells, count
 
@@ -252,7 +252,7 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
                         random_seed: int = 123456, candidates=True, workers: int = 2,
                         masses: Optional[np.ndarray] = None, bounds=None, k_arguments: Optional[dict] = None,
                         times: Optional[dict] = None, deviants: bool = False,
-                        candidates_arguments: Optional[dict] = None) -> List[dict]:
+                        candidates_arguments: Optional[dict] = None, dissolve: bool = False) -> List[dict]:
     """One phase of the walk (``_compute_metacells_of_piles``, :1250-1309) as far as this package goes: for every pile
     of ``pile_of_cells`` (the pile index of every atlas cell, -1 = in no pile) the k-NN graph (downsample -> feature
     genes -> log-fraction -> similarity -> balanced graph, direct.py:214-283) and, with ``candidates``, ``choose_seeds``
@@ -262,10 +262,12 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
     ``random_seed`` (:1274-1279).  ``masses``: the mass of every cell for the candidates (default: its UMIs, direct.py
     ``cell_umis``).  ``candidates="loop"``: the whole ``compute_candidate_metacells`` loop instead of its opening
     (``metacells_b200.candidates``, with ``candidates_arguments`` for its parameters in place of ``bounds``); ``deviants``:
-    then also ``find_deviant_cells`` on every pile (``metacells_b200.deviants``; two piles at a time: the dense matrices of a
-    16 000-cell pile take 3.5 GB).  Returns, on every rank, one dictionary per pile in pile order: ``cells`` (atlas rows),
+    then also ``find_deviant_cells`` on every pile (``metacells_b200.deviants``; up to 32 piles side by side, as far as their
+    dense matrices fit 64 GB: 3.5 GB for a 16 000-cell pile).  Returns, on every rank, one dictionary per pile in pile order: ``cells`` (atlas rows),
     ``k``, ``edges`` and, with ``candidates``, ``communities`` (int32 per pile cell), ``score``, ``seeds``, and with
-    ``deviants`` the boolean ``deviants`` mask."""
+    ``deviants`` the boolean ``deviants`` mask; ``dissolve`` (with ``deviants``): then also ``dissolve_metacells``
+    (``metacells_b200.dissolve``): ``metacells`` (int32 per pile cell, -1 = outlier) and the ``dissolved`` mask, which is
+    what ``compute_direct_metacells`` leaves of a pile (pipeline/direct.py:311-338)."""
     rows_of_piles = _rows_of_piles(pile_of_cells)
     sizes = [len(rows) for rows in rows_of_piles]
     mine = pl.piles_of_rank(sizes, rank, world_size)
@@ -321,10 +323,22 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
                     pile = entry[0]
                     rows = rows_of_piles[pile]
                     with atlas.pile(rows) as handle:
-                        return pile, find_deviant_cells(handle, results[pile]["communities"], total_umis_per_cell=cell_umis[rows])
+                        mask = find_deviant_cells(handle, results[pile]["communities"], total_umis_per_cell=cell_umis[rows])
+                        if not dissolve:
+                            return pile, mask, None
+                        from .dissolve import dissolve_metacells
 
-                for pile, mask in pool.map(deviants_of, graphs):
+                        return pile, mask, dissolve_metacells(handle, results[pile]["communities"], mask,
+                                                              np.ascontiguousarray(masses[rows], dtype="float32"))
+
+                # the gaps kernel keeps one warp per candidate busy (a pile: a few dozen warps of a whole GPU), so piles
+                # run side by side as far as their dense matrices (8 bytes per cell and gene) fit 64 GB
+                largest = max(sizes[pile] for pile, _ in graphs)
+                beside = int(min(32, max(workers, 64e9 // max(8 * largest * atlas.shape[1], 1))))
+                for pile, mask, dissolved in pipeline.worker_pool(beside).map(deviants_of, graphs):
                     results[pile]["deviants"] = mask
+                    if dissolved is not None:
+                        results[pile]["metacells"], results[pile]["dissolved"] = dissolved
     finally:
         for _, graph in graphs:
             graph.close()
@@ -414,9 +428,16 @@ def group_metacells_into_piles(atlas: Atlas, metacell_of_cells: np.ndarray, meta
 
 
 def divide_and_conquer_graphs(atlas: Atlas, *, rank: int = 0, world_size: int = 1, features: int = 2000,
-                              random_seed: int = 123456, workers: int = 2, target_pile_size: Optional[int] = None) -> dict:
+                              random_seed: int = 123456, workers: int = 2, target_pile_size: Optional[int] = None,
+                              pile_steps: str = "opening") -> dict:
     """Preliminary phase -> groups -> final phase over a resident atlas (:947-1060).  Returns the piles and candidate
-    metacells of both phases and the wall time of every step (``times``; seconds on this rank)."""
+    metacells of both phases and the wall time of every step (``times``; seconds on this rank).  ``pile_steps``: what is
+    done to every pile after its k-NN graph -- ``"opening"``: seeds + the first partition optimisation; ``"direct"``: all
+    of ``compute_direct_metacells`` (the whole candidates loop, deviant cells, dissolve): the cells a pile leaves as
+    outliers are then in no group and no final pile (the reference walks them again in its outlier levels, which are
+    not built)."""
+    assert pile_steps in ("opening", "direct")
+    steps = dict(candidates="loop", deviants=True, dissolve=True) if pile_steps == "direct" else {}
     times: dict = {}
     cells = atlas.shape[0]
     if target_pile_size is None:
@@ -424,7 +445,7 @@ def divide_and_conquer_graphs(atlas: Atlas, *, rank: int = 0, world_size: int = 
     preliminary_pile_of_cells = pl.random_piles(cells, target_pile_size, random_seed=random_seed).astype("int32")
     phase_times: dict = {}
     preliminary = compute_piles_phase(atlas, preliminary_pile_of_cells, rank=rank, world_size=world_size, features=features,
-                                      random_seed=random_seed, workers=workers, times=phase_times)
+                                      random_seed=random_seed, workers=workers, times=phase_times, **steps)
     times["preliminary"] = phase_times
     result = {"target_pile_size": int(target_pile_size), "preliminary_pile_of_cells": preliminary_pile_of_cells,
               "preliminary": preliminary, "times": times}
@@ -436,7 +457,7 @@ def divide_and_conquer_graphs(atlas: Atlas, *, rank: int = 0, world_size: int = 
                                                      features=features, random_seed=random_seed, times=times)
     phase_times = {}
     final = compute_piles_phase(atlas, final_pile_of_cells, rank=rank, world_size=world_size, features=features,
-                                random_seed=random_seed, workers=workers, times=phase_times)
+                                random_seed=random_seed, workers=workers, times=phase_times, **steps)
     times["final"] = phase_times
     result.update(preliminary_metacells=metacells_count, final_pile_of_cells=final_pile_of_cells, final=final)
     result["metacell_of_cells"], result["metacells"] = metacells_of_phase(cells, final)

@@ -154,3 +154,23 @@ def test_two_phase_walk(small_atlas):
     for key in ("preliminary", "final"):
         assert first["times"][key]["graphs_s"] > 0
     assert first["times"]["groups_s"] > 0
+
+
+def test_two_phase_walk_with_the_whole_pile_pipeline(small_atlas):
+    """`pile_steps="direct"`: every pile goes through the candidates loop, deviants and dissolve; the walk is reproducible,
+    the outliers of the preliminary phase are in no final pile, everything else in exactly one."""
+    from metacells_b200 import divide_and_conquer as dc
+
+    with dc.Atlas.from_host(small_atlas) as atlas:
+        first = dc.divide_and_conquer_graphs(atlas, features=300, target_pile_size=650, pile_steps="direct")
+        second = dc.divide_and_conquer_graphs(atlas, features=300, target_pile_size=650, pile_steps="direct")
+    assert np.array_equal(first["metacell_of_cells"], second["metacell_of_cells"])
+    assert np.array_equal(first["final_pile_of_cells"], second["final_pile_of_cells"])
+    preliminary_metacells, count = dc.metacells_of_phase(2600, first["preliminary"])
+    assert count == first["preliminary_metacells"] and all("deviants" in pile and "metacells" in pile for pile in first["preliminary"])
+    final = first["final_pile_of_cells"]
+    assert np.array_equal(final >= 0, preliminary_metacells >= 0)
+    for metacell in range(count):
+        assert len(np.unique(final[preliminary_metacells == metacell])) == 1
+    inside = first["metacell_of_cells"] >= 0
+    assert inside.sum() > 0.5 * 2600 and not inside[final < 0].any()
