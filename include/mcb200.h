@@ -336,6 +336,28 @@ int mcb_pile_create_dense_dev(const float* dense, int64_t cells, int64_t genes, 
  * float32 value numpy computes in any order. */
 int mcb_pile_sum_groups(mcb_pile* pile, const int32_t* group_of_cells, int64_t groups, double* sums);
 
+/* collect_metacells for the cells of a pile (pipeline/collect.py:127-232): per metacell and gene the UMIs
+ * (`umis_per_gene`, sums_device float32 [metacells, genes]), the cells left without the gene after each cell is downsampled
+ * to its metacell's `zeros_downsample_umis` (`zeros_per_gene`, zeros_device int32 [metacells, genes]; the cells of a
+ * metacell are sampled as one matrix: seed_index_of_cells is a cell's row in it, :160-171 -> downsample.cpp:148) and the
+ * fractions (fractions_device float32 [metacells, genes]): geometric != 0 (`metacell_geo_mean`, the default): the weighted
+ * geometric mean over the metacell's cells of umis / total + regularization, less that of the regularization, zeroed where
+ * the gene has no UMIs or the result is negative, normalised to 1 (:196-225); geometric == 0: the downsampled UMIs' share
+ * is NOT provided here, the plain UMIs' share is (:181-194 with the stored counts).  `scale` (per metacell) multiplies
+ * the float32 fraction as `fraction *= total_umis` does for the metacell groups (:229-230); 1 leaves it.  Host arrays per
+ * cell: metacell (0 .. metacells - 1, the cells in metacell order), weight (log2 of the cell's UMIs), regularization
+ * (`metacell_umis_regularization` / UMIs), total UMIs (float64), samples, seed index; per metacell:
+ * mean_log_regularization = sum(weight * log(regularization)) / sum(weight), weight_sum, scale, total_umis, cells.  The
+ * sums are made in cell order without atomics (the same bits in every run and on every rank); the sums of UMIs and the
+ * zeros are exact; the fractions are float64 arithmetic with the device's log / exp, within a few ulps of
+ * numpy's (the parity tests hold them to 1e-6 relative). */
+int mcb_pile_collect_metacells(mcb_pile* pile, const int32_t* metacell_of_cells, int64_t metacells, const double* weight_of_cells,
+                               const double* regularization_of_cells, const double* total_of_cells,
+                               const int32_t* samples_of_cells, const int32_t* seed_index_of_cells, uint64_t random_seed,
+                               int geometric, const double* mean_log_regularization, const double* weight_sum, const double* scale,
+                               const double* total_umis, const int32_t* cells_of_metacells, float* fractions_device,
+                               float* sums_device, int32_t* zeros_device);
+
 /* ---- gaps.cpp ------------------------------------------------------------------------------------ */
 
 /* compute_cell_gaps (gaps.cpp:6-186; bound as xt.compute_cell_gaps, tools/deviants.py:309-326): per candidate metacell and

@@ -15,7 +15,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
                            cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr,
-                           unsigned long long* column_stats = nullptr, float top_threshold = 0.0f);
+                           unsigned long long* column_stats = nullptr, float top_threshold = 0.0f, const int32_t* seed_rows = nullptr);
 int column_totals_launch(const float* data, const int32_t* indices, int64_t nnz, int64_t columns, float* totals,
                          cudaStream_t stream);
 int log_fraction_dense_launch(const float* data, const int32_t* indices, const int32_t* indptr, int64_t rows,
@@ -1081,6 +1081,163 @@ int mcb_pile_sum_groups(mcb_pile* pile, const int32_t* group_of_cells, int64_t g
     MCB_LAUNCH_CHECK();
     MCB_TRY(copy_to_host(sums, d_sums.ptr, (size_t)groups * pile->genes * sizeof(double), stream));
     MCB_CUDA(cudaStreamSynchronize(stream));
+    return MCB_OK;
+}
+
+}  // extern "C"
+
+// ---- collect_metacells (pipeline/collect.py:127-232) ------------------------------------------------------------------
+
+namespace {
+
+// One CTA per metacell, its cells one after the other (a barrier between two cells): a cell's stored counts are added to
+// the metacell's per-gene UMIs, the genes it still holds after the "zeros" downsampling are counted, and its share of the
+// weighted geometric mean of the gene fractions (collect.py:196-225) is added up as
+// weight * (log(umis / total + regularization) - log(regularization)):  a gene a cell does not express contributes
+// weight * log(regularization), the same for every gene, which the finishing kernel adds for all cells at once.  No
+// atomics: the float64 sums are made in cell order, so every run and every rank gets the same bits (the ranks of a walk
+// must agree on the grouping they each compute from these).
+__global__ void __launch_bounds__(256) collect_cells_kernel(const float* __restrict__ data, const float* __restrict__ downsampled,
+                                                           const int32_t* __restrict__ indices, const int32_t* __restrict__ indptr,
+                                                           int64_t genes, const int32_t* __restrict__ first_cell_of,
+                                                           const double* __restrict__ weight, const double* __restrict__ regularization,
+                                                           const double* __restrict__ total, float* __restrict__ sums,
+                                                           int32_t* __restrict__ kept, double* __restrict__ logs) {
+    const int64_t metacell = blockIdx.x;
+    const int64_t base = metacell * genes;
+    for (int row = first_cell_of[metacell]; row < first_cell_of[metacell + 1]; ++row) {
+        const double w = weight[row], r = regularization[row], t = total[row];
+        const double log_r = log(r);
+        for (int e = indptr[row] + threadIdx.x; e < indptr[row + 1]; e += blockDim.x) {
+            const float umis = data[e];
+            if (umis == 0.0f) continue;
+            const int64_t at = base + indices[e];
+            sums[at] += umis;
+            if (downsampled[e] != 0.0f) kept[at] += 1;
+            if (logs != nullptr) logs[at] += w * (log((double)umis / t + r) - log_r);
+        }
+        __syncthreads();
+    }
+}
+
+// One CTA per metacell: the fractions are finished (collect.py:216-232: the geometric mean less that of the
+// regularization, genes without UMIs and negative values zeroed, normalised to 1, float32, times `scale`), the kept
+// counts become the zeros.
+__global__ void __launch_bounds__(256) collect_finish_kernel(int64_t genes, const float* __restrict__ sums, int32_t* __restrict__ kept_then_zeros,
+                                                            const double* __restrict__ logs, const double* __restrict__ mean_log_regularization,
+                                                            const double* __restrict__ weight_sum, const double* __restrict__ scale,
+                                                            const double* __restrict__ total_umis, const int32_t* __restrict__ cells_of,
+                                                            float* __restrict__ fractions) {
+    __shared__ double partial[8];
+    const int64_t metacell = blockIdx.x;
+    const int64_t base = metacell * genes;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool geometric = logs != nullptr;
+    const double mean_log_r = geometric ? mean_log_regularization[metacell] : 0.0;
+    const double of_regularization = geometric ? exp(mean_log_r) : 0.0;
+    const double weights = geometric ? weight_sum[metacell] : 1.0;
+    double sum = 0.0;
+    for (int64_t gene = threadIdx.x; gene < genes; gene += blockDim.x) {
+        double fraction;
+        if (geometric) {
+            fraction = exp(mean_log_r + logs[base + gene] / weights) - of_regularization;
+            if (sums[base + gene] == 0.0f || fraction < 0.0) fraction = 0.0;
+        } else {
+            fraction = (double)sums[base + gene];
+        }
+        sum += fraction;
+        kept_then_zeros[base + gene] = cells_of[metacell] - kept_then_zeros[base + gene];
+    }
+    for (int offset = 16; offset > 0; offset >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, offset);
+    if (lane == 0) partial[warp] = sum;
+    __syncthreads();
+    sum = 0.0;
+    for (int w = 0; w < 8; ++w) sum += partial[w];
+    const double factor = scale[metacell];
+    for (int64_t gene = threadIdx.x; gene < genes; gene += blockDim.x) {
+        double fraction;
+        if (geometric) {
+            fraction = exp(mean_log_r + logs[base + gene] / weights) - of_regularization;
+            if (sums[base + gene] == 0.0f || fraction < 0.0) fraction = 0.0;
+            fraction /= sum;
+        } else {
+            fraction = (double)sums[base + gene] / total_umis[metacell];
+        }
+        // .astype("float32"), then `*= total_umis` with a numpy int64: a float64 product stored as float32
+        fractions[base + gene] = factor == 1.0 ? (float)fraction : (float)((double)(float)fraction * factor);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcb_pile_collect_metacells(mcb_pile* pile, const int32_t* metacell_of_cells, int64_t metacells, const double* weight_of_cells,
+                               const double* regularization_of_cells, const double* total_of_cells,
+                               const int32_t* samples_of_cells, const int32_t* seed_index_of_cells, uint64_t random_seed,
+                               int geometric, const double* mean_log_regularization, const double* weight_sum, const double* scale,
+                               const double* total_umis, const int32_t* cells_of_metacells, float* fractions_device,
+                               float* sums_device, int32_t* zeros_device) {
+    MCB_REQUIRE(pile && metacell_of_cells && metacells >= 1 && weight_of_cells && regularization_of_cells && total_of_cells &&
+                    samples_of_cells && seed_index_of_cells && mean_log_regularization && weight_sum && scale && total_umis &&
+                    cells_of_metacells && fractions_device && sums_device && zeros_device,
+                "collect_metacells: null argument");
+    const int64_t cells = pile->cells, genes = pile->genes;
+    // the cells of a metacell lie together, the metacells in order: their first cells
+    std::vector<int32_t> first_cell_of((size_t)metacells + 1, 0);
+    for (int64_t cell = 0; cell < cells; ++cell) {
+        const int32_t metacell = metacell_of_cells[cell];
+        MCB_REQUIRE(metacell >= 0 && metacell < metacells, "collect_metacells: cell %lld is in metacell %d of %lld", (long long)cell,
+                    metacell, (long long)metacells);
+        MCB_REQUIRE(cell == 0 || metacell >= metacell_of_cells[cell - 1], "collect_metacells: the cells must be in metacell order");
+        first_cell_of[(size_t)metacell + 1] += 1;
+    }
+    for (int64_t metacell = 0; metacell < metacells; ++metacell) first_cell_of[(size_t)metacell + 1] += first_cell_of[(size_t)metacell];
+    cudaStream_t stream = pile->stream;
+    MCB_TRY(wait_for_upload(pile));
+    Scratch d_metacell, d_weight, d_regularization, d_total, d_samples, d_seed_rows, d_down, d_logs, d_mean, d_weights, d_scale,
+        d_totals, d_counts;
+    auto upload = [&](Scratch& device, const void* host, size_t bytes) -> int {
+        MCB_TRY(device.alloc(bytes, stream));
+        MCB_CUDA(cudaMemcpyAsync(device.ptr, host, bytes, cudaMemcpyHostToDevice, stream));
+        return MCB_OK;
+    };
+    MCB_TRY(upload(d_metacell, first_cell_of.data(), ((size_t)metacells + 1) * sizeof(int32_t)));
+    MCB_TRY(upload(d_weight, weight_of_cells, (size_t)cells * sizeof(double)));
+    MCB_TRY(upload(d_regularization, regularization_of_cells, (size_t)cells * sizeof(double)));
+    MCB_TRY(upload(d_total, total_of_cells, (size_t)cells * sizeof(double)));
+    MCB_TRY(upload(d_samples, samples_of_cells, (size_t)cells * sizeof(int32_t)));
+    MCB_TRY(upload(d_seed_rows, seed_index_of_cells, (size_t)cells * sizeof(int32_t)));
+    MCB_TRY(upload(d_mean, mean_log_regularization, (size_t)metacells * sizeof(double)));
+    MCB_TRY(upload(d_weights, weight_sum, (size_t)metacells * sizeof(double)));
+    MCB_TRY(upload(d_scale, scale, (size_t)metacells * sizeof(double)));
+    MCB_TRY(upload(d_totals, total_umis, (size_t)metacells * sizeof(double)));
+    MCB_TRY(upload(d_counts, cells_of_metacells, (size_t)metacells * sizeof(int32_t)));
+    // the "zeros" downsampling of collect.py:160-171: every metacell's cells as a matrix of their own (the seed of a row is
+    // made of its index in that matrix), each to its metacell's quantile of the cells' UMIs
+    MCB_TRY(d_down.alloc((size_t)std::max<int64_t>(pile->nnz, 1) * sizeof(float), stream));
+    MCB_TRY(downsample_rows_launch(pile->data, d_down.as<float>(), pile->indptr, d_samples.as<int32_t>(), 0, 0, cells, 0,
+                                   pile->widest, random_seed, 1, 0, nullptr, stream, nullptr, nullptr, nullptr, 0.0f,
+                                   d_seed_rows.as<int32_t>()));
+    const size_t entries = (size_t)metacells * genes;
+    MCB_CUDA(cudaMemsetAsync(sums_device, 0, entries * sizeof(float), stream));
+    MCB_CUDA(cudaMemsetAsync(zeros_device, 0, entries * sizeof(int32_t), stream));
+    if (geometric) {
+        MCB_TRY(d_logs.alloc(entries * sizeof(double), stream));
+        MCB_CUDA(cudaMemsetAsync(d_logs.ptr, 0, entries * sizeof(double), stream));
+    }
+    MCB_PROFILED("collect_cells", stream,
+                 collect_cells_kernel<<<(unsigned)metacells, 256, 0, stream>>>(
+                     pile->data, d_down.as<float>(), pile->indices, pile->indptr, genes, d_metacell.as<int32_t>(),
+                     d_weight.as<double>(), d_regularization.as<double>(), d_total.as<double>(), sums_device, zeros_device,
+                     geometric ? d_logs.as<double>() : nullptr));
+    MCB_LAUNCH_CHECK();
+    MCB_PROFILED("collect_finish", stream,
+                 collect_finish_kernel<<<(unsigned)metacells, 256, 0, stream>>>(
+                     genes, sums_device, zeros_device, geometric ? d_logs.as<double>() : nullptr, d_mean.as<double>(),
+                     d_weights.as<double>(), d_scale.as<double>(), d_totals.as<double>(), d_counts.as<int32_t>(), fractions_device));
+    MCB_LAUNCH_CHECK();
+    MCB_CUDA(cudaStreamSynchronize(stream));  // the host arrays above may be pageable
     return MCB_OK;
 }
 

@@ -44,6 +44,7 @@ struct DownsampleParams {
     int64_t first_row;       // rows [first_row, rows) are processed
     uint64_t seed;
     int use_row_seed;        // 1: seed + 997 * row (matrix forms); 0: seed as given (array form)
+    const int32_t* seed_rows;  // nullable: the row index the seed is made of (a row's index in the matrix it is sampled as part of)
     uint32_t* workspace;     // 2 * capacity uint32 per CTA when rows do not fit shared memory
     int64_t capacity;        // elements per array in `workspace` (0: shared memory only)
     int smem_capacity;       // elements per array that fit shared memory
@@ -151,7 +152,7 @@ __global__ void __launch_bounds__(DS_THREADS) downsample_kernel(DownsampleParams
 
         uint64_t row_seed = p.seed;
         if (p.use_row_seed)
-            row_seed = p.seed == 0 ? 0 : p.seed + (uint64_t)row * 997ull;
+            row_seed = p.seed == 0 ? 0 : p.seed + (uint64_t)(p.seed_rows ? (int64_t)p.seed_rows[row] : row) * 997ull;
         uint32_t state = (uint32_t)(row_seed % MINSTD_M);
         if (state == 0)
             state = 1;  // std::linear_congruential_engine::seed
@@ -345,7 +346,7 @@ __global__ void __launch_bounds__(DW_WARPS * 32) downsample_warp_kernel(WarpDown
 
         uint64_t row_seed = p.seed;
         if (p.use_row_seed)
-            row_seed = p.seed == 0 ? 0 : p.seed + (uint64_t)row * 997ull;
+            row_seed = p.seed == 0 ? 0 : p.seed + (uint64_t)(p.seed_rows ? (int64_t)p.seed_rows[row] : row) * 997ull;
         uint32_t state = (uint32_t)(row_seed % MINSTD_M);
         if (state == 0)
             state = 1;
@@ -483,7 +484,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
                            cudaStream_t stream, const int32_t* indices = nullptr, float* column_totals = nullptr,
-                           unsigned long long* column_stats = nullptr, float top_threshold = 0.0f);
+                           unsigned long long* column_stats = nullptr, float top_threshold = 0.0f, const int32_t* seed_rows = nullptr);
 
 int downsample_launch(const float* input, float* output, const int32_t* indptr, const int32_t* samples,
                       int32_t samples_all, int64_t rows, int64_t columns, int64_t max_row_size, uint64_t seed,
@@ -496,7 +497,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
                            int32_t samples_all, int64_t first_row, int64_t last_row, int64_t columns, int64_t max_row_size,
                            uint64_t seed, int use_row_seed, unsigned long long known_max_total, int* deferred_flag,
                            cudaStream_t stream, const int32_t* indices, float* column_totals, unsigned long long* column_stats,
-                           float top_threshold) {
+                           float top_threshold, const int32_t* seed_rows) {
     const int64_t rows = last_row - first_row;
     if (rows <= 0)
         return MCB_OK;
@@ -511,6 +512,7 @@ int downsample_rows_launch(const float* input, float* output, const int32_t* ind
     p.first_row = first_row;
     p.seed = seed;
     p.use_row_seed = use_row_seed;
+    p.seed_rows = seed_rows;
     // column totals of the output (compressed input only): added by the kernel that writes it
     MCB_REQUIRE(column_totals == nullptr || (indices != nullptr && indptr != nullptr),
                 "downsample: column totals need a compressed matrix");

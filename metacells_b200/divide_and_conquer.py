@@ -135,6 +135,59 @@ class Atlas:
                        ctypes.c_void_p(sums.data_ptr()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
         return sums
 
+    def collect_metacells(self, metacell_of_cells: np.ndarray, metacells_count: int, *, random_seed: int,
+                          metacell_geo_mean: bool = True, metacell_umis_regularization: float = 1 / 16.0,
+                          zeros_cell_size_quantile: float = 0.1, metacell_groups: bool = False,
+                          chunk_cells: int = 16384) -> dict:
+        """``collect_metacells`` (pipeline/collect.py:127-232) over the resident atlas: for every metacell ``grouped``
+        (cells), ``total_umis``, ``zeros_downsample_umis`` (host vectors), and CUDA ``torch`` tensors [metacells, genes]:
+        ``umis_per_gene`` (float32), ``zeros_per_gene`` (int32) and ``fraction_per_gene`` (float32; with
+        ``metacell_groups`` multiplied by the metacell's total UMIs: the "effective UMIs" the grouping of the metacells
+        works on, :229-230).  The metacells are walked in chunks of about ``chunk_cells`` cells, each a pile gathered on the
+        device (``mcb_pile_collect_metacells``); cells of a negative metacell are left out."""
+        import torch
+
+        metacell_of_cells = np.asarray(metacell_of_cells)
+        assert len(metacell_of_cells) == self.shape[0]
+        plan = collect_plan(metacell_of_cells, metacells_count, self.cell_umis, metacell_umis_regularization=metacell_umis_regularization,
+                            zeros_cell_size_quantile=zeros_cell_size_quantile, metacell_groups=metacell_groups)
+        genes = self.shape[1]
+        fractions = torch.empty((metacells_count, genes), dtype=torch.float32, device="cuda")
+        sums = torch.empty((metacells_count, genes), dtype=torch.float32, device="cuda")
+        zeros = torch.empty((metacells_count, genes), dtype=torch.int32, device="cuda")
+        function = lib().mcb_pile_collect_metacells
+        function.restype = ctypes.c_int
+        pointer = lambda array: ctypes.c_void_p(array.ctypes.data)  # noqa: E731
+        starts = plan["starts"]
+        first = 0
+        while first < metacells_count:
+            last = first + 1
+            while last < metacells_count and starts[last + 1] - starts[first] <= chunk_cells:
+                last += 1
+            cells = slice(starts[first], starts[last])
+            metacells = slice(first, last)
+            rows = plan["rows"][cells]
+            if len(rows):
+                per_cell = {name: np.ascontiguousarray(plan[name][cells]) for name in ("weight", "regularization", "umis", "samples",
+                                                                                       "seed_index")}
+                local = np.ascontiguousarray(plan["metacell"][cells] - first, dtype="int32")
+                per_metacell = {name: np.ascontiguousarray(plan[name][metacells]) for name in ("mean_log_regularization", "weight_sum",
+                                                                                               "scale", "total_umis_f64", "grouped_i32")}
+                with self.pile(rows) as pile:
+                    check(function(pile._handle, pointer(local), ctypes.c_int64(last - first), pointer(per_cell["weight"]),
+                                   pointer(per_cell["regularization"]), pointer(per_cell["umis"]), pointer(per_cell["samples"]),
+                                   pointer(per_cell["seed_index"]), ctypes.c_uint64(int(random_seed)),
+                                   ctypes.c_int(int(bool(metacell_geo_mean))), pointer(per_metacell["mean_log_regularization"]),
+                                   pointer(per_metacell["weight_sum"]), pointer(per_metacell["scale"]),
+                                   pointer(per_metacell["total_umis_f64"]), pointer(per_metacell["grouped_i32"]),
+                                   ctypes.c_void_p(fractions[first].data_ptr()), ctypes.c_void_p(sums[first].data_ptr()),
+                                   ctypes.c_void_p(zeros[first].data_ptr())))
+            else:
+                fractions[metacells], sums[metacells], zeros[metacells] = 0, 0, 0
+            first = last
+        return {"grouped": plan["grouped"], "total_umis": plan["total_umis"], "zeros_downsample_umis": plan["zeros_downsample_umis"],
+                "umis_per_gene": sums, "zeros_per_gene": zeros, "fraction_per_gene": fractions}
+
     def close(self) -> None:
         if getattr(self, "_handle", None):
             lib().mcb_atlas_free(self._handle)
@@ -205,6 +258,62 @@ def _atlas_from_host_shares(cls, share_data, share_indices, share_indptr: np.nda
 
 
 Atlas.from_host_shares = classmethod(_atlas_from_host_shares)  # type: ignore[attr-defined]
+
+
+def quantile_of_groups(sorted_values: np.ndarray, starts: np.ndarray, quantile: float) -> np.ndarray:
+    """``np.quantile(group, quantile)`` (the default linear method) of every group of a float64 vector whose groups lie one
+    after the other (``starts``: their offsets, one more than groups), each sorted ascending; NaN for an empty group.
+    numpy's own steps (``_quantile``: virtual index ``quantile * (n - 1)``, ``_lerp`` with its switch at one half) on all
+    groups at once."""
+    sizes = np.diff(starts)
+    filled = sizes > 0
+    index = quantile * (np.maximum(sizes, 1) - 1)
+    previous = np.floor(index).astype("int64")
+    gamma = index - previous
+    following = np.minimum(previous + 1, np.maximum(sizes, 1) - 1)
+    low = sorted_values[np.minimum(starts[:-1] + previous, len(sorted_values) - 1)] if len(sorted_values) else np.zeros(len(sizes))
+    high = sorted_values[np.minimum(starts[:-1] + following, len(sorted_values) - 1)] if len(sorted_values) else np.zeros(len(sizes))
+    difference = high - low
+    result = low + difference * gamma
+    late = gamma >= 0.5
+    result[late] = (high - difference * (1 - gamma))[late]
+    return np.where(filled, result, np.nan)
+
+
+def collect_plan(metacell_of_cells: np.ndarray, metacells_count: int, cell_umis: np.ndarray, *,
+                 metacell_umis_regularization: float = 1 / 16.0, zeros_cell_size_quantile: float = 0.1,
+                 metacell_groups: bool = False) -> dict:
+    """The per-cell and per-metacell vectors of ``collect_metacells`` that do not touch the genes (pipeline/collect.py:
+    127-161, :207-214), for all metacells at once: the cells in metacell order (``rows``, ``metacell``, ``starts``), per cell
+    ``umis`` (float64), ``weight`` (log2 UMIs), ``regularization``, ``samples`` (the metacell's ``zeros_downsample_umis``),
+    ``seed_index`` (the cell's place in its metacell); per metacell ``grouped``, ``total_umis`` (int64),
+    ``zeros_downsample_umis``, ``mean_log_regularization``, ``weight_sum``, ``scale``."""
+    metacell_of_cells = np.asarray(metacell_of_cells)
+    order = np.argsort(metacell_of_cells, kind="stable")
+    order = order[metacell_of_cells[order] >= 0]
+    metacell = metacell_of_cells[order].astype("int64")
+    grouped = np.bincount(metacell, minlength=metacells_count).astype("int64")
+    starts = np.concatenate([[0], np.cumsum(grouped)])
+    umis = np.asarray(cell_umis)[order].astype("float64")  # :128: the cells' totals as float64
+    total_umis = np.zeros(metacells_count, dtype="int64")
+    np.add.at(total_umis, metacell, umis.astype("int64"))  # :153
+    by_size = np.lexsort((umis, metacell))
+    quantiles = quantile_of_groups(umis[by_size], starts, zeros_cell_size_quantile)
+    zeros_downsample_umis = np.rint(np.where(np.isnan(quantiles), 0, quantiles)).astype("int64")  # :159: Python's round
+    with np.errstate(divide="ignore", invalid="ignore"):
+        weight = np.log2(umis)  # :211
+        regularization = metacell_umis_regularization / umis  # :210
+        weighted = np.zeros(metacells_count)
+        np.add.at(weighted, metacell, weight * np.log(regularization))
+        weight_sum = np.zeros(metacells_count)
+        np.add.at(weight_sum, metacell, weight)
+        mean_log_regularization = np.where(grouped > 0, weighted / np.where(weight_sum == 0, 1, weight_sum), 0.0)
+    return {"rows": order.astype("int64"), "metacell": metacell, "starts": starts, "umis": umis, "weight": weight,
+            "regularization": regularization, "samples": zeros_downsample_umis[metacell].astype("int32"),
+            "seed_index": (np.arange(len(order)) - starts[metacell]).astype("int32"), "grouped": grouped,
+            "grouped_i32": grouped.astype("int32"), "total_umis": total_umis, "total_umis_f64": total_umis.astype("float64"),
+            "zeros_downsample_umis": zeros_downsample_umis, "mean_log_regularization": mean_log_regularization,
+            "weight_sum": weight_sum, "scale": total_umis.astype("float64") if metacell_groups else np.ones(metacells_count)}
 
 
 def _rows_of_piles(pile_of_cells: np.ndarray) -> List[np.ndarray]:
@@ -351,9 +460,12 @@ def compute_piles_phase(atlas: Atlas, pile_of_cells: np.ndarray, *, rank: int = 
 
 
 def group_metacells_into_piles(atlas: Atlas, metacell_of_cells: np.ndarray, metacells_count: int, *, target_pile_size: int,
-                               features: int = 2000, random_seed: int = 123456, times: Optional[dict] = None) -> np.ndarray:
-    """``_compute_metacell_groups`` (:1153-1245): the final pile of every cell.  The UMIs of every metacell are summed on
-    the device (``collect_metacells``, pipeline/collect.py:162-201), the metacells are the cells of a grouping pile whose
+                               features: int = 2000, random_seed: int = 123456, times: Optional[dict] = None,
+                               grouping_data: str = "collect") -> np.ndarray:
+    """``_compute_metacell_groups`` (:1153-1245): the final pile of every cell.  The metacells are collected on the device
+    (``Atlas.collect_metacells`` with ``metacell_groups``: every metacell's geometric-mean gene fractions times its total
+    UMIs, pipeline/collect.py:196-230; ``grouping_data="sums"``: their plain UMI sums, the round's first form), the
+    metacells are the cells of a grouping pile whose
     masses are their cell counts, with target mass = the pile size, target size ``target_metacells_in_pile``,
     ``piles_knn_k_size_factor`` and the piles' split / merge factors (:1188-1210), and the communities of its candidate
     partition are the final piles.  Every rank computes the same grouping.  More metacells than fit one pile are grouped
@@ -361,7 +473,16 @@ def group_metacells_into_piles(atlas: Atlas, metacell_of_cells: np.ndarray, meta
     import torch
 
     started = time.perf_counter()
-    sums = atlas.sum_groups(metacell_of_cells, metacells_count)
+    assert grouping_data in ("collect", "sums")
+    if grouping_data == "collect":
+        # The effective UMIs are rounded to whole numbers: the per-pile path works on counts (the numpy-made log table, the
+        # exact integer gene statistics).  The reference keeps the fractional values of the metacells it does not
+        # downsample (those under the samples count) and truncates the others (downsample.cpp:26): under half a UMI per
+        # gene and metacell either way.
+        sums = torch.round(atlas.collect_metacells(metacell_of_cells, metacells_count, random_seed=random_seed,
+                                                   metacell_groups=True)["fraction_per_gene"])
+    else:
+        sums = atlas.sum_groups(metacell_of_cells, metacells_count)
     metacell_sizes = np.bincount(metacell_of_cells[metacell_of_cells >= 0], minlength=metacells_count).astype("float32")
     metacell_umis = sums.sum(dim=1).cpu().numpy().astype("float32")
     bounds = pipeline.metacell_bounds(target_metacell_size=TARGET_METACELLS_IN_PILE, target_metacell_umis=target_pile_size,

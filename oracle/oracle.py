@@ -1017,3 +1017,53 @@ def dissolve_metacells(umis: sp.spmatrix, candidates: np.ndarray, deviants: Opti
             candidate_of_cells[cell_indices] = -1
             did_dissolve = True
     return (compress(candidate_of_cells) if did_dissolve else candidate_of_cells), dissolved_of_cells
+
+
+# ---- collect_metacells (pipeline/collect.py:127-232) ----------------------------------------------------------------------
+
+
+def collect_metacells(umis: sp.csr_matrix, metacell_of_cells: np.ndarray, *, random_seed: int, metacell_geo_mean: bool = True,
+                      metacell_umis_regularization: float = 1 / 16.0, zeros_cell_size_quantile: float = 0.1,
+                      metacell_groups: bool = False) -> dict:
+    """Metacell by metacell as ``_collect_metacell`` does it (dense sub-matrices, numpy / scipy.stats in float64, this
+    file's ``downsample_dense`` for the zeros): ``grouped``, ``total_umis``, ``zeros_downsample_umis`` per metacell and
+    ``umis_per_gene`` (float32), ``fraction_per_gene`` (float32), ``zeros_per_gene`` (int32) per metacell and gene."""
+    import scipy.stats as ss
+
+    metacell_of_cells = np.asarray(metacell_of_cells).copy()
+    metacell_of_cells[metacell_of_cells < 0] = -1
+    metacells_count = int(np.max(metacell_of_cells)) + 1
+    umis_per_cell = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float64")
+    results = {"grouped": [], "total_umis": [], "zeros_downsample_umis": [], "umis_per_gene": [], "fraction_per_gene": [],
+               "zeros_per_gene": []}
+    for metacell_index in range(metacells_count):
+        mask = metacell_of_cells == metacell_index
+        umis_of_cells = umis_per_cell[mask]
+        total_umis = np.sum(umis_of_cells.astype("int64"))
+        dense = np.ascontiguousarray(umis[mask, :].toarray(), dtype="float32")
+        zeros_downsample_umis = round(np.quantile(umis_of_cells, zeros_cell_size_quantile))
+        downsampled = downsample_dense(dense, np.full(dense.shape[0], zeros_downsample_umis, dtype="int32"), random_seed)
+        zeros_per_gene = np.sum(downsampled == 0, axis=0).astype("int32")
+        umis_per_gene = np.sum(np.asfortranarray(dense), axis=0).astype("float32")
+        if not metacell_geo_mean:
+            total_downsampled = np.sum(downsampled)
+            fraction_per_gene = np.sum(downsampled, axis=0).astype("float32") / total_downsampled
+        else:
+            fraction_per_cell = dense / umis_of_cells[:, np.newaxis]
+            regularization_per_cell = metacell_umis_regularization / umis_of_cells
+            weight_per_cell = np.log2(umis_of_cells)
+            fraction_per_cell = fraction_per_cell + regularization_per_cell[:, np.newaxis]
+            regularization = ss.mstats.gmean(regularization_per_cell, weights=weight_per_cell)
+            fraction_per_gene = ss.mstats.gmean(fraction_per_cell.transpose(), axis=1, weights=weight_per_cell)
+            fraction_per_gene = np.asarray(fraction_per_gene) - regularization
+            fraction_per_gene[umis_per_gene == 0] = 0
+            fraction_per_gene[fraction_per_gene < 0] = 0
+            fraction_per_gene /= np.sum(fraction_per_gene)
+        fraction_per_gene = fraction_per_gene.astype("float32")
+        if metacell_groups:
+            fraction_per_gene *= total_umis
+        for name, value in (("grouped", int(np.sum(mask))), ("total_umis", int(total_umis)),
+                            ("zeros_downsample_umis", int(zeros_downsample_umis)), ("umis_per_gene", umis_per_gene),
+                            ("fraction_per_gene", fraction_per_gene), ("zeros_per_gene", zeros_per_gene)):
+            results[name].append(value)
+    return {name: (np.vstack(values) if name.endswith("_per_gene") else np.array(values)) for name, values in results.items()}

@@ -55,3 +55,31 @@ def test_results_of_piles_are_gathered_across_ranks():
         worker.join(timeout=60)
     for _, piles, sums in results:
         assert piles == [0, 1, 2, 3, 4] and sums == [0, 1, 3, 6, 10]
+
+
+def test_collect_plan_follows_numpy():
+    """The vectorised per-metacell vectors of `collect_metacells` == the reference's per-metacell numpy calls
+    (pipeline/collect.py:145-161, :207-214): np.quantile + Python's round, int64 totals, scipy's weighted gmean."""
+    import scipy.stats as ss
+
+    from metacells_b200 import divide_and_conquer as dc
+
+    rng = np.random.default_rng(4)
+    cell_umis = rng.integers(300, 20000, size=3000).astype("float32")
+    metacell_of_cells = rng.integers(-1, 90, size=3000).astype("int32")
+    metacell_of_cells[metacell_of_cells == 40] = 41
+    plan = dc.collect_plan(metacell_of_cells, 90, cell_umis, metacell_groups=True)
+    assert sorted(plan["rows"].tolist()) == np.flatnonzero(metacell_of_cells >= 0).tolist()
+    for metacell in range(90):
+        cells = np.flatnonzero(metacell_of_cells == metacell)
+        mine = plan["rows"][plan["starts"][metacell]:plan["starts"][metacell + 1]]
+        assert np.array_equal(mine, cells) and plan["grouped"][metacell] == len(cells)
+        assert np.array_equal(plan["seed_index"][plan["starts"][metacell]:plan["starts"][metacell + 1]], np.arange(len(cells)))
+        if len(cells) == 0:
+            continue
+        umis = cell_umis[cells].astype("float64")
+        assert plan["total_umis"][metacell] == np.sum(umis.astype("int64")) == plan["scale"][metacell]
+        assert plan["zeros_downsample_umis"][metacell] == round(np.quantile(umis, 0.1))
+        assert (plan["samples"][plan["starts"][metacell]:plan["starts"][metacell + 1]] == plan["zeros_downsample_umis"][metacell]).all()
+        regularization = ss.mstats.gmean((1 / 16.0) / umis, weights=np.log2(umis))
+        assert np.isclose(np.exp(plan["mean_log_regularization"][metacell]), regularization, rtol=1e-13, atol=0)

@@ -174,3 +174,39 @@ def test_two_phase_walk_with_the_whole_pile_pipeline(small_atlas):
         assert len(np.unique(final[preliminary_metacells == metacell])) == 1
     inside = first["metacell_of_cells"] >= 0
     assert inside.sum() > 0.5 * 2600 and not inside[final < 0].any()
+
+
+@pytest.mark.parametrize("geo_mean, groups", [(True, True), (True, False), (False, False)])
+def test_collect_metacells_matches_oracle(small_atlas, geo_mean, groups):
+    """`Atlas.collect_metacells` (pipeline/collect.py:127-232) against the oracle's metacell-by-metacell restatement: cells,
+    total UMIs, the zeros' downsampling depth, UMIs per gene and zeros per gene `==`; the fractions (float64 log / exp on the
+    device against numpy's) within 1e-6 relative.  The oracle's fractions without the geometric mean are the downsampled
+    UMIs' share, which is not provided: only the exact outputs are compared there."""
+    from oracle import oracle
+
+    from metacells_b200 import divide_and_conquer as dc
+
+    rng = np.random.default_rng(9)
+    metacell_of_cells = rng.integers(0, 70, size=2600).astype("int32")
+    metacell_of_cells[rng.random(2600) < 0.05] = -1
+    metacell_of_cells[np.flatnonzero(metacell_of_cells == 12)[1:]] = 13  # one of a single cell
+    expected = oracle.collect_metacells(small_atlas, metacell_of_cells, random_seed=123456, metacell_geo_mean=geo_mean,
+                                        metacell_groups=groups)
+    with dc.Atlas.from_host(small_atlas) as atlas:
+        mine = atlas.collect_metacells(metacell_of_cells, 70, random_seed=123456, metacell_geo_mean=geo_mean,
+                                       metacell_groups=groups, chunk_cells=500)
+        whole = atlas.collect_metacells(metacell_of_cells, 70, random_seed=123456, metacell_geo_mean=geo_mean,
+                                        metacell_groups=groups)
+    filled = expected["grouped"] > 0
+    for name in ("grouped", "total_umis"):
+        assert np.array_equal(mine[name], expected[name])
+    assert np.array_equal(mine["zeros_downsample_umis"][filled], expected["zeros_downsample_umis"][filled])
+    assert np.array_equal(mine["umis_per_gene"].cpu().numpy(), expected["umis_per_gene"])
+    assert np.array_equal(mine["zeros_per_gene"].cpu().numpy()[filled], expected["zeros_per_gene"][filled])
+    for name in ("umis_per_gene", "zeros_per_gene", "fraction_per_gene"):
+        assert np.array_equal(mine[name].cpu().numpy(), whole[name].cpu().numpy()), name  # the chunking does not show
+    if geo_mean:
+        fractions = mine["fraction_per_gene"].cpu().numpy()[filled]
+        theirs = expected["fraction_per_gene"][filled]
+        assert np.array_equal(fractions == 0, theirs == 0)
+        assert np.allclose(fractions, theirs, rtol=1e-6, atol=0)
