@@ -136,3 +136,32 @@ def test_pile_candidates_match_oracle(cells, genes, target_umis_of_mean):
     assert_same_trace(mine, theirs)
     assert np.array_equal(candidate, expected)
     assert sum(step[0] == "optimize" for step in theirs) >= 2  # at least one round of cancelled communities
+
+
+@pytest.mark.parametrize("cells", [4, 9, 25, 70])
+def test_tiny_piles_behave_as_the_oracle(cells):
+    """Piles far under a metacell's size (the leftovers of a divide-and-conquer walk): the loop gives the oracle's
+    candidates, or both refuse the input (an assertion of the reference's natives surfaces as McbError / ReferenceAssert)."""
+    from metacells_b200._lib import McbError
+    from metacells_b200.candidates import compute_candidate_metacells
+    from metacells_b200.pipeline import pile_knn_graph_on_device
+
+    umis = synth_umis(cells, 1500, seed=31)
+    graph, cell_umis = pile_knn_graph_on_device(umis, features=200)
+    try:
+        outgoing, _ = graph.to_scipy()
+        arguments = dict(random_seed=SEED, target_metacell_umis=int(48 * cell_umis.mean()))
+        try:
+            expected = oracle.compute_candidate_metacells(outgoing, cell_umis, **arguments)
+        except (oracle.ReferenceAssert, AssertionError, ValueError, IndexError) as failure:
+            expected = type(failure)
+        try:
+            candidate = compute_candidate_metacells(graph, cell_umis, **arguments)
+        except (McbError, AssertionError, ValueError, IndexError) as failure:
+            candidate = type(failure)
+    finally:
+        graph.close()
+    if isinstance(expected, type) or isinstance(candidate, type):
+        assert isinstance(expected, type) and isinstance(candidate, type), (expected, candidate)
+    else:
+        assert np.array_equal(candidate, expected)

@@ -157,3 +157,25 @@ def test_dissolve_and_the_whole_pile_match_oracle(ref):
     metacell, dissolved = oracle.dissolve_metacells(umis, candidate, deviant, cell_umis, **arguments)
     assert np.array_equal(whole["candidate"], candidate) and np.array_equal(whole["deviant"], deviant)
     assert np.array_equal(whole["metacell"], metacell) and np.array_equal(whole["dissolved"], dissolved)
+
+
+def test_deviants_and_dissolve_corner_cases(ref):
+    """A pile of no more cells than `max_gap_cells_count` has no deviants (tools/deviants.py:260-261); candidates under four
+    cells are never looked at (gaps.cpp:62-64); when every candidate is under the minimal size everything is dissolved."""
+    from metacells_b200.deviants import find_deviant_cells
+    from metacells_b200.dissolve import dissolve_metacells
+    from metacells_b200.pipeline import Pile
+
+    tiny = synth_umis(3, 500, seed=5, depth_scale=3.0)
+    with Pile(tiny) as pile:
+        assert not find_deviant_cells(pile, np.zeros(3, dtype="int32")).any()
+    umis = synth_umis(120, 2000, seed=6, depth_scale=3.0)
+    cell_umis = np.asarray(umis.sum(axis=1)).reshape(-1).astype("float32")
+    candidates = (np.arange(120) // 3).astype("int32")  # forty candidates of three cells
+    with Pile(umis) as pile:
+        deviants = find_deviant_cells(pile, candidates)
+        assert np.array_equal(deviants, oracle.gaps_deviant_cells(umis, candidates, ref)) and not deviants.any()
+        metacell, dissolved = dissolve_metacells(pile, candidates, deviants, cell_umis)
+    expected = oracle.dissolve_metacells(umis, candidates, deviants, cell_umis)
+    assert np.array_equal(metacell, expected[0]) and np.array_equal(dissolved, expected[1])
+    assert dissolved.all() and (metacell == -1).all()
