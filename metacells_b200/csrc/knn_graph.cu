@@ -158,9 +158,13 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                 // the row's largest t can only be an entry that passes, when there is one (rows without are redone
                 // by balance_best_kernel)
                 uint32_t best = 0;
+                float t[2] = {0.0f, 0.0f};  // the square root is taken once, for the row's best entry and for what is parked
 #pragma unroll
                 for (int half = 0; half < 2; ++half)
-                    if (passes[half]) best = max(best, pack_tile_best(balanced_t_of_product(product[half]), lane + 32 * half));
+                    if (passes[half]) {
+                        t[half] = balanced_t_of_product(product[half]);
+                        best = max(best, pack_tile_best(t[half], lane + 32 * half));
+                    }
                 best = __reduce_max_sync(0xffffffffu, best);
                 const uint32_t mask0 = __ballot_sync(0xffffffffu, kept[0]), mask1 = __ballot_sync(0xffffffffu, kept[1]);
                 const int count = __popc(mask0) + __popc(mask1);
@@ -170,7 +174,7 @@ __global__ void __launch_bounds__(BAL_THREADS) balance_kernel(BalanceParams p) {
                     for (int half = 0; half < 2; ++half)
                         if (kept[half])
                             slots[(half ? __popc(mask0) : 0) + __popc((half ? mask1 : mask0) & lower_lanes)] =
-                                __fadd_rn(balanced_t_of_product(product[half]), p.shift);
+                                __fadd_rn(t[half], p.shift);
                     if (lane == 0) p.masks[row * p.tiles + column_tile] = (unsigned long long)mask0 | ((unsigned long long)mask1 << 32);
                 }
                 if (lane == 0) {
