@@ -194,16 +194,30 @@ __global__ void accumulate_totals_kernel(const float* __restrict__ out_w, const 
     incoming_log2[node] = total_incoming > 0 ? mc_log2(total_incoming, t) : 0.0;  // :124
 }
 
-__global__ void rescore_table_kernel(Entry* __restrict__ table, int64_t entries) {
+// Scores of the totals, and `linked_bits`: bit p of node v's words is set iff v has any weight towards partition p, that is
+// iff table[v][p] is not the default entry (0, 0, log2(EPSILON) / 2).  One lane per (node, partition padded to 32).
+__global__ void rescore_table_kernel(Entry* __restrict__ table, int nodes, int partitions, int words,
+                                     uint32_t* __restrict__ linked_bits) {
     __shared__ unsigned long long staged[LOG_TABLE_WORDS];
     stage_log_tables(staged);
     __syncthreads();
     const LogTables t = log_tables(staged);
     const double default_score = rescore(0.0, 0.0, t);  // NodeScore(): log2(EPSILON) / 2
-    for (int64_t at = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; at < entries; at += int64_t(gridDim.x) * blockDim.x) {
-        Entry entry = table[at];
-        entry.score = (entry.outgoing != 0.0 || entry.incoming != 0.0) ? rescore(entry.outgoing, entry.incoming, t) : default_score;
-        table[at] = entry;
+    const int64_t items = int64_t(nodes) * words * 32;
+    for (int64_t at = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; at < items; at += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t word = at >> 5;
+        const int node = int(word / words);
+        const int p = int(word - int64_t(node) * words) * 32 + int(at & 31);
+        bool linked = false;
+        if (p < partitions) {
+            Entry* slot = table + int64_t(node) * partitions + p;
+            Entry entry = *slot;
+            linked = entry.outgoing != 0.0 || entry.incoming != 0.0;
+            entry.score = linked ? rescore(entry.outgoing, entry.incoming, t) : default_score;
+            *slot = entry;
+        }
+        const unsigned mask = __ballot_sync(FULL, linked);
+        if ((at & 31) == 0) linked_bits[word] = mask;
     }
 }
 
@@ -289,6 +303,7 @@ struct OptParams {
     const float* mass_of_nodes;
     int32_t* partition_of_nodes;
     Entry* table;
+    uint32_t* linked_bits;  // [nodes][words]: the entries of the table that are not the default one
     Entry* self;
     double* temperature_of_nodes;
     uint8_t* frozen;
@@ -299,7 +314,7 @@ struct OptParams {
     int32_t* sizes;
     double* masses;
     double* scores;
-    int nodes, partitions, padded, warps;
+    int nodes, partitions, padded, warps, words;
     int parallel_shuffle;  // the shared-memory plan has room for the raw generator stream (8 bytes per node)
     Bounds bounds;
     double cooldown_pass, cooldown_node;
@@ -529,22 +544,49 @@ __device__ void refresh_partition(const PartitionState& s, int p, const Bounds& 
 __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const WarpBuffers& B, const LogTables& t,
                              int node, double temperature, int lane) {
     const int partitions = P.partitions;
-    const int current = P.partition_of_nodes[node];
-    if (S.sizes[current] < 2) return 0;  // :575
     const long long entered = clock64();
     const Entry* row = P.table + int64_t(node) * partitions;
-    const Entry current_entry = row[current];
+    const uint32_t* bits = P.linked_bits + int64_t(node) * P.words;
+    uint32_t first_bits = lane < P.words ? bits[lane] : 0u;  // in flight beside the gather below
+    const Entry current_entry = P.self[node];                // == row[current], with the partition: one gather
+    const int current = int(current_entry.partition);
+    if (S.sizes[current] < 2) return 0;  // :575
     const int current_connectivity = connectivity(current_entry.outgoing, current_entry.incoming);
 
-    // :647-662 and :699-723
-#pragma unroll 4
-    for (int p = lane; p < partitions; p += 32) {
-        const Entry entry = row[p];
-        if (p == current) {
-            B.cold[p] = -entry.score;
-            B.total[p] = -entry.score;
-            B.linked[p] = 0;
-        } else {
+    // :647-662 and :699-723.  Most of the row is the default entry (a node has weight towards a few dozen partitions):
+    // every slot gets the default entry's values, then only the entries `linked_bits` marks are read (a 16 KB row scan by
+    // each of 16 warps at once is bound by what one SM takes from L2; the listed entries are a tenth of it).
+    {
+        const double default_score = rescore(0.0, 0.0, t);
+        const int unlinked = current_connectivity > 0 ? 65536 - current_connectivity : 0;
+        for (int p = lane; p < partitions; p += 32) {
+            B.cold[p] = default_score;
+            B.total[p] = default_score;
+            B.linked[p] = unlinked;
+        }
+        int listed = 0;
+        for (int first = 0; first < P.words; first += 32) {
+            uint32_t mine = first == 0 ? first_bits : (first + lane < P.words ? bits[first + lane] : 0u);
+            int before = __popc(mine);
+#pragma unroll
+            for (int step = 1; step < 32; step <<= 1) {
+                const int below = __shfl_up_sync(FULL, before, step);
+                if (lane >= step) before += below;
+            }
+            const int total = __shfl_sync(FULL, before, 31);
+            int at = listed + before - __popc(mine);
+            while (mine) {
+                B.list[at++] = uint16_t((first + lane) * 32 + __ffs(mine) - 1);
+                mine &= mine - 1u;
+            }
+            listed += total;
+        }
+        __syncwarp();
+#pragma unroll 2
+        for (int i = lane; i < listed; i += 32) {
+            const int p = B.list[i];
+            if (p == current) continue;
+            const Entry entry = row[p];
             const int other_connectivity = connectivity(entry.outgoing, entry.incoming);
             int disconnected = 0;
             if (current_connectivity > 0 && other_connectivity == 0) disconnected = 1;
@@ -552,6 +594,11 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
             B.cold[p] = entry.score;
             B.total[p] = entry.score;
             B.linked[p] = (other_connectivity - current_connectivity) + disconnected * 65536;
+        }
+        if (lane == 0) {
+            B.cold[current] = -current_entry.score;
+            B.total[current] = -current_entry.score;
+            B.linked[current] = 0;
         }
     }
     __syncwarp();
@@ -609,23 +656,43 @@ __device__ int evaluate_node(const OptParams& P, const PartitionState& S, const 
             if (lane == 0) B.fine[1] += now - lap + (long long)(diff[0] == 1e300) + (long long)(diff[EVAL_UNROLL - 1] == 1e300);
             lap = now;
         }
-        unsigned peers_of[EVAL_UNROLL];  // the groups of equal partitions of all four chunks first: independent of each other
+        // The groups of equal partitions of all four chunks first (independent of each other), and for every group a run of
+        // consecutive staging slots, in lane order inside the run: the first lane of a group then adds exactly its group's
+        // terms from addresses known before the chain starts (32 predicated steps over all the slots, or a walk over the
+        // set bits whose loads depend on the bit found, were both measured slower).
+        int leader[EVAL_UNROLL], members[EVAL_UNROLL], first[EVAL_UNROLL], slot[EVAL_UNROLL];
 #pragma unroll
-        for (int j = 0; j < EVAL_UNROLL; ++j) peers_of[j] = __match_any_sync(FULL, q[j]);
+        for (int j = 0; j < EVAL_UNROLL; ++j) {
+            const unsigned peers = __match_any_sync(FULL, q[j]);
+            leader[j] = __ffs(peers) - 1;
+            members[j] = __popc(peers);
+            slot[j] = __popc(peers & ((1u << lane) - 1u));
+            first[j] = leader[j] == lane ? members[j] : 0;
+        }
+#pragma unroll
+        for (int step = 1; step < 32; step <<= 1) {
+#pragma unroll
+            for (int j = 0; j < EVAL_UNROLL; ++j) {
+                const int below = __shfl_up_sync(FULL, first[j], step);
+                if (lane >= step) first[j] += below;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < EVAL_UNROLL; ++j) {
+            first[j] = __shfl_sync(FULL, first[j] - members[j], leader[j]);  // at a group's first lane: the slots before it
+            slot[j] += first[j];
+        }
 #pragma unroll
         for (int j = 0; j < EVAL_UNROLL; ++j) {
             if (start + j * 32 >= count) break;
-            const unsigned peers = peers_of[j];
             if (linked[j] != 0) atomicAdd(&B.linked[q[j]], linked[j]);  // integers: any order; rarely non-zero
-            B.staging[lane] = diff[j];
+            B.staging[slot[j]] = diff[j];
             __syncwarp();
-            if (q[j] >= 0 && lane == __ffs(peers) - 1) {  // the first lane of a partition adds its terms in lane order
-                // (32 predicated steps, unrolled: the loads of the terms issue ahead of the dependent adds; a loop over
-                // the set bits only was measured slower)
+            if (q[j] >= 0 && lane == leader[j]) {
                 double chain = B.cold[q[j]];
-#pragma unroll 8
-                for (int source = 0; source < 32; ++source)
-                    if (peers >> source & 1u) chain = dadd(chain, B.staging[source]);
+                const double* terms = B.staging + first[j];
+#pragma unroll 4
+                for (int i = 0; i < members[j]; ++i) chain = dadd(chain, terms[i]);
                 B.cold[q[j]] = chain;
             }
             __syncwarp();
@@ -752,6 +819,9 @@ __device__ void apply_move(const OptParams& P, const PartitionState& S, const Lo
         const double outgoing_weight = neighbour.outgoing;
         const double incoming_weight = neighbour.incoming;
         Entry* row = P.table + int64_t(other) * partitions;
+        uint32_t* words = P.linked_bits + int64_t(other) * P.words;  // every `other` is one thread's: plain read-modify-write
+        uint32_t word_from = words[from >> 5];
+        uint32_t word_to = words[to >> 5];
         Entry left = row[from];
         left.incoming = clamp0(dsub(left.incoming, outgoing_weight));
         left.outgoing = clamp0(dsub(left.outgoing, incoming_weight));
@@ -762,6 +832,16 @@ __device__ void apply_move(const OptParams& P, const PartitionState& S, const Lo
         joined.outgoing = clamp0(dadd(joined.outgoing, incoming_weight));
         joined.score = rescore(joined.outgoing, joined.incoming, t);
         row[to] = joined;
+        const bool left_empty = left.outgoing == 0.0 && left.incoming == 0.0;
+        const bool joined_linked = joined.outgoing != 0.0 || joined.incoming != 0.0;
+        if ((from >> 5) == (to >> 5)) {
+            if (left_empty) word_from &= ~(1u << (from & 31));
+            if (joined_linked) word_from |= 1u << (to & 31);
+            words[from >> 5] = word_from;
+        } else {
+            if (left_empty) words[from >> 5] = word_from & ~(1u << (from & 31));
+            if (joined_linked && !(word_to >> (to & 31) & 1u)) words[to >> 5] = word_to | 1u << (to & 31);
+        }
         const int own = int(P.self[other].partition);
         if (own == from) {
             left.partition = own;
@@ -1098,10 +1178,12 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
     const bool parallel_shuffle = n >= 64 && n <= 46340 && fixed + shuffle_bytes <= shared_limit && std::getenv("MCB_SERIAL_SHUFFLE") == nullptr;
     const size_t shared_bytes = fixed + std::max(size_t(warps) * warp_buffer_bytes(padded), parallel_shuffle ? shuffle_bytes : size_t(n) * 2);
 
-    Scratch table, self, neighbours, union_count, incoming_log2, sizes, masses, scores, temperatures, frozen,
+    Scratch table, linked_bits, self, neighbours, union_count, incoming_log2, sizes, masses, scores, temperatures, frozen,
         order, visit_temperature, active, result, stats_device;
     const int64_t entries = int64_t(n) * partitions;
     MCB_TRY(table.alloc(size_t(entries) * sizeof(Entry), stream));
+    const int words = int(ceil_div(partitions, 32));
+    MCB_TRY(linked_bits.alloc(size_t(n) * words * 4, stream));
     MCB_TRY(self.alloc(size_t(n) * sizeof(Entry), stream));
     MCB_TRY(neighbours.alloc(size_t(union_capacity) * sizeof(Neighbour), stream));
     MCB_TRY(union_count.alloc(size_t(n) * 4, stream));
@@ -1129,7 +1211,8 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
                      out_w, out_idx, out_ptr, in_w, in_idx, in_ptr, partition_of_nodes, n, partitions, table.as<Entry>(),
                      incoming_log2.as<double>(), flags + 2));
     MCB_LAUNCH_CHECK();
-    MCB_PROFILED("rescore_table", stream, rescore_table_kernel<<<wide_blocks, 256, 0, stream>>>(table.as<Entry>(), entries));
+    MCB_PROFILED("rescore_table", stream, rescore_table_kernel<<<wide_blocks, 256, 0, stream>>>(
+                     table.as<Entry>(), n, partitions, words, linked_bits.as<uint32_t>()));
     MCB_LAUNCH_CHECK();
     MCB_PROFILED("partition_totals", stream, partition_totals_kernel<<<int(ceil_div(partitions, 32)), 32, 0, stream>>>(
                      partition_of_nodes, mass_of_nodes, table.as<Entry>(), n, partitions, sizes.as<int32_t>(),
@@ -1154,6 +1237,8 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
         params.mass_of_nodes = mass_of_nodes;
         params.partition_of_nodes = partition_of_nodes;
         params.table = table.as<Entry>();
+        params.linked_bits = linked_bits.as<uint32_t>();
+        params.words = words;
         params.self = self.as<Entry>();
         params.temperature_of_nodes = temperatures.as<double>();
         params.frozen = frozen.as<uint8_t>();
