@@ -813,54 +813,83 @@ __device__ void apply_move(const OptParams& P, const PartitionState& S, const Lo
     const int partitions = P.partitions;
     const int64_t base = int64_t(P.out_ptr[node]) + P.in_ptr[node];
     const int count = P.union_count[node];
-    for (int e = threadIdx.x; e < count; e += blockDim.x) {
-        const Neighbour neighbour = P.neighbours[base + e];
-        const int other = neighbour.node;
-        const double outgoing_weight = neighbour.outgoing;
-        const double incoming_weight = neighbour.incoming;
-        Entry* row = P.table + int64_t(other) * partitions;
-        uint32_t* words = P.linked_bits + int64_t(other) * P.words;  // every `other` is one thread's: plain read-modify-write
-        uint32_t word_from = words[from >> 5];
-        uint32_t word_to = words[to >> 5];
-        Entry left = row[from];
-        left.incoming = clamp0(dsub(left.incoming, outgoing_weight));
-        left.outgoing = clamp0(dsub(left.outgoing, incoming_weight));
-        left.score = rescore(left.outgoing, left.incoming, t);
-        row[from] = left;
-        Entry joined = row[to];
-        joined.incoming = clamp0(dadd(joined.incoming, outgoing_weight));
-        joined.outgoing = clamp0(dadd(joined.outgoing, incoming_weight));
-        joined.score = rescore(joined.outgoing, joined.incoming, t);
-        row[to] = joined;
-        const bool left_empty = left.outgoing == 0.0 && left.incoming == 0.0;
-        const bool joined_linked = joined.outgoing != 0.0 || joined.incoming != 0.0;
-        if ((from >> 5) == (to >> 5)) {
-            if (left_empty) word_from &= ~(1u << (from & 31));
-            if (joined_linked) word_from |= 1u << (to & 31);
-            words[from >> 5] = word_from;
-        } else {
-            if (left_empty) words[from >> 5] = word_from & ~(1u << (from & 31));
-            if (joined_linked && !(word_to >> (to & 31) & 1u)) words[to >> 5] = word_to | 1u << (to & 31);
+    // what the one thread of the tail needs, in flight during the loop (the node's own row is not touched by its move)
+    Entry own{};
+    double node_mass = 0.0;
+    if (threadIdx.x == 0) {
+        own = P.table[int64_t(node) * partitions + to];
+        node_mass = P.mass_of_nodes[node];
+    }
+    // Up to MOVE_ITEMS neighbours per thread and round: every load of all of them (two entries, two bitmap words and the
+    // neighbour's partition each: latency of HBM, the table is larger than L2) before the first store.  The neighbours are
+    // distinct nodes, so their rows, words and self[] entries do not overlap.
+    constexpr int MOVE_ITEMS = 1;
+    for (int e0 = threadIdx.x; e0 < count; e0 += MOVE_ITEMS * blockDim.x) {
+        Neighbour neighbour[MOVE_ITEMS];
+        Entry left[MOVE_ITEMS], joined[MOVE_ITEMS];
+        uint32_t word_from[MOVE_ITEMS], word_to[MOVE_ITEMS];
+        int own_partition[MOVE_ITEMS];
+        bool has[MOVE_ITEMS];
+#pragma unroll
+        for (int u = 0; u < MOVE_ITEMS; ++u) {
+            has[u] = e0 + u * int(blockDim.x) < count;
+            neighbour[u] = P.neighbours[base + (has[u] ? e0 + u * int(blockDim.x) : e0)];
         }
-        const int own = int(P.self[other].partition);
-        if (own == from) {
-            left.partition = own;
-            P.self[other] = left;
-        } else if (own == to) {
-            joined.partition = own;
-            P.self[other] = joined;
+#pragma unroll
+        for (int u = 0; u < MOVE_ITEMS; ++u) {
+            if (!has[u]) continue;
+            const Entry* row = P.table + int64_t(neighbour[u].node) * partitions;
+            const uint32_t* words = P.linked_bits + int64_t(neighbour[u].node) * P.words;
+            word_from[u] = words[from >> 5];
+            word_to[u] = words[to >> 5];
+            left[u] = row[from];
+            joined[u] = row[to];
+            own_partition[u] = int(P.self[neighbour[u].node].partition);
+        }
+#pragma unroll
+        for (int u = 0; u < MOVE_ITEMS; ++u) {
+            if (!has[u]) continue;
+            const int other = neighbour[u].node;
+            const double outgoing_weight = neighbour[u].outgoing;
+            const double incoming_weight = neighbour[u].incoming;
+            Entry* row = P.table + int64_t(other) * partitions;
+            uint32_t* words = P.linked_bits + int64_t(other) * P.words;
+            left[u].incoming = clamp0(dsub(left[u].incoming, outgoing_weight));
+            left[u].outgoing = clamp0(dsub(left[u].outgoing, incoming_weight));
+            left[u].score = rescore(left[u].outgoing, left[u].incoming, t);
+            row[from] = left[u];
+            joined[u].incoming = clamp0(dadd(joined[u].incoming, outgoing_weight));
+            joined[u].outgoing = clamp0(dadd(joined[u].outgoing, incoming_weight));
+            joined[u].score = rescore(joined[u].outgoing, joined[u].incoming, t);
+            row[to] = joined[u];
+            const bool left_empty = left[u].outgoing == 0.0 && left[u].incoming == 0.0;
+            const bool joined_linked = joined[u].outgoing != 0.0 || joined[u].incoming != 0.0;
+            if ((from >> 5) == (to >> 5)) {
+                uint32_t word = word_from[u];
+                if (left_empty) word &= ~(1u << (from & 31));
+                if (joined_linked) word |= 1u << (to & 31);
+                if (word != word_from[u]) words[from >> 5] = word;
+            } else {
+                if (left_empty) words[from >> 5] = word_from[u] & ~(1u << (from & 31));
+                if (joined_linked && !(word_to[u] >> (to & 31) & 1u)) words[to >> 5] = word_to[u] | 1u << (to & 31);
+            }
+            if (own_partition[u] == from) {
+                left[u].partition = from;
+                P.self[other] = left[u];
+            } else if (own_partition[u] == to) {
+                joined[u].partition = to;
+                P.self[other] = joined[u];
+            }
         }
     }
     if (threadIdx.x == 0) {
         P.partition_of_nodes[node] = to;
-        Entry own = P.table[int64_t(node) * partitions + to];
         own.partition = to;
         P.self[node] = own;
         S.sizes[from] -= 1;
         S.sizes[to] += 1;
         S.scores[from] = dadd(S.scores[from], cold_from);
         S.scores[to] = dadd(S.scores[to], cold_to);
-        const double node_mass = P.mass_of_nodes[node];
         S.masses[from] = dsub(S.masses[from], node_mass);
         S.masses[to] = dadd(S.masses[to], node_mass);
     }
