@@ -416,7 +416,7 @@ int pile_log_fraction(mcb_pile* pile, const int32_t* feature_genes, int64_t* fea
     const int32_t* genes_device = pile->top_genes.as<int32_t>();
     if (feature_genes != nullptr) {
         MCB_TRY(d_genes.alloc((size_t)features * sizeof(int32_t), stream));
-        MCB_CUDA(cudaMemcpyAsync(d_genes.ptr, feature_genes, (size_t)features * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+        MCB_TRY(upload_small(d_genes.ptr, feature_genes, (size_t)features * sizeof(int32_t), stream));
         genes_device = d_genes.as<int32_t>();
     }
     MCB_TRY(d_slot.alloc((size_t)pile->genes * sizeof(int32_t), stream));
@@ -446,7 +446,7 @@ int pile_log_fraction(mcb_pile* pile, const int32_t* feature_genes, int64_t* fea
             MCB_CUDA(cudaMalloc(&cache.device, (size_t)table_size * sizeof(float)));
             cache.host.assign(log_table, log_table + table_size);
             cache.device_index = device_index;
-            MCB_CUDA(cudaMemcpyAsync(cache.device, cache.host.data(), (size_t)table_size * sizeof(float), cudaMemcpyHostToDevice, stream));
+            MCB_TRY(upload_small(cache.device, cache.host.data(), (size_t)table_size * sizeof(float), stream));
         }
         table_device = cache.device;
     }
@@ -939,7 +939,7 @@ int mcb_host_sliding_median_f32(const float* values, int64_t count, int64_t wind
     Scratch d_values, d_out;
     MCB_TRY(d_values.alloc((size_t)count * sizeof(float), stream));
     MCB_TRY(d_out.alloc((size_t)outputs * sizeof(float), stream));
-    MCB_CUDA(cudaMemcpyAsync(d_values.ptr, values, (size_t)count * sizeof(float), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(upload_small(d_values.ptr, values, (size_t)count * sizeof(float), stream));
     MCB_PROFILED("sliding_median", stream,
                  sliding_median_kernel<<<(unsigned)ceil_div(outputs, 8), 256, 0, stream>>>(d_values.as<float>(), outputs, (int)window,
                                                                                          d_out.as<float>()));
@@ -959,8 +959,8 @@ int mcb_host_sliding_median_ordered_f32(const float* values, const int64_t* orde
     MCB_TRY(d_values.alloc((size_t)count * sizeof(float), stream));
     MCB_TRY(d_order.alloc((size_t)count * sizeof(int64_t), stream));
     MCB_TRY(d_out.alloc((size_t)count * sizeof(double), stream));
-    MCB_CUDA(cudaMemcpyAsync(d_values.ptr, values, (size_t)count * sizeof(float), cudaMemcpyHostToDevice, stream));
-    MCB_CUDA(cudaMemcpyAsync(d_order.ptr, order, (size_t)count * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(upload_small(d_values.ptr, values, (size_t)count * sizeof(float), stream));
+    MCB_TRY(upload_small(d_order.ptr, order, (size_t)count * sizeof(int64_t), stream));
     MCB_PROFILED("sliding_median", stream,
                  sliding_median_ordered_kernel<<<(unsigned)ceil_div(count, 8), 256, 0, stream>>>(
                      d_values.as<float>(), d_order.as<int64_t>(), count, (int)window, d_out.as<double>()));
@@ -1006,7 +1006,7 @@ int mcb_pile_gene_columns(mcb_pile* pile, const int32_t* genes, int64_t count, f
     MCB_REQUIRE(count <= 65535, "pile: at most 65535 gene columns per call");
     MCB_TRY(d_genes.alloc((size_t)count * sizeof(int32_t), stream));
     MCB_TRY(d_values.alloc((size_t)count * pile->cells * sizeof(float), stream));
-    MCB_CUDA(cudaMemcpyAsync(d_genes.ptr, genes, (size_t)count * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(upload_small(d_genes.ptr, genes, (size_t)count * sizeof(int32_t), stream));
     const float* source = pile->has_downsampled ? pile->downsampled.as<float>() : pile->data;
     const dim3 grid((unsigned)ceil_div(pile->cells, 256), (unsigned)count);
     MCB_PROFILED("gene_columns", stream,
@@ -1072,7 +1072,7 @@ int mcb_pile_sum_groups(mcb_pile* pile, const int32_t* group_of_cells, int64_t g
     Scratch d_groups, d_sums;
     MCB_TRY(d_groups.alloc((size_t)pile->cells * sizeof(int32_t), stream));
     MCB_TRY(d_sums.alloc((size_t)groups * pile->genes * sizeof(double), stream));
-    MCB_CUDA(cudaMemcpyAsync(d_groups.ptr, group_of_cells, (size_t)pile->cells * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(upload_small(d_groups.ptr, group_of_cells, (size_t)pile->cells * sizeof(int32_t), stream));
     MCB_CUDA(cudaMemsetAsync(d_sums.ptr, 0, (size_t)groups * pile->genes * sizeof(double), stream));
     MCB_PROFILED("pile_sum_groups", stream,
                  pile_sum_groups_kernel<<<(unsigned)ceil_div(pile->cells, 8), 256, 0, stream>>>(

@@ -104,6 +104,7 @@ static inline int copy_to_host(void* host, const void* device, size_t bytes, cud
     return MCB_OK;
 }
 
+int upload_small(void* device, const void* host, size_t bytes, cudaStream_t stream);  // host -> device, not through the copy engine when small
 int sm_count();
 int allow_dynamic_shared(const void* kernel, size_t bytes);  // opt in to `bytes` of dynamic shared memory (only ever raised)
 int thread_stream(cudaStream_t* stream);  // the calling host thread's own stream on the current device

@@ -376,8 +376,8 @@ int correlate_umma_launch(const float* a_hi, const float* a_lo, int64_t rows_a, 
     tile_order(tiles_a, tiles_b, symmetric, order);
     Scratch tiles;
     MCB_TRY(tiles.alloc(order.size() * sizeof(int2), stream));
-    // pageable source: the copy is staged before the call returns, so `order` may go out of scope
-    MCB_CUDA(cudaMemcpyAsync(tiles.ptr, order.data(), order.size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
+    // staged before the call returns (page-locked ring or the driver's own staging), so `order` may go out of scope
+    MCB_TRY(upload_small(tiles.ptr, order.data(), order.size() * sizeof(int2), stream));
     UmmaParams p{};
     p.output = output;
     p.out_stride = out_stride;

@@ -1179,7 +1179,7 @@ int partitions_launch(const float* out_w, const int32_t* out_idx, const int32_t*
     MCB_TRY(flags_device.alloc(8 * sizeof(int), stream));
     int* flags = flags_device.as<int>();
     const int flags_init[8] = {-1, 0, 0, 0, 0, 0, 0, 0};
-    MCB_CUDA(cudaMemcpyAsync(flags, flags_init, sizeof(flags_init), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(upload_small(flags, flags_init, sizeof(flags_init), stream));
     MCB_PROFILED("partition_range", stream, partition_range_kernel<<<std::min<int>(int(ceil_div(n, 256)), 1024), 256, 0, stream>>>(
                      partition_of_nodes, n, flags));
     MCB_LAUNCH_CHECK();

@@ -127,6 +127,80 @@ int pinned_staging(void** buffer) {
     return MCB_OK;
 }
 
+// Host -> device for the small arrays a stage takes from the host (gene lists, orders, tile lists, flags) WITHOUT the copy
+// engine.  The engine serves copies in the order they were submitted: once the next pile's CSR (hundreds of MB, a stream of
+// its own) is in its queue, a 4 KB cudaMemcpyAsync of the current pile's stream waits behind all of it, and the current
+// pile's kernels with it -- upload and compute end up one after the other (measured: 16 ms per pile instead of 9).  So the
+// bytes go into a page-locked slice of the calling host thread and a kernel of the stream reads them over the link.
+// The slice is a ring; before it wraps the thread waits for the last kernel that read from it (long done by then).
+namespace {
+__global__ void upload_small_kernel(uint32_t* __restrict__ device, const uint32_t* __restrict__ host, size_t words) {
+    for (size_t at = blockIdx.x * size_t(blockDim.x) + threadIdx.x; at < words; at += size_t(gridDim.x) * blockDim.x)
+        device[at] = host[at];
+}
+}  // namespace
+
+int upload_small(void* device, const void* host, size_t bytes, cudaStream_t stream) {
+    constexpr size_t SLICE = size_t(1) << 20, SLICES = 64, LIMIT = SLICE / 2;
+    struct Ring {
+        unsigned char* slice = nullptr;
+        size_t cursor = 0;
+        cudaEvent_t last = nullptr;
+        cudaStream_t stream = nullptr;
+        bool pending = false, asked = false;
+    };
+    static std::mutex mutex;
+    static unsigned char* block = nullptr;
+    static bool tried = false;
+    static std::atomic<size_t> next{0};
+    static thread_local Ring ring;
+    if (bytes == 0)
+        return MCB_OK;
+    static const bool disabled = getenv("MCB_NO_SMALL_UPLOADS") != nullptr;  // developer aid: everything through the copy engine
+    const bool fits = !disabled && bytes <= LIMIT && bytes % 4 == 0 && reinterpret_cast<uintptr_t>(device) % 4 == 0;
+    if (fits && !ring.asked) {
+        ring.asked = true;
+        {
+            std::lock_guard<std::mutex> lock(mutex);
+            if (!tried) {
+                tried = true;
+                void* allocated = nullptr;
+                if (cudaHostAlloc(&allocated, SLICE * SLICES, cudaHostAllocPortable | cudaHostAllocMapped) == cudaSuccess)
+                    block = static_cast<unsigned char*>(allocated);
+                else
+                    cudaGetLastError();  // not fatal: the copy engine remains
+            }
+        }
+        const size_t slot = next.fetch_add(1);
+        if (block != nullptr && slot < SLICES && cudaEventCreateWithFlags(&ring.last, cudaEventDisableTiming) == cudaSuccess)
+            ring.slice = block + slot * SLICE;
+    }
+    if (!fits || ring.slice == nullptr) {
+        MCB_CUDA(cudaMemcpyAsync(device, host, bytes, cudaMemcpyHostToDevice, stream));
+        return MCB_OK;
+    }
+    const size_t rounded = (bytes + 255) / 256 * 256;
+    if (ring.pending && (ring.stream != stream || ring.cursor + rounded > SLICE)) {
+        MCB_CUDA(cudaEventSynchronize(ring.last));  // every kernel that read the ring was launched on ring.stream before it
+        ring.pending = false;
+        ring.cursor = 0;
+    }
+    if (ring.cursor + rounded > SLICE)
+        ring.cursor = 0;
+    unsigned char* staged = ring.slice + ring.cursor;
+    memcpy(staged, host, bytes);
+    const size_t words = bytes / 4;
+    const int blocks = int(std::min<size_t>((words + 255) / 256, 64));
+    MCB_PROFILED("upload_small", stream, upload_small_kernel<<<blocks, 256, 0, stream>>>(
+                     static_cast<uint32_t*>(device), reinterpret_cast<const uint32_t*>(staged), words));
+    MCB_LAUNCH_CHECK();
+    MCB_CUDA(cudaEventRecord(ring.last, stream));
+    ring.cursor += rounded;
+    ring.stream = stream;
+    ring.pending = true;
+    return MCB_OK;
+}
+
 // A stream of the calling host thread's own (per device): host entry points that may be called from several
 // threads at once (one pile each) run side by side instead of queueing on the legacy default stream.  The stream
 // outlives its thread on purpose: piles and graphs created by a worker thread keep using it (their scratch is freed on

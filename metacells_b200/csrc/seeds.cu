@@ -527,7 +527,7 @@ int seeds_launch(const float* out_w, const int32_t* out_idx, const int32_t* out_
     MCB_TRY(result.alloc(4 * sizeof(int32_t), stream));
     const int32_t result_init[4] = {0, 0, 0, -1};
     int32_t result_host[4];
-    MCB_CUDA(cudaMemcpyAsync(result.ptr, result_init, sizeof(result_init), cudaMemcpyHostToDevice, stream));
+    MCB_TRY(upload_small(result.ptr, result_init, sizeof(result_init), stream));
     MCB_PROFILED("seeds_prepare", stream, seeds_prepare_kernel<<<int(std::min<int64_t>(ceil_div(n, 8), int64_t(sm_count()) * 8)), 256, 0, stream>>>(
                      in_idx, in_ptr, seed_of_nodes, n, connected.as<int32_t>(), result.as<int32_t>()));
     MCB_LAUNCH_CHECK();
