@@ -441,9 +441,10 @@ def run_gpu_arm(args):
 
     def steps_e2e_overlapped(steps):
         """K end-to-end steps as a worker walks its piles (divide_and_conquer.py:1264-1295 hands piles out one after the
-        other): the upload of pile k + 1 is started after the first launches of pile k and runs under its kernels on the
-        pile's copy stream, and the graph of pile k is copied to the host (mcb_graph_read_start, a stream of the graph's
-        own) under the first kernels of pile k + 1.  Every step still uploads its pile and reads its graph back inside
+        other): the upload of pile k + 1 is started before the launches of pile k (its buffers are allocated in stream order: behind
+        pile k's downsampling the copy would start a millisecond later) and runs under its kernels on the pile's copy
+        stream, and the graph of pile k is copied to the host (mcb_graph_read_start, a stream of the graph's own) under the
+        first kernels of pile k + 1.  Every step still uploads its pile and reads its graph back inside
         the timed region; only the first upload and the last read are exposed."""
         nnz = 0
         upload = uploader["upload"]
@@ -463,13 +464,16 @@ def run_gpu_arm(args):
                 library.call("mcb_graph_read_finish", graph)
                 library.lib.mcb_graph_free(graph)
 
+        upload_late = os.environ.get("MCB_BENCH_UPLOAD_AFTER_LAUNCH")  # developer aid: the order measured 0.6 ms slower
         for index in range(steps):
             pile = pending.pop(0)
             lap("start")
+            if not upload_late and index + 1 < steps:
+                pending.append(upload())
 
             def meanwhile(last=index + 1 == steps):
                 lap("launched")
-                if not last:
+                if not last and upload_late:
                     pending.append(upload())
                 lap("upload issued")
                 finish_read()  # before this pile's graph is read into the same host buffers
