@@ -110,6 +110,41 @@ def test_ordered_sliding_median_matches_the_host_path():
         assert np.array_equal(ahead, expected, equal_nan=True)
 
 
+def test_small_host_arrays_through_the_page_locked_ring():
+    """The order and values of the sliding median reach the device through `upload_small` (runtime.cu: a page-locked ring of
+    1 MB per host thread read by a kernel, not the copy engine): enough calls to wrap the ring many times, from two host
+    threads at once, with and without the ring (`MCB_NO_SMALL_UPLOADS` is read once, so the second form is a subprocess)."""
+    import os
+    import subprocess
+    import sys
+    from concurrent.futures import ThreadPoolExecutor
+
+    from test_select_host import pandas_window_medians
+
+    from metacells_b200 import select
+
+    def walk(seed):
+        rng = np.random.default_rng(seed)
+        for count in (27000, 40000, 27000, 150, 35000, 27000, 43000, 27000, 200, 27000):  # 12 bytes each: the ring wraps
+            values = rng.normal(size=count).astype("float32")
+            order_by = rng.integers(0, max(count // 4, 1), size=count).astype("float32")
+            expected = select._sliding_median(values, order_by, 101, window_medians=pandas_window_medians)
+            assert np.array_equal(select._sliding_median(values, order_by, 101), expected, equal_nan=True), (seed, count)
+        return True
+
+    with ThreadPoolExecutor(max_workers=2) as pool:
+        assert all(pool.map(walk, (1, 2)))
+    if os.environ.get("MCB_NO_SMALL_UPLOADS") is None:
+        code = ("import sys; sys.path.insert(0, 'tests'); import numpy as np; from metacells_b200 import select; "
+                "from test_select_host import pandas_window_medians as p; r = np.random.default_rng(3); "
+                "v = r.normal(size=27000).astype('float32'); o = r.integers(0, 6000, size=27000).astype('float32'); "
+                "assert np.array_equal(select._sliding_median(v, o, 101), select._sliding_median(v, o, 101, window_medians=p))")
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        done = subprocess.run([sys.executable, "-c", code], cwd=root, env=dict(os.environ, MCB_NO_SMALL_UPLOADS="1"),
+                              capture_output=True, text=True, timeout=600)
+        assert done.returncode == 0, done.stderr[-2000:]
+
+
 def test_pile_graph_on_selected_genes_matches_the_staged_path():
     """`features="select"` through the pile pipeline == selecting with the oracle and building the graph stage by stage."""
     from synth import synth_umis
