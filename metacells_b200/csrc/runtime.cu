@@ -147,6 +147,7 @@ int upload_small(void* device, const void* host, size_t bytes, cudaStream_t stre
         size_t cursor = 0;
         cudaEvent_t last = nullptr;
         cudaStream_t stream = nullptr;
+        int device = -1;  // the device `last` belongs to
         bool pending = false, asked = false;
     };
     static std::mutex mutex;
@@ -172,8 +173,23 @@ int upload_small(void* device, const void* host, size_t bytes, cudaStream_t stre
             }
         }
         const size_t slot = next.fetch_add(1);
-        if (block != nullptr && slot < SLICES && cudaEventCreateWithFlags(&ring.last, cudaEventDisableTiming) == cudaSuccess)
+        if (block != nullptr && slot < SLICES)
             ring.slice = block + slot * SLICE;
+    }
+    if (fits && ring.slice != nullptr) {  // the event is the current device's: a thread that moved to another GPU gets a new one
+        int device = 0;
+        MCB_CUDA(cudaGetDevice(&device));
+        if (device != ring.device) {
+            if (ring.pending)
+                MCB_CUDA(cudaEventSynchronize(ring.last));
+            if (ring.last != nullptr)
+                cudaEventDestroy(ring.last);
+            ring.last = nullptr;
+            ring.pending = false;
+            ring.cursor = 0;
+            MCB_CUDA(cudaEventCreateWithFlags(&ring.last, cudaEventDisableTiming));
+            ring.device = device;
+        }
     }
     if (!fits || ring.slice == nullptr) {
         MCB_CUDA(cudaMemcpyAsync(device, host, bytes, cudaMemcpyHostToDevice, stream));
