@@ -4,6 +4,7 @@ import multiprocessing as mp
 import os
 
 import numpy as np
+import pytest
 
 
 def test_target_pile_size():
@@ -43,11 +44,12 @@ def _gather_worker(rank, world_size, port, queue):
     dist.destroy_process_group()
 
 
-def test_results_of_piles_are_gathered_across_ranks():
+@pytest.mark.parametrize("world_size", [2, 8])  # 8: five piles over eight ranks, three ranks hold none (the grouping piles of a walk)
+def test_results_of_piles_are_gathered_across_ranks(world_size):
     context = mp.get_context("spawn")
     queue = context.Queue()
-    port = 29500 + os.getpid() % 1000
-    workers = [context.Process(target=_gather_worker, args=(rank, 2, port, queue)) for rank in range(2)]
+    port = 29500 + (os.getpid() + world_size) % 1000
+    workers = [context.Process(target=_gather_worker, args=(rank, world_size, port, queue)) for rank in range(world_size)]
     for worker in workers:
         worker.start()
     results = [queue.get(timeout=120) for _ in workers]
