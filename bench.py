@@ -637,18 +637,29 @@ def run_gpu_arm(args):
     if expected_digest and digest != expected_digest:
         raise SystemExit(f"bench: the timed pile's k-NN graph differs from the pinned digest ({digest} != {expected_digest})")
 
+    def extra_leg(name, leg):
+        """The legs beside the headline (the atlas walk, the oversized pile, the candidates) must not cost the line that is
+        already measured: a failure every rank sees alike (a limit, out of memory) is reported under the leg's key.  A
+        failure of one rank alone still leaves the others waiting in the leg's next collective."""
+        try:
+            return leg()
+        except Exception as error:  # noqa: BLE001
+            print(f"[bench] rank {rank}: {name} failed: {error!r}", file=sys.stderr, flush=True)
+            return {"error": f"{type(error).__name__}: {error}"[:400]}
+
     atlas = None
     if args.atlas_cells > 0:
         resident.clear()  # the resident pile's arrays are not needed any more
         torch.cuda.empty_cache()
-        atlas = time_atlas_walk(args, args.atlas_cells, device, rank, world, barrier)
+        atlas = extra_leg("atlas walk", lambda: time_atlas_walk(args, args.atlas_cells, device, rank, world, barrier))
         extra = [int(text) for text in args.atlas_extra.split(",") if text.strip()]
-        if extra:
-            atlas["other_sizes"] = [time_atlas_walk(args, size, device, rank, world, barrier) for size in extra]
+        if extra and "error" not in atlas:
+            atlas["other_sizes"] = [extra_leg("atlas walk", lambda size=size: time_atlas_walk(args, size, device, rank, world, barrier))
+                                    for size in extra]
 
     oversized = None
     if world > 1 and args.oversized_cells > 0:
-        oversized = time_oversized(args, rank, world, device, barrier)
+        oversized = extra_leg("oversized pile", lambda: time_oversized(args, rank, world, device, barrier))
 
     if rank != 0:
         if world > 1:
@@ -754,7 +765,7 @@ def run_gpu_arm(args):
     if oversized is not None:
         line["oversized"] = oversized
     if world == 1 and args.candidate_piles > 0:
-        line["candidates"] = time_candidates(args, umis)
+        line["candidates"] = extra_leg("candidates", lambda: time_candidates(args, umis))
     os.sched_setaffinity(0, launcher_cpus)  # the CPU baseline uses every core the launcher gave us
     if world == 1 and not args.no_cpu_baseline:
         step, info, _ = cpu_step_factory(args)

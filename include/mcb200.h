@@ -177,6 +177,10 @@ typedef struct mcb_graph mcb_graph;
 /* compute_obs_obs_knn_graph on a float32 similarity matrix [n, n]: rank (knn_graph.py:285-297),
  * balance (:300-340), prune (:343-392), weigh (:395-407), growing k until every row keeps
  * min_outgoing_degree edges (:251-268).  Free the result with mcb_graph_free. */
+/* Test aid, computed on the HOST (no GPU needed): sums[r] = numpy's float32 np.add.reduceat over values[offsets[r] ..
+ * offsets[r + 1]) -- the row totals scipy's csr sum(axis=1) yields for tools/knn_graph.py:399 (_weigh_edges) -- by the very
+ * code the device runs for rows whose float32 total is not exact (csrc/numpy_sum.cuh).  Empty segments yield 0. */
+int mcb_host_numpy_add_reduce_f32(const float* values, const int64_t* offsets, int64_t rows, float* sums);
 int mcb_host_knn_graph_f32(const float* similarity, int64_t n, int64_t k, double balanced_ranks_factor,
                            double incoming_degree_factor, double outgoing_degree_factor, int64_t min_outgoing_degree,
                            mcb_graph** out);

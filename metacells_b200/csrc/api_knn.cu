@@ -4,6 +4,7 @@
 #include <memory>
 #include <utility>
 
+#include "numpy_sum.cuh"
 #include "common.cuh"
 #include "knn_graph.cuh"
 #include "../../include/mcb200.h"
@@ -308,6 +309,16 @@ int mcb_dev_knn_graph_f32(const float* similarity, int64_t n, int64_t k, double 
     MCB_TRY(knn_graph_device(similarity, n, k, balanced_ranks_factor, incoming_degree_factor, outgoing_degree_factor,
                              min_outgoing_degree, (cudaStream_t)stream, graph.get()));
     *out = graph.release();
+    return MCB_OK;
+}
+
+int mcb_host_numpy_add_reduce_f32(const float* values, const int64_t* offsets, int64_t rows, float* sums) {
+    MCB_REQUIRE(offsets != nullptr && sums != nullptr && rows >= 0, "numpy_add_reduce: bad arguments");
+    for (int64_t row = 0; row < rows; ++row) {
+        const int64_t count = offsets[row + 1] - offsets[row];
+        MCB_REQUIRE(count >= 0 && count <= 0x7fffffff, "numpy_add_reduce: offsets are not monotone at %lld", (long long)row);
+        sums[row] = count == 0 ? 0.0f : mcb::numpy_add_reduce_f32(values + offsets[row], (int)count);
+    }
     return MCB_OK;
 }
 

@@ -18,6 +18,7 @@
 #include <type_traits>
 #include <algorithm>
 
+#include "numpy_sum.cuh"
 #include "common.cuh"
 #include "select.cuh"
 #include "prune_mirror.cuh"
@@ -435,7 +436,11 @@ __global__ void __launch_bounds__(256) merge_preserved_kernel(MergeParams p) {
 
 // ---- weigh_edges ---------------------------------------------------------------------------------------
 
-// float32 row sums accumulated left to right as scipy's csr_matvec does; scale = 1 / sum.
+// float32 row sums as scipy's csr sum(axis=1) makes them (np.add.reduceat: numpy's pairwise order, numpy_sum.cuh); scale =
+// 1 / sum.  A sum that is exact in float32 is the same in every order, and the balanced ranks of a pile's graph (multiples
+// of 1/8, totals below 2^21) are: the left-to-right sum is kept whenever the float64 sum says it is exact, numpy's order is
+// followed where it is not (graphs with k beyond ~1000: the grouping piles of a small atlas, k = n - 1 = 1864 -- there the
+// left-to-right sum is off by up to 4e-6 and the optimiser's "outgoing weights sum to 1" assertion fails).
 __global__ void row_scale_kernel(const float* __restrict__ data, const int32_t* __restrict__ indptr, int64_t n,
                                  float* __restrict__ scale, int32_t* __restrict__ min_size) {
     const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -443,7 +448,14 @@ __global__ void row_scale_kernel(const float* __restrict__ data, const int32_t* 
     if (row < n) {
         const int lo = indptr[row], hi = indptr[row + 1];
         float sum = 0.0f;
-        for (int e = lo; e < hi; ++e) sum = __fadd_rn(sum, data[e]);
+        double wide = 0.0;
+        for (int e = lo; e < hi; ++e) {
+            const float value = data[e];
+            sum = __fadd_rn(sum, value);
+            wide = __dadd_rn(wide, (double)value);
+        }
+        if ((double)sum != wide && hi > lo)
+            sum = numpy_add_reduce_f32(data + lo, hi - lo);
         scale[row] = __frcp_rn(sum);  // np.reciprocal
         size = hi - lo;
     }

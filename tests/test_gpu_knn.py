@@ -212,6 +212,27 @@ def test_knn_graph_matches_oracle(cells, k, ties):
     assert np.allclose(np.asarray(weights.sum(axis=1)).reshape(-1), 1.0, atol=1e-5)
 
 
+def test_knn_graph_of_every_other_node_matches_oracle():
+    """k = n - 1 = 1864 (the grouping pile of a 60 000-cell atlas): rows of 1 864 balanced ranks between 4 000 and 5 900 whose
+    float32 totals are not exact, so the weights depend on the order scipy's `sum(axis=1)` adds them in (numpy's pairwise
+    order, csrc/numpy_sum.cuh); summed left to right the rows are off by up to 4e-6 and `optimize_partitions` refuses the
+    graph ("the outgoing weights of every node sum to 1", partitions.cpp:182-183)."""
+    from metacells_b200 import tools as tl
+
+    sim = _similarity(1865, 4, ties=False)
+    expected_weights, expected_pruned, _, expected_k = oracle.knn_graph(sim, 1864)
+    weights, pruned, used_k = tl.compute_obs_obs_knn_graph(sim, k=1864, return_details=True)
+    assert used_k == expected_k == 1864
+    _assert_same_csr(pruned, expected_pruned)
+    _assert_same_csr(weights, expected_weights)
+    totals = np.array([weights.data[weights.indptr[row]:weights.indptr[row + 1]].astype("float64").sum() for row in range(1865)])
+    assert np.abs(totals - 1).max() < 1e-6
+    rows = np.arange(1865)
+    left_to_right = np.array([np.cumsum(expected_pruned.data[expected_pruned.indptr[row]:expected_pruned.indptr[row + 1]],
+                                        dtype="float32")[-1] for row in rows])
+    assert (left_to_right != np.asarray(expected_pruned.sum(axis=1)).reshape(-1)).sum() > 900  # the order matters here
+
+
 def test_knn_graph_grows_k_until_min_degree():
     from metacells_b200 import tools as tl
 
